@@ -1,0 +1,130 @@
+/* pwc_b200.h -- C ABI of libpwc_b200.so: the B200 (sm_100a) PWC-Net inference hot path.
+ *
+ * Drop-in boundary.  Every entry point takes plain device pointers, sizes and a CUDA stream
+ * handle (void* == cudaStream_t), returns a cudaError_t as int (0 == success), never throws,
+ * never allocates, never synchronises.  No torch types appear here.  The reference interfaces
+ * each one replaces are cited as /root/reference paths (file:line).
+ *
+ * Activation layout inside the library ("NHWC + pitch"): element (n,y,x,c) of a tensor lives at
+ *     base[((n*H + y)*W + x) * pitch + coff + c]
+ * so a layer can read/write a channel slice of a wider buffer (the DenseNet concat buffer of
+ * PWCNet.py:202-264 is ONE such buffer per level; no torch.cat ever runs).
+ * dtype codes: PWC_F32 = 0, PWC_BF16 = 1.
+ */
+#ifndef PWC_B200_H_
+#define PWC_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PWC_F32 0
+#define PWC_BF16 1
+
+#define PWC_LAYOUT_NHWC 0
+#define PWC_LAYOUT_NCHW 1
+
+/* Library / build identification. Returns e.g. 100 for an sm_100a build. */
+int pwc_b200_arch(void);
+const char* pwc_b200_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * (1) API-compatible cost volume: replaces correlation_cuda.forward()
+ *     models/correlation_package/correlation_cuda.cc:10-87 (binding),
+ *     models/correlation_package/correlation_cuda_kernel.cu:46-147 (channels_first + correlation_forward)
+ *     for the PWC-Net configuration pad_size = max_displacement = md, kernel_size = 1,
+ *     stride1 = stride2 = 1 (PWCNet.py:71).
+ *   f1, f2 : [B,C,H,W] contiguous NCHW, dtype fp32
+ *   out    : [B,(2md+1)^2,H,W] contiguous NCHW fp32;
+ *            out[n,(dy+md)*(2md+1)+(dx+md),y,x] = (1/C) * sum_c f1[n,c,y,x]*f2[n,c,y+dy,x+dx], 0 outside.
+ *   No rInput1/rInput2 scratch is needed (the padded NHWC copies of correlation_cuda.cc:36-41 are gone).
+ * ------------------------------------------------------------------------------------------ */
+int pwc_corr_fwd(const void* f1, const void* f2, void* out,
+                 int B, int C, int H, int W, int md, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (2) Fused warp + validity mask + cost volume + LeakyReLU: replaces, in one kernel,
+ *     PWCDCNet.warp (PWCNet.py:141-177), self.corr (correlation_cuda_kernel.cu:46-147 + the three
+ *     fill_ of correlation_cuda.cc:40-42) and self.leakyRELU (PWCNet.py:199,214,228,242,258).
+ *   f1   : features of image 1, element (n,y,x,c) at f1[((n*H+y)*W+x)*f1_pitch + c]   (NHWC)
+ *          or f1[((n*C+c)*H+y)*W+x] when layout == PWC_LAYOUT_NCHW (pitches ignored)
+ *   f2   : features of image 2, same convention with f2_pitch
+ *   flow : NULL (level 6: no warp, PWCNet.py:198) or the upsampled flow, element (n,y,x,k),
+ *          k=0:u(x) k=1:v(y), at flow[((n*H+y)*W+x)*flow_pitch + k] (NHWC) / [((n*2+k)*H+y)*W+x] (NCHW)
+ *   flow_scale  : 20/2^L (PWCNet.py:212,226,240,256)
+ *   align_corners : 0 = how the reference runs under torch>=1.3 (grid_sample default); 1 = 2018 semantics
+ *   mask_thresh : 0.9999f (PWCNet.py:174);  slope : 0.1f LeakyReLU (1.0f = none)
+ *   out  : 81 channels, element (n,y,x,k) at out[((n*H+y)*W+x)*out_pitch + k] (NHWC)
+ *          or out[((n*81+k)*H+y)*W+x] (NCHW)
+ *   dtype: PWC_F32 or PWC_BF16 for f1/f2/out (flow is always fp32); arithmetic is fp32.
+ * ------------------------------------------------------------------------------------------ */
+int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void* f2, long f2_pitch,
+                            const float* flow, long flow_pitch, float flow_scale,
+                            int align_corners, float mask_thresh, float slope,
+                            void* out, long out_pitch,
+                            int B, int C, int H, int W, int md,
+                            int layout, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (3) fp32 convolution on CUDA cores (exact-fp32 mode and the thin layers): 3x3, stride 1|2,
+ *     dilation d, padding d, fused bias + LeakyReLU(slope); replaces nn.Conv2d + nn.LeakyReLU
+ *     of conv() (PWCNet.py:26-30) and predict_flow() (PWCNet.py:32-33).
+ *   in   : NHWC+pitch fp32; reads channels [in_coff, in_coff+Cin) (Cin, in_coff, in_pitch % 4 == 0);
+ *          in2 (may be NULL) is the source for images n >= n_split (same split as the outputs below)
+ *   w    : packed [9][CinP][CoutP] fp32, CinP = roundup(Cin,16), CoutP = roundup(Cout,64), zero padded
+ *          (pwc_pack_conv_weight_f32 below produces it from the torch [Cout,Cin,3,3] tensor)
+ *   bias : [Cout] fp32
+ *   out  : NHWC+pitch fp32; images n < n_split go to out (pitch/coff), images n >= n_split go to
+ *          out2 (index n - n_split) -- lets the siamese pyramid write image-1 features straight into
+ *          the concat buffer and image-2 features into their own tensor. n_split >= N disables it.
+ *   slope: 0.1f for conv(), 1.0f for predict_flow (no activation)
+ * ------------------------------------------------------------------------------------------ */
+int pwc_conv3x3_f32_fwd(const float* in, long in_pitch, int in_coff,
+                        const float* in2, long in2_pitch, int in2_coff, int Cin,
+                        const float* w, const float* bias,
+                        float* out, long out_pitch, int out_coff,
+                        float* out2, long out2_pitch, int out2_coff, int n_split,
+                        int Cout, int N, int Hin, int Win, int stride, int dil, float slope,
+                        const float* residual, long res_pitch,
+                        void* stream);
+
+/* Host-side helper (runs on the given stream, device pointers): torch conv weight [Cout,Cin,3,3]
+ * -> [9][CinP][CoutP]; input channel i of the layer lands at packed row chan_map[i] (NULL = identity). */
+int pwc_pack_conv_weight_f32(const float* w_torch, float* w_packed, const int* chan_map,
+                             int Cout, int Cin, int CinP, int CoutP, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (4) Two-channel transposed convolution 4x4, stride 2, padding 1 (+bias, no activation):
+ *     replaces deconv() (PWCNet.py:35-36) for deconvL (2->2) and upfeatL (od+448 -> 2),
+ *     PWCNet.py:208-209,222-223,236-237,252-253.
+ *   in  : NHWC+pitch fp32, channels [in_coff, in_coff+Cin), spatial Hin x Win
+ *   w   : torch ConvTranspose2d layout [Cin,2,4,4] fp32 with chan_map applied by the caller (see packer)
+ *         packed as [16 taps][2][CinP]
+ *   out : NHWC+pitch fp32, 2 channels at out_coff, spatial 2Hin x 2Win; out_f32b (optional, may be NULL)
+ *         receives a second copy with pitch 2 (the flow tensor the next level's warp reads).
+ * ------------------------------------------------------------------------------------------ */
+int pwc_deconv4x4s2_c2_f32_fwd(const float* in, long in_pitch, int in_coff, int Cin,
+                               const float* w, const float* bias,
+                               float* out, long out_pitch, int out_coff,
+                               float* out_b, long out_b_pitch,
+                               int N, int Hin, int Win, void* stream);
+
+int pwc_pack_deconv_weight_f32(const float* w_torch, float* w_packed, const int* chan_map,
+                               int Cin, int CinP, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (5) Input / output format kernels (the tensor the drivers build: [B,6,H,W] fp32 NCHW,
+ *     inference.py:217-223, pwc_extract_flow_video.py:204-206; flow2 returned as [B,2,H/4,W/4]).
+ *   pwc_pack_input : x[B,6,H,W] -> NHWC [2B,H,W,4] (channel 3 = 0); images 0..B-1 = im1, B..2B-1 = im2
+ *   pwc_unpack_flow: NHWC [B,h,w,pitch] channels [coff,coff+2) -> NCHW [B,2,h,w], times `scale`
+ * ------------------------------------------------------------------------------------------ */
+int pwc_pack_input_f32(const float* x, float* out, int B, int H, int W, void* stream);
+int pwc_unpack_flow_f32(const float* in, long in_pitch, int in_coff, float* out,
+                        int B, int H, int W, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PWC_B200_H_ */

@@ -1,0 +1,77 @@
+"""ctypes binding of libpwc_b200.so (the C ABI declared in include/pwc_b200.h).
+
+The product path has no CPU fallback: if the library is missing or a CUDA device is absent the
+callers raise.  ``load()`` builds the library in-tree when the sources are newer (nvcc, sm_100a).
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpwc_b200.so")
+_lib = None
+
+F32, BF16 = 0, 1
+NHWC, NCHW = 0, 1
+
+_vp, _i, _l, _f = ctypes.c_void_p, ctypes.c_int, ctypes.c_long, ctypes.c_float
+
+SIGNATURES = {
+    "pwc_b200_arch": (_i, []),
+    "pwc_b200_version": (ctypes.c_char_p, []),
+    "pwc_corr_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "pwc_warp_corr_lrelu_fwd": (_i, [_vp, _l, _vp, _l, _vp, _l, _f, _i, _f, _f, _vp, _l,
+                                     _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "pwc_conv3x3_f32_fwd": (_i, [_vp, _l, _i, _vp, _l, _i, _i, _vp, _vp, _vp, _l, _i, _vp, _l, _i, _i,
+                                 _i, _i, _i, _i, _i, _i, _f, _vp, _l, _vp]),
+    "pwc_pack_conv_weight_f32": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "pwc_deconv4x4s2_c2_f32_fwd": (_i, [_vp, _l, _i, _i, _vp, _vp, _vp, _l, _i, _vp, _l, _i, _i, _i, _vp]),
+    "pwc_pack_deconv_weight_f32": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "pwc_pack_input_f32": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "pwc_unpack_flow_f32": (_i, [_vp, _l, _i, _vp, _i, _i, _i, _f, _vp]),
+}
+
+
+class PwcLibraryError(RuntimeError):
+    pass
+
+
+def load(build_if_needed=True):
+    """Load (building first if sources are newer and nvcc exists).  Raises PwcLibraryError if unavailable."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if build_if_needed:
+        try:
+            from . import build as _build
+            if _build.needs_build() and os.path.exists(_build.NVCC):
+                _build.build()
+        except Exception as e:  # noqa: BLE001
+            if not os.path.isfile(LIB_PATH):
+                raise PwcLibraryError(f"libpwc_b200.so is not built and could not be built: {e}") from e
+    if not os.path.isfile(LIB_PATH):
+        raise PwcLibraryError(f"{LIB_PATH} not found: run `python -m opticalflow_b200.build`")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as e:
+            raise PwcLibraryError(f"libpwc_b200.so does not export {name}") from e
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(err, what):
+    if err != 0:
+        raise RuntimeError(f"{what}: CUDA call failed (cudaError {err})")
+
+
+def ptr(t):
+    """data pointer of a torch tensor (or None)."""
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def stream_handle():
+    import torch
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,86 @@
+"""Functional wrappers over the C ABI for tests, the microbenchmark and callers that hold torch tensors."""
+import torch
+
+from . import _lib
+
+
+def warp_corr_lrelu(f1, f2, flow=None, flow_scale=1.0, align_corners=False, mask_thresh=0.9999, slope=0.1,
+                    layout="nchw", out=None):
+    """Fused warp + mask + 81-channel cost volume + LeakyReLU (pwc_warp_corr_lrelu_fwd).
+
+    layout 'nchw': f1,f2 [B,C,H,W], flow [B,2,H,W] -> out [B,81,H,W] (fp32).
+    layout 'nhwc': f1,f2 [B,H,W,C] (last dim may be a wider pitch via .stride(2)), flow [B,H,W,2], out [B,H,W,81]
+                   fp32 or bf16 features.
+    """
+    lib = _lib.load()
+    if not f1.is_cuda:
+        raise RuntimeError("warp_corr_lrelu: CUDA tensors required (no CPU fallback)")
+    st = _lib.stream_handle()
+    if layout == "nchw":
+        f1, f2 = f1.contiguous(), f2.contiguous()
+        B, C, H, W = f1.shape
+        flow = None if flow is None else flow.contiguous().float()
+        if out is None:
+            out = torch.empty(B, 81, H, W, device=f1.device, dtype=torch.float32)
+        e = lib.pwc_warp_corr_lrelu_fwd(_lib.ptr(f1), 0, _lib.ptr(f2), 0, _lib.ptr(flow), 0, float(flow_scale),
+                                        int(align_corners), mask_thresh, slope, _lib.ptr(out), 0,
+                                        B, C, H, W, 4, _lib.NCHW, _lib.F32, st)
+    else:
+        B, H, W, C = f1.shape
+        assert f1.stride(3) == 1 and f2.stride(3) == 1
+        dt = _lib.BF16 if f1.dtype == torch.bfloat16 else _lib.F32
+        flow = None if flow is None else flow.contiguous().float()
+        if out is None:
+            out = torch.empty(B, H, W, 81, device=f1.device, dtype=f1.dtype)
+        e = lib.pwc_warp_corr_lrelu_fwd(_lib.ptr(f1), f1.stride(2), _lib.ptr(f2), f2.stride(2), _lib.ptr(flow), 2,
+                                        float(flow_scale), int(align_corners), mask_thresh, slope,
+                                        _lib.ptr(out), out.stride(2), B, C, H, W, 4, _lib.NHWC, dt, st)
+    _lib.check(e, "pwc_warp_corr_lrelu_fwd")
+    return out
+
+
+def conv3x3_f32(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=None, out=None, out_coff=0,
+                chan_map=None, residual=None):
+    """fp32 CUDA-core conv (pwc_conv3x3_f32_fwd) on an NHWC tensor x [N,H,W,pitch]; reads channels
+    [in_coff, in_coff+cin_span); weight is the torch [Cout,Cin,3,3] tensor (packed here, per call)."""
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    N, H, W, pitch = x.shape
+    cout, cin = weight.shape[:2]
+    span = cin_span if cin_span is not None else cin
+    cinp, coutp = (span + 15) // 16 * 16, (cout + 63) // 64 * 64
+    wp = torch.empty(9 * cinp * coutp, device=x.device, dtype=torch.float32)
+    mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
+    w32 = weight.detach().float().contiguous()
+    _lib.check(lib.pwc_pack_conv_weight_f32(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), cout, cin, cinp, coutp, st), "pack")
+    ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    if out is None:
+        out = torch.zeros(N, ho, wo, cout, device=x.device, dtype=torch.float32)
+    b32 = bias.detach().float().contiguous()
+    e = lib.pwc_conv3x3_f32_fwd(_lib.ptr(x), pitch, in_coff, None, 0, 0, span, _lib.ptr(wp), _lib.ptr(b32),
+                                _lib.ptr(out), out.shape[-1], out_coff, None, 0, 0, N, cout, N, H, W, stride, dil,
+                                slope, _lib.ptr(residual), (residual.shape[-1] if residual is not None else 0), st)
+    _lib.check(e, "pwc_conv3x3_f32_fwd")
+    torch.cuda.current_stream().synchronize()
+    return out
+
+
+def deconv4x4s2_c2_f32(x, weight, bias, in_coff=0, cin_span=None, chan_map=None):
+    """2-channel ConvTranspose2d(4,2,1) on NHWC x [N,H,W,pitch]; weight torch layout [Cin,2,4,4]."""
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    N, H, W, pitch = x.shape
+    cin = weight.shape[0]
+    span = cin_span if cin_span is not None else (cin + 3) // 4 * 4
+    cinp = (span + 3) // 4 * 4
+    wp = torch.empty(32 * cinp, device=x.device, dtype=torch.float32)
+    mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
+    w32 = weight.detach().float().contiguous()
+    _lib.check(lib.pwc_pack_deconv_weight_f32(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), cin, cinp, st), "pack")
+    out = torch.zeros(N, 2 * H, 2 * W, 2, device=x.device, dtype=torch.float32)
+    b32 = bias.detach().float().contiguous()
+    e = lib.pwc_deconv4x4s2_c2_f32_fwd(_lib.ptr(x), pitch, in_coff, span, _lib.ptr(wp), _lib.ptr(b32),
+                                       _lib.ptr(out), 2, 0, None, 0, N, H, W, st)
+    _lib.check(e, "pwc_deconv4x4s2_c2_f32_fwd")
+    torch.cuda.current_stream().synchronize()
+    return out
