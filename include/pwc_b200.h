@@ -124,6 +124,33 @@ int pwc_pack_input_f32(const float* x, float* out, int B, int H, int W, void* st
 int pwc_unpack_flow_f32(const float* in, long in_pitch, int in_coff, float* out,
                         int B, int H, int W, float scale, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * (6) bf16 tensor-core convolution (tcgen05.mma + TMEM + TMA implicit GEMM), 3x3, stride 1|2, dilation d,
+ *     padding d, fused bias + LeakyReLU; same role as (3) for the bf16-conv mode (conv(), PWCNet.py:26-30;
+ *     decoder PWCNet.py:202-264; context net PWCNet.py:126-132,267-268; predict_flow PWCNet.py:32-33).
+ *   A descriptor object holds the TMA tensor maps (they embed the buffer addresses), so it is created once per
+ *   (layer, buffers, shape) -- host memory only -- and launched many times.  create/destroy are host calls;
+ *   launch enqueues one kernel on `stream`.
+ *   in/in2 : bf16 NHWC+pitch, channels [coff, coff+cin_span); cin_span % kc == 0, kc in {16,32,64};
+ *            pitch and coff multiples of 8.  in2 (may be NULL) serves images n >= n_split.
+ *   w      : packed bf16 [9][cin_span/kc][coutp][kc] (pwc_pack_conv_weight_bf16), coutp % 16 == 0, <= 256
+ *   out    : out_f32 == 0: bf16 NHWC+pitch slice (all coutp channels are written; pad channels get 0);
+ *            out_f32 == 1: fp32, channels < cout only, plus optional fp32 residual (dc_conv7 + flow2, PWCNet.py:268)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct pwc_tc_conv pwc_tc_conv;
+int pwc_tc_conv_create(pwc_tc_conv** handle,
+                       const void* in, long in_pitch, int in_coff,
+                       const void* in2, long in2_pitch, int in2_coff, int n_split, int cin_span, int kc,
+                       const void* w_packed, const float* bias, int cout, int coutp,
+                       void* out, long out_pitch, int out_coff,
+                       void* out2, long out2_pitch, int out2_coff, int out_f32,
+                       const float* residual, long res_pitch,
+                       int N, int Hin, int Win, int stride, int dil, float slope);
+int pwc_tc_conv_launch(const pwc_tc_conv* handle, void* stream);
+void pwc_tc_conv_destroy(pwc_tc_conv* handle);
+int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, const int* chan_map,
+                              int Cout, int Cin, int cin_span, int kc, int coutp, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,11 @@ SIGNATURES = {
     "pwc_pack_conv_weight_f32": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "pwc_deconv4x4s2_c2_f32_fwd": (_i, [_vp, _l, _i, _i, _vp, _vp, _vp, _l, _i, _vp, _l, _i, _i, _i, _vp]),
     "pwc_pack_deconv_weight_f32": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "pwc_tc_conv_create": (_i, [ctypes.POINTER(_vp), _vp, _l, _i, _vp, _l, _i, _i, _i, _i, _vp, _vp, _i, _i,
+                                _vp, _l, _i, _vp, _l, _i, _i, _vp, _l, _i, _i, _i, _i, _i, _f]),
+    "pwc_tc_conv_launch": (_i, [_vp, _vp]),
+    "pwc_tc_conv_destroy": (None, [_vp]),
+    "pwc_pack_conv_weight_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "pwc_pack_input_f32": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "pwc_unpack_flow_f32": (_i, [_vp, _l, _i, _vp, _i, _i, _i, _f, _vp]),
 }

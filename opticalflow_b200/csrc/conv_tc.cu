@@ -1,0 +1,297 @@
+// bf16 implicit-GEMM 3x3 convolution on the 5th-gen tensor cores (tcgen05.mma, accumulators in TMEM, operands staged
+// by TMA), fused bias + LeakyReLU epilogue that writes straight into a channel slice of the concat buffer.
+// Replaces nn.Conv2d + nn.LeakyReLU of conv() (/root/reference/models/PWCNet.py:26-30) for the decoder
+// (PWCNet.py:202-264), the context network (PWCNet.py:126-132,267-268) and the stride-1 pyramid layers.
+//
+// GEMM view: D[128 pixels, Cout] += A[128 pixels, KC] * W[Cout, KC]^T for each (tap, KC-channel chunk).
+//   * M tile = 8x16 output pixels of one image.  For tap (ky,kx) the A tile is the SAME box of the NHWC tensor shifted
+//     by ((ky-1)*dil, (kx-1)*dil): one 4-D TMA box (KC, 16, 8, 1); out-of-image coordinates are zero-filled by TMA,
+//     which implements the convolution padding.  The box lands in smem as 128 rows of KC bf16 = the K-major
+//     SWIZZLE_{128,64,32}B layout tcgen05 consumes.
+//   * weights are pre-packed [tap][chunk][CoutP][KC] bf16: one 2-D TMA box (KC, CoutP) per (tap, chunk).
+//   * warp roles (192 threads): warp0 = TMA producer, warp1 = TMEM allocator + single-thread MMA issuer,
+//     warps2-5 = epilogue (tcgen05.ld -> bias/LeakyReLU -> bf16/fp32 global stores).  Persistent over tiles, TMEM
+//     accumulator double-buffered so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+#include "tmap.cuh"
+#include "../../include/pwc_b200.h"
+
+#include <new>
+
+namespace pwc {
+
+constexpr int kTcTH = 8, kTcTW = 16, kTcM = 128, kTcThreads = 192;
+
+struct TcConvParams {
+  int N, Hin, Win, Hout, Wout, stride, dil;
+  int cout, coutp, kc, nchunk, n_split;
+  int tiles_x, tiles_y, num_tiles, stages;
+  uint32_t a_bytes, stage_bytes, tmem_cols;
+  const float* bias; float slope;
+  void* out; long out_pitch; int out_coff;
+  void* out2; long out2_pitch; int out2_coff;
+  int out_f32;
+  const float* residual; long res_pitch;
+};
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+               const __grid_constant__ CUtensorMap tmB, const TcConvParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-B aligned base (SWIZZLE_128B atoms)
+  const uint32_t base = (ptx::smem_addr(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = base + p.stages * p.stage_bytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (p.stages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * p.stages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * p.stages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * p.stages + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_addr(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ksteps = 9 * p.nchunk;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA0); ptx::prefetch_tmap(&tmA1); ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < p.stages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 4); }
+    ptx::fence_barrier_init();
+    ptx::fence_proxy_async();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, p.tmem_cols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
+        const int n = t / (p.tiles_x * p.tiles_y);
+        const int r = t - n * (p.tiles_x * p.tiles_y);
+        const int ty0 = (r / p.tiles_x) * kTcTH, tx0 = (r % p.tiles_x) * kTcTW;
+        const CUtensorMap* tmA = (n >= p.n_split) ? &tmA1 : &tmA0;
+        const int nn = (n >= p.n_split) ? n - p.n_split : n;
+        for (int tap = 0; tap < 9; ++tap) {
+          const int ky = tap / 3, kx = tap - 3 * ky;
+          const int y = ty0 * p.stride + (ky - 1) * p.dil, x = tx0 * p.stride + (kx - 1) * p.dil;
+          for (int ch = 0; ch < p.nchunk; ++ch) {
+            ptx::mbar_wait(empty_bar(s), ph ^ 1);
+            const uint32_t sa = base + s * p.stage_bytes;
+            ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (uint32_t)p.coutp * p.kc * 2);
+            ptx::tma_load_4d(sa, tmA, full_bar(s), ch * p.kc, x, y, nn);
+            ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * p.nchunk + ch) * p.coutp);
+            if (++s == p.stages) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      const uint32_t idesc = ptx::make_idesc_bf16(kTcM, p.coutp);
+      const uint32_t row_bytes = p.kc * 2;
+      const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
+      int s = 0; uint32_t ph = 0;
+      int acc = 0; uint32_t aph = 0;
+      for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
+        ptx::mbar_wait(tempty_bar(acc), aph ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.coutp);
+        for (int k = 0; k < ksteps; ++k) {
+          ptx::mbar_wait(full_bar(s), ph);
+          ptx::tc_fence_after();
+          const uint32_t sa = base + s * p.stage_bytes;
+          const uint64_t da = ptx::make_kmajor_desc(sa, 8 * row_bytes, ltype);
+          const uint64_t db = ptx::make_kmajor_desc(sa + p.a_bytes, 8 * row_bytes, ltype);
+          for (int kk = 0; kk < p.kc / 16; ++kk)
+            ptx::umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (k | kk) ? 1u : 0u);
+          ptx::umma_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
+          if (++s == p.stages) { s = 0; ph ^= 1; }
+        }
+        ptx::umma_commit(tfull_bar(acc));          // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; aph ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5 =====================
+    const int lg = warp & 3;                       // TMEM lane group this warp may access
+    const int m = lg * 32 + lane;                  // pixel within the tile
+    const int py = m >> 4, px = m & 15;
+    int acc = 0; uint32_t aph = 0;
+    for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
+      const int n = t / (p.tiles_x * p.tiles_y);
+      const int r = t - n * (p.tiles_x * p.tiles_y);
+      const int oy = (r / p.tiles_x) * kTcTH + py, ox = (r % p.tiles_x) * kTcTW + px;
+      const bool live = (oy < p.Hout) && (ox < p.Wout);
+      const bool second = (n >= p.n_split) && (p.out2 != nullptr);
+      const int nn = second ? n - p.n_split : n;
+      const long pix = ((long)nn * p.Hout + oy) * p.Wout + ox;
+      ptx::mbar_wait(tfull_bar(acc), aph);
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * p.coutp);
+      for (int c0 = 0; c0 < p.coutp; c0 += 16) {
+        uint32_t v[16];
+        ptx::tmem_ld16(taddr + c0, v);
+        ptx::tmem_ld_wait();
+        if (live) {
+          float f[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int co = c0 + i;
+            const float b = (co < p.cout) ? __ldg(p.bias + co) : 0.f;
+            f[i] = lrelu(__uint_as_float(v[i]) + b, p.slope);
+          }
+          if (p.out_f32) {
+            float* o = reinterpret_cast<float*>(p.out) + pix * p.out_pitch + p.out_coff;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int co = c0 + i;
+              if (co < p.cout) {
+                float val = f[i];
+                if (p.residual) val += p.residual[pix * p.res_pitch + co];
+                o[co] = val;
+              }
+            }
+          } else {
+            __nv_bfloat16* o = second ? reinterpret_cast<__nv_bfloat16*>(p.out2) + pix * p.out2_pitch + p.out2_coff
+                                      : reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.out_pitch + p.out_coff;
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+              w[i] = *reinterpret_cast<uint32_t*>(&h);
+            }
+            uint4* o4 = reinterpret_cast<uint4*>(o + c0);
+            o4[0] = make_uint4(w[0], w[1], w[2], w[3]);
+            o4[1] = make_uint4(w[4], w[5], w[6], w[7]);
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty_bar(acc));
+      if (++acc == 2) { acc = 0; aph ^= 1; }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+}  // namespace pwc
+
+// ------------------------------------------------------------------------------------------------------------------
+// host side: descriptor object (tensor maps + parameters), launch, weight packing
+// ------------------------------------------------------------------------------------------------------------------
+struct pwc_tc_conv {
+  CUtensorMap tmA0, tmA1, tmB;
+  pwc::TcConvParams p;
+  size_t smem_bytes;
+  int grid;
+};
+
+namespace pwc {
+
+__global__ void pack_conv_weight_bf16_kernel(const float* __restrict__ wt, __nv_bfloat16* __restrict__ wp,
+                                             const int* __restrict__ map, int Cout, int Cin, int nchunk, int kc, int coutp) {
+  // wt: [Cout][Cin][3][3] fp32 -> wp: [9][nchunk][coutp][kc] bf16 (pre-zeroed)
+  const long total = (long)Cout * Cin * 9;
+  for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+    const int tap = e % 9; const long r = e / 9;
+    const int ci = r % Cin, co = r / Cin;
+    const int row = map ? map[ci] : ci;
+    const int ch = row / kc, kk = row - ch * kc;
+    wp[(((long)tap * nchunk + ch) * coutp + co) * kc + kk] = __float2bfloat16_rn(wt[e]);
+  }
+}
+
+static int g_num_sms = 0;
+
+}  // namespace pwc
+
+extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
+                                  const void* in, long in_pitch, int in_coff,
+                                  const void* in2, long in2_pitch, int in2_coff, int n_split, int cin_span, int kc,
+                                  const void* w_packed, const float* bias, int cout, int coutp,
+                                  void* out, long out_pitch, int out_coff,
+                                  void* out2, long out2_pitch, int out2_coff, int out_f32,
+                                  const float* residual, long res_pitch,
+                                  int N, int Hin, int Win, int stride, int dil, float slope) {
+  using namespace pwc;
+  if (!handle) return (int)cudaErrorInvalidValue;
+  *handle = nullptr;
+  if ((kc != 16 && kc != 32 && kc != 64) || cin_span % kc || coutp % 16 || coutp < 16 || coutp > 256 || cout > coutp ||
+      (in_pitch & 7) || (in_coff & 7) || (in2 && ((in2_pitch & 7) || (in2_coff & 7))) ||
+      (!out_f32 && ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7))))) ||
+      (stride != 1 && stride != 2))
+    return (int)cudaErrorInvalidValue;
+  pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
+  if (!h) return (int)cudaErrorMemoryAllocation;
+  TcConvParams& p = h->p;
+  p.N = N; p.Hin = Hin; p.Win = Win; p.stride = stride; p.dil = dil;
+  p.Hout = (Hin - 1) / stride + 1; p.Wout = (Win - 1) / stride + 1;
+  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cin_span / kc;
+  p.n_split = (in2 || out2) ? n_split : N;
+  p.tiles_x = cdiv(p.Wout, kTcTW); p.tiles_y = cdiv(p.Hout, kTcTH); p.num_tiles = p.tiles_x * p.tiles_y * N;
+  p.a_bytes = (uint32_t)kTcM * kc * 2;
+  p.stage_bytes = (p.a_bytes + (uint32_t)coutp * kc * 2 + 1023u) & ~1023u;
+  int stages = (int)((200u * 1024u) / p.stage_bytes);
+  p.stages = stages > 8 ? 8 : (stages < 2 ? 2 : stages);
+  uint32_t cols = 32; while (cols < 2u * coutp) cols <<= 1;
+  if (cols > 512) { delete h; return (int)cudaErrorInvalidValue; }
+  p.tmem_cols = cols;
+  p.bias = bias; p.slope = slope;
+  p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
+  p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff;
+  p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
+  h->smem_bytes = (size_t)p.stages * p.stage_bytes + 8 * (2 * p.stages + 5) + 1024;
+  const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
+  const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
+  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, Win, Hin,
+                         in2 ? p.n_split : N, kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
+  if (!e) {
+    if (in2) {
+      const __nv_bfloat16* a1 = reinterpret_cast<const __nv_bfloat16*>(in2) + in2_coff;
+      e = make_tmap_nhwc(&h->tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a1, in2_pitch, cin_span, Win, Hin, N - p.n_split,
+                         kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
+    } else {
+      h->tmA1 = h->tmA0;
+    }
+  }
+  if (!e) e = make_tmap_2d(&h->tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w_packed, (long)9 * p.nchunk * coutp, kc, kc, coutp, swz);
+  if (e) { delete h; return e; }
+  if (!g_num_sms) {
+    int dev = 0; cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+    cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  }
+  h->grid = p.num_tiles < g_num_sms ? p.num_tiles : g_num_sms;
+  *handle = h;
+  return 0;
+}
+
+extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
+  if (!h) return (int)cudaErrorInvalidValue;
+  pwc::conv_tc_kernel<<<h->grid, pwc::kTcThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmA1, h->tmB, h->p);
+  return (int)cudaGetLastError();
+}
+
+extern "C" void pwc_tc_conv_destroy(pwc_tc_conv* h) { delete h; }
+
+extern "C" int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, const int* chan_map,
+                                         int Cout, int Cin, int cin_span, int kc, int coutp, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (cin_span % kc) return (int)cudaErrorInvalidValue;
+  const int nchunk = cin_span / kc;
+  cudaError_t e = cudaMemsetAsync(w_packed, 0, 2 * (size_t)9 * nchunk * coutp * kc, s);
+  if (e != cudaSuccess) return (int)e;
+  pwc::pack_conv_weight_bf16_kernel<<<256, 256, 0, s>>>(w_torch, reinterpret_cast<__nv_bfloat16*>(w_packed), chan_map,
+                                                        Cout, Cin, nchunk, kc, coutp);
+  return (int)cudaGetLastError();
+}

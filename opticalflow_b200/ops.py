@@ -84,3 +84,43 @@ def deconv4x4s2_c2_f32(x, weight, bias, in_coff=0, cin_span=None, chan_map=None)
     _lib.check(e, "pwc_deconv4x4s2_c2_f32_fwd")
     torch.cuda.current_stream().synchronize()
     return out
+
+
+def pick_kc(cin_span):
+    return 64 if cin_span % 64 == 0 else (32 if cin_span % 32 == 0 else 16)
+
+
+def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=None, out=None, out_coff=0,
+               chan_map=None, out_f32=False, residual=None, reps=1):
+    """bf16 tcgen05 conv (pwc_tc_conv_*) on an NHWC bf16 tensor x [N,H,W,pitch]; weight torch [Cout,Cin,3,3] fp32."""
+    import ctypes
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    N, H, W, pitch = x.shape
+    assert x.dtype == torch.bfloat16
+    cout, cin = weight.shape[:2]
+    span = cin_span if cin_span is not None else (cin + 15) // 16 * 16
+    kc = pick_kc(span)
+    coutp = (cout + 15) // 16 * 16
+    wp = torch.empty(9 * span * coutp, device=x.device, dtype=torch.bfloat16)
+    mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
+    w32 = weight.detach().float().contiguous()
+    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), cout, cin, span, kc, coutp, st), "pack")
+    ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    if out is None:
+        out = torch.zeros(N, ho, wo, coutp if not out_f32 else cout, device=x.device,
+                          dtype=torch.float32 if out_f32 else torch.bfloat16)
+    b32 = bias.detach().float().contiguous()
+    h = ctypes.c_void_p()
+    e = lib.pwc_tc_conv_create(ctypes.byref(h), _lib.ptr(x), pitch, in_coff, None, 0, 0, N, span, kc,
+                               _lib.ptr(wp), _lib.ptr(b32), cout, coutp, _lib.ptr(out), out.shape[-1], out_coff,
+                               None, 0, 0, int(out_f32), _lib.ptr(residual),
+                               (residual.shape[-1] if residual is not None else 0), N, H, W, stride, dil, slope)
+    _lib.check(e, "pwc_tc_conv_create")
+    try:
+        for _ in range(reps):
+            _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
+        torch.cuda.current_stream().synchronize()
+    finally:
+        lib.pwc_tc_conv_destroy(h)
+    return out
