@@ -249,7 +249,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--batch", type=int, default=B_DEF)
     ap.add_argument("--height", type=int, default=H_DEF)
     ap.add_argument("--width", type=int, default=W_DEF)

@@ -151,6 +151,21 @@ void pwc_tc_conv_destroy(pwc_tc_conv* handle);
 int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, const int* chan_map,
                               int Cout, int Cin, int cin_span, int kc, int coutp, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * (7) bf16-mode companions (fp32 arithmetic, bf16 storage).
+ *   pwc_conv1a_bf16_fwd : first pyramid layer conv1a (3->16, stride 2, +LeakyReLU; PWCNet.py:52,184,190) fused with
+ *       the im1/im2 split of PWCNet.py:181-182.  x [B,6,H,W] fp32 NCHW (the driver tensor), w torch [16,3,3,3] fp32,
+ *       out bf16 NHWC [2B,H/2,W/2,16]; images 0..B-1 = im1 of each pair, B..2B-1 = im2.
+ *   pwc_deconv4x4s2_c2_fwd : (4) with selectable input / output dtype (PWC_F32 | PWC_BF16); out_b stays fp32.
+ * ------------------------------------------------------------------------------------------ */
+int pwc_conv1a_bf16_fwd(const float* x, const float* w, const float* bias, void* out,
+                        int B, int H, int W, float slope, void* stream);
+int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
+                           const float* w, const float* bias,
+                           void* out, int out_dtype, long out_pitch, int out_coff,
+                           float* out_b, long out_b_pitch,
+                           int N, int Hin, int Win, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -185,6 +185,33 @@ warp_corr_nhwc_kernel(const __grid_constant__ CUtensorMap tmF1, const WarpCorrPa
       const int per_img = p.tiles_x * p.tiles_y;
       const int n = t / per_img, rr = t - n * per_img;
       const int x0 = (rr % p.tiles_x) * kTW, r0 = (rr / p.tiles_x) * ROWS - kMD;
+      // ---- L2 prefetch of the NEXT tile's flow rows and the image-2 rows its samples most likely fall in ----
+      {
+        const int t2 = t + gridDim.x;
+        if (t2 < p.num_tiles) {
+          const int n2 = t2 / per_img, rr2 = t2 - n2 * per_img;
+          const int x02 = (rr2 % p.tiles_x) * kTW, r02 = (rr2 / p.tiles_x) * ROWS - kMD;
+          const int xs = max(x02 - 12, 0), xe = min(x02 + kTW + 12, W);
+          if (ptid < ROWS + 8) {
+            const int y = r02 - 4 + ptid;
+            if (y >= 0 && y < H) {
+              const uintptr_t a = reinterpret_cast<uintptr_t>(f2 + (((long)n2 * H + y) * W + xs) * p.f2_pitch);
+              const uintptr_t e = reinterpret_cast<uintptr_t>(f2 + (((long)n2 * H + y) * W + xe - 1) * p.f2_pitch + C);
+              const uintptr_t a16 = a & ~(uintptr_t)15;
+              ptx::prefetch_l2_bulk(reinterpret_cast<const void*>(a16), (uint32_t)((e - a16 + 15) & ~(uintptr_t)15));
+            }
+          } else if (p.flow != nullptr && ptid >= 32 && ptid < 32 + ROWS) {
+            const int y = r02 + (ptid - 32);
+            if (y >= 0 && y < H) {
+              const int fs = max(x02 - kMD, 0), fe = min(x02 + kTW + kMD, W);
+              const uintptr_t a = reinterpret_cast<uintptr_t>(p.flow + (((long)n2 * H + y) * W + fs) * p.flow_pitch);
+              const uintptr_t e = reinterpret_cast<uintptr_t>(p.flow + (((long)n2 * H + y) * W + fe - 1) * p.flow_pitch + 2);
+              const uintptr_t a16 = a & ~(uintptr_t)15;
+              ptx::prefetch_l2_bulk(reinterpret_cast<const void*>(a16), (uint32_t)((e - a16 + 15) & ~(uintptr_t)15));
+            }
+          }
+        }
+      }
       // ---- per-tile table of sample coordinates / masked corner weights ----
       named_bar_sync(1, kProdWarps * 32);          // everyone is done reading the previous tile's table
       for (int e = ptid; e < G::kW2Pix; e += kProdWarps * 32) {
@@ -229,7 +256,7 @@ warp_corr_nhwc_kernel(const __grid_constant__ CUtensorMap tmF1, const WarpCorrPa
         const bool cok = c < C;
         const T* f2c = f2n + c;
         constexpr int kIters = G::kW2Pix / (kProdWarps * 4);
-        constexpr int kUnroll = (ROWS == 8) ? 2 : 5;
+        constexpr int kUnroll = 5;
 #pragma unroll kUnroll
         for (int itp = 0; itp < kIters; ++itp) {
           const int pix = itp * (kProdWarps * 4) + pw * 4 + sub;

@@ -1,0 +1,246 @@
+"""bf16-conv execution plan of the B200 PWC-Net forward (PWCDCNet.forward, /root/reference/models/PWCNet.py:180-273).
+
+Same buffer plan as engine.Plan (one NHWC concat buffer per level, no torch.cat), but activations are stored in bf16
+and every 3x3 convolution except conv1a runs on the 5th-gen tensor cores (csrc/conv_tc.cu: tcgen05.mma, TMEM
+accumulators, TMA operands, fp32 accumulate, fused bias + LeakyReLU, output written into its concat slice).
+conv1a (Cin = 3) and the 2-channel transposed convolutions are HBM-bound CUDA-core kernels (csrc/misc_bf16.cu); the
+flow tensors (predict_flowL outputs, up_flow read by the warp, final flow2) stay fp32.  The whole forward is a fixed
+launch list and is captured once into a CUDA graph.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+from .engine import (C1_OFF, CORR_OFF, DC, DEC_START, DEC_WRITE, FLOW_SCALE, PYR_CH, UPFEAT_OFF, UPFLOW_OFF, chan_map,
+                     concat_width)
+
+BF = torch.bfloat16
+
+
+def _roundup(a, b):
+    return (a + b - 1) // b * b
+
+
+def _kc(span):
+    return 64 if span % 64 == 0 else (32 if span % 32 == 0 else 16)
+
+
+PYR_CP = [4] + [_roundup(c, 16) for c in PYR_CH[1:]]      # 16, 32, 64, 96, 128, 208
+
+
+class _TcLayer:
+    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp")
+
+
+class PlanBF16:
+    def __init__(self, model, B, H, W, device, align_corners=False, use_graph=True):
+        if H % 64 or W % 64:
+            raise ValueError(f"H and W must be multiples of 64 (6 stride-2 levels), got {H}x{W}")
+        self.lib = _lib.load()
+        self.B, self.H, self.W, self.device = B, H, W, device
+        self.align_corners = int(bool(align_corners))
+        self.use_graph = use_graph
+        zb = lambda *s: torch.zeros(*s, device=device, dtype=BF)            # noqa: E731
+        zf = lambda *s: torch.zeros(*s, device=device, dtype=torch.float32)  # noqa: E731
+        self.x_static = zf(B, 6, H, W)
+        self.hw = {l: (H >> l, W >> l) for l in range(1, 7)}
+        self.pa = {l: zb(2 * B, *self.hw[l], PYR_CP[l]) for l in range(1, 7)}
+        self.pb = {l: zb(2 * B, *self.hw[l], PYR_CP[l]) for l in range(1, 7)}
+        self.cat, self.f2, self.flow, self.upflow = {}, {}, {}, {}
+        for l in range(2, 7):
+            h, w = self.hw[l]
+            self.cat[l] = zb(B, h, w, concat_width(l))
+            self.f2[l] = zb(B, h, w, PYR_CP[l])
+            self.flow[l] = zf(B, h, w, 4)
+            if l < 6:
+                self.upflow[l] = zf(B, h, w, 2)
+        self.f1_6 = zb(B, *self.hw[6], PYR_CP[6])
+        h2, w2 = self.hw[2]
+        self.dc = [zb(B, h2, w2, c) for (_, c, _) in DC]
+        self.flow_out4 = zf(B, h2, w2, 4)
+        self.out = zf(B, 2, h2, w2)
+        self.weights_version = None
+        self.layers = {}
+        self.small = {}
+        self.ops = []
+        self.op_info = []          # (name, algorithmic flops) per launch, for profiling tools
+        self.graph = None
+        self.launches = 0
+
+    def __del__(self):
+        try:
+            for L in self.layers.values():
+                if L.handle:
+                    self.lib.pwc_tc_conv_destroy(L.handle)
+        except Exception:  # noqa: BLE001
+            pass
+
+    # ------------------------------------------------------------------ layer construction
+    def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
+            cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None):
+        L = _TcLayer()
+        L.key, L.cin, L.cout, L.span, L.kc, L.cmap = key, cin, cout, span, _kc(span), cmap
+        L.coutp = _roundup(cout, 16)
+        dev = self.device
+        L.w = torch.zeros(9 * span * L.coutp, device=dev, dtype=BF)
+        L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
+        h = ctypes.c_void_p()
+        e = self.lib.pwc_tc_conv_create(
+            ctypes.byref(h), _lib.ptr(src), src.shape[-1], src_coff,
+            _lib.ptr(src2), (src2.shape[-1] if src2 is not None else 0), src2_coff, n_split, span, L.kc,
+            _lib.ptr(L.w), _lib.ptr(L.b), cout, L.coutp, _lib.ptr(dst), dst.shape[-1], dst_coff,
+            _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32),
+            _lib.ptr(residual), (residual.shape[-1] if residual is not None else 0), N, hin, win, stride, dil, slope)
+        _lib.check(e, f"pwc_tc_conv_create {key}")
+        L.handle = h
+        self.layers[key] = L
+        lib = self.lib
+        ho, wo = (hin - 1) // stride + 1, (win - 1) // stride + 1
+        self.op_info.append((key, 2.0 * N * ho * wo * cout * cin * 9))
+        self.ops.append(lambda st: _lib.check(lib.pwc_tc_conv_launch(h, st), key))
+
+    def _deconv(self, key, cin, src, src_coff, span, dst, dst_coff, hin, win, dst_b=None):
+        dev = self.device
+        cinp = _roundup(span, 4)
+        w = torch.zeros(32 * cinp, device=dev, dtype=torch.float32)
+        b = torch.zeros(2, device=dev, dtype=torch.float32)
+        self.small[key] = (w, b, cin, cinp)
+        lib, B = self.lib, self.B
+        idt = _lib.BF16 if src.dtype == BF else _lib.F32
+        odt = _lib.BF16 if dst.dtype == BF else _lib.F32
+        args = (_lib.ptr(src), idt, src.shape[-1], src_coff, span, _lib.ptr(w), _lib.ptr(b), _lib.ptr(dst), odt,
+                dst.shape[-1], dst_coff, _lib.ptr(dst_b), (dst_b.shape[-1] if dst_b is not None else 0), B, hin, win)
+        self.op_info.append((key, 2.0 * B * hin * win * 4 * 2 * cin * 4))
+        self.ops.append(lambda st: _lib.check(lib.pwc_deconv4x4s2_c2_fwd(*args, st), key))
+
+    def _corr(self, lvl):
+        h, w = self.hw[lvl]
+        cat = self.cat[lvl]
+        C = PYR_CH[lvl]
+        if lvl == 6:
+            f1p, f1_pitch, flow, fp, scale = _lib.ptr(self.f1_6), PYR_CP[6], None, 0, 1.0
+        else:
+            f1p = ctypes.c_void_p(cat.data_ptr() + 2 * C1_OFF)
+            f1_pitch, flow, fp, scale = cat.shape[-1], self.upflow[lvl], 2, FLOW_SCALE[lvl]
+        outp = ctypes.c_void_p(cat.data_ptr() + 2 * CORR_OFF)
+        lib = self.lib
+        args = (f1p, f1_pitch, _lib.ptr(self.f2[lvl]), PYR_CP[lvl], _lib.ptr(flow), fp, scale, self.align_corners,
+                0.9999, 0.1, outp, cat.shape[-1], self.B, C, h, w, 4, _lib.NHWC, _lib.BF16)
+        self.op_info.append((f"warp_corr{lvl}", 2.0 * self.B * h * w * 81 * C))
+        self.ops.append(lambda st: _lib.check(lib.pwc_warp_corr_lrelu_fwd(*args, st), f"warp_corr{lvl}"))
+
+    def _build(self):
+        B, lib = self.B, self.lib
+        dev = self.device
+        # conv1a on CUDA cores, straight from the NCHW fp32 input
+        self.w1a = torch.zeros(16, 3, 3, 3, device=dev)
+        self.b1a = torch.zeros(16, device=dev)
+        a1 = (_lib.ptr(self.x_static), _lib.ptr(self.w1a), _lib.ptr(self.b1a), _lib.ptr(self.pa[1]), B, self.H, self.W, 0.1)
+        self.op_info.append(("conv1a.0", 2.0 * 2 * B * (self.H // 2) * (self.W // 2) * 16 * 27))
+        self.ops.append(lambda st: _lib.check(lib.pwc_conv1a_bf16_fwd(*a1, st), "conv1a"))
+        for l in range(1, 7):
+            names = (f"conv{l}a", f"conv{l}aa", f"conv{l}b") if l < 6 else ("conv6aa", "conv6a", "conv6b")
+            h, w = self.hw[l]
+            if l > 1:
+                hin, win = self.hw[l - 1]
+                cin = PYR_CH[l - 1]
+                if l == 2:
+                    self._tc(names[0] + ".0", cin, PYR_CH[l], self.pa[1], 0, PYR_CP[1], self.pa[l], 0, 2 * B, hin, win, stride=2)
+                else:
+                    self._tc(names[0] + ".0", cin, PYR_CH[l], self.cat[l - 1], C1_OFF, PYR_CP[l - 1], self.pa[l], 0, 2 * B,
+                             hin, win, stride=2, src2=self.f2[l - 1], n_split=B)
+            self._tc(names[1] + ".0", PYR_CH[l], PYR_CH[l], self.pa[l], 0, PYR_CP[l], self.pb[l], 0, 2 * B, h, w)
+            if l == 1:
+                self._tc(names[2] + ".0", 16, 16, self.pb[1], 0, 16, self.pa[1], 0, 2 * B, h, w)
+            elif l < 6:
+                self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.cat[l], C1_OFF, 2 * B, h, w,
+                         dst2=self.f2[l], n_split=B)
+            else:
+                self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.f1_6, 0, 2 * B, h, w,
+                         dst2=self.f2[l], n_split=B)
+        for l in (6, 5, 4, 3, 2):
+            h, w = self.hw[l]
+            cat, wd = self.cat[l], concat_width(l)
+            nin = 81 + (0 if l == 6 else PYR_CH[l] + 4)
+            self._corr(l)
+            for k in range(5):
+                cm = chan_map(l, DEC_START[k])
+                self._tc(f"conv{l}_{k}.0", len(cm), [128, 128, 96, 64, 32][k], cat, DEC_START[k], wd - DEC_START[k], cat,
+                         DEC_WRITE[k], B, h, w, cmap=cm)
+            cm = chan_map(l, 0)
+            self._tc(f"predict_flow{l}", len(cm), 2, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=True)
+            if l > 2:
+                self._deconv(f"deconv{l}", 2, self.flow[l], 0, 4, self.cat[l - 1], UPFLOW_OFF, h, w, dst_b=self.upflow[l - 1])
+                self._deconv(f"upfeat{l}", 448 + nin, cat, 0, wd, self.cat[l - 1], UPFEAT_OFF, h, w)
+        h, w = self.hw[2]
+        cm = chan_map(2, 0)
+        src, cin, span, cmap = self.cat[2], len(cm), concat_width(2), cm
+        for i, (name, cout, dil) in enumerate(DC):
+            self._tc(name + ".0", cin, cout, src, 0, span, self.dc[i], 0, B, h, w, dil=dil, cmap=cmap)
+            src, cin, span, cmap = self.dc[i], cout, cout, None
+        self._tc("dc_conv7", 32, 2, src, 0, 32, self.flow_out4, 0, B, h, w, slope=1.0, out_f32=True, residual=self.flow[2])
+        uo = (_lib.ptr(self.flow_out4), 4, 0, _lib.ptr(self.out), B, h, w, 1.0)
+        self.op_info.append(("unpack_flow", 0.0))
+        self.ops.append(lambda st: _lib.check(lib.pwc_unpack_flow_f32(*uo, st), "unpack_flow"))
+        self.launches = len(self.ops)
+
+    # ------------------------------------------------------------------ weights
+    def pack_weights(self, model):
+        ver = tuple(p._version for p in model.parameters()) + (id(model),)
+        if ver == self.weights_version:
+            return
+        if not self.ops:
+            self._build()
+        lib, dev = self.lib, self.device
+        st = _lib.stream_handle()
+        sd = {k: v.detach().to(device=dev, dtype=torch.float32).contiguous() for k, v in model.state_dict().items()}
+        keep = []
+        for key, L in self.layers.items():
+            wt = sd[key + ".weight"]
+            assert wt.shape[0] == L.cout and wt.shape[1] == L.cin, (key, tuple(wt.shape), L.cin, L.cout)
+            mp = None
+            if L.cmap is not None:
+                mp = torch.tensor(L.cmap, device=dev, dtype=torch.int32); keep.append(mp)
+            _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.cout, L.cin, L.span, L.kc,
+                                                     L.coutp, st), f"pack {key}")
+            L.b.copy_(sd[key + ".bias"])
+        for key, (w, b, cin, cinp) in self.small.items():
+            wt = sd[key + ".weight"]
+            mp = None
+            if key.startswith("upfeat"):
+                mp = torch.tensor(chan_map(int(key[-1]), 0), device=dev, dtype=torch.int32); keep.append(mp)
+            _lib.check(lib.pwc_pack_deconv_weight_f32(_lib.ptr(wt), _lib.ptr(w), _lib.ptr(mp), cin, cinp, st), f"pack {key}")
+            b.copy_(sd[key + ".bias"])
+        self.w1a.copy_(sd["conv1a.0.weight"]); self.b1a.copy_(sd["conv1a.0.bias"])
+        torch.cuda.current_stream().synchronize()
+        self.weights_version = ver
+
+    # ------------------------------------------------------------------ forward
+    def _launch_all(self):
+        st = _lib.stream_handle()
+        for op in self.ops:
+            op(st)
+
+    def run(self, x=None, all_levels=False):
+        """x: [B,6,H,W] fp32 (device, or pinned host: it is copied into the plan's static input).  Returns flow2
+        [B,2,H/4,W/4] fp32 (a plan-owned tensor)."""
+        if x is not None and x.data_ptr() != self.x_static.data_ptr():
+            self.x_static.copy_(x, non_blocking=True)
+        if not self.use_graph:
+            self._launch_all()
+            return self.out
+        if self.graph is None:
+            self._launch_all()                      # warm-up outside capture (cudaFuncSetAttribute etc.)
+            torch.cuda.current_stream().synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._launch_all()
+            self.graph = g
+        self.graph.replay()
+        return self.out
+
+    def level_flow(self, lvl):
+        return self.flow[lvl][..., :2].permute(0, 3, 1, 2).contiguous()

@@ -124,3 +124,39 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     finally:
         lib.pwc_tc_conv_destroy(h)
     return out
+
+
+def conv1a_bf16(x, weight, bias, slope=0.1):
+    """conv1a fused with the im1/im2 split (pwc_conv1a_bf16_fwd): x [B,6,H,W] fp32 -> bf16 NHWC [2B,H/2,W/2,16]."""
+    lib = _lib.load()
+    B, _, H, W = x.shape
+    out = torch.empty(2 * B, H // 2, W // 2, 16, device=x.device, dtype=torch.bfloat16)
+    w32, b32 = weight.detach().float().contiguous(), bias.detach().float().contiguous()
+    e = lib.pwc_conv1a_bf16_fwd(_lib.ptr(x.contiguous()), _lib.ptr(w32), _lib.ptr(b32), _lib.ptr(out), B, H, W, slope,
+                                _lib.stream_handle())
+    _lib.check(e, "pwc_conv1a_bf16_fwd")
+    torch.cuda.current_stream().synchronize()
+    return out
+
+
+def deconv4x4s2_c2(x, weight, bias, out_dtype=torch.float32, in_coff=0, cin_span=None, chan_map=None):
+    """2-channel ConvTranspose2d(4,2,1) with fp32/bf16 input and output (pwc_deconv4x4s2_c2_fwd)."""
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    N, H, W, pitch = x.shape
+    cin = weight.shape[0]
+    span = cin_span if cin_span is not None else (cin + 3) // 4 * 4
+    cinp = (span + 3) // 4 * 4
+    wp = torch.empty(32 * cinp, device=x.device, dtype=torch.float32)
+    mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
+    w32 = weight.detach().float().contiguous()
+    _lib.check(lib.pwc_pack_deconv_weight_f32(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), cin, cinp, st), "pack")
+    out = torch.zeros(N, 2 * H, 2 * W, 2, device=x.device, dtype=out_dtype)
+    outb = torch.zeros(N, 2 * H, 2 * W, 2, device=x.device, dtype=torch.float32)
+    b32 = bias.detach().float().contiguous()
+    dt = lambda t: _lib.BF16 if t == torch.bfloat16 else _lib.F32  # noqa: E731
+    e = lib.pwc_deconv4x4s2_c2_fwd(_lib.ptr(x), dt(x.dtype), pitch, in_coff, span, _lib.ptr(wp), _lib.ptr(b32),
+                                   _lib.ptr(out), dt(out_dtype), 2, 0, _lib.ptr(outb), 2, N, H, W, st)
+    _lib.check(e, "pwc_deconv4x4s2_c2_fwd")
+    torch.cuda.current_stream().synchronize()
+    return out, outb

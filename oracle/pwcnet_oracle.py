@@ -235,10 +235,20 @@ def warp_corr_lrelu_numpy(f1, f2, flow, scale, align_corners=False, slope=0.1, m
 # ----------------------------------------------------------------------------------------------
 # full forward
 # ----------------------------------------------------------------------------------------------
+_BF16_SIM = [False]   # forward(..., bf16_storage=True): model the bf16-conv mode's storage roundings (test aid)
+
+
+def _q(t):
+    return t.bfloat16().float() if _BF16_SIM[0] else t
+
+
 def _conv(sd, name, x, stride=1, pad=1, dil=1, act=True):
     key = f"{name}.0" if act else name
-    y = F.conv2d(x, sd[f"{key}.weight"], sd[f"{key}.bias"], stride=stride, padding=pad, dilation=dil)
-    return F.leaky_relu(y, 0.1) if act else y
+    w = sd[f"{key}.weight"]
+    if name != "conv1a":          # conv1a runs on CUDA cores with fp32 weights in the bf16 mode too
+        w = _q(w)
+    y = F.conv2d(x, w, sd[f"{key}.bias"], stride=stride, padding=pad, dilation=dil)
+    return _q(F.leaky_relu(y, 0.1)) if act else y      # predict_flow / dc_conv7 outputs stay fp32
 
 
 def _deconv(sd, name, x):
@@ -246,9 +256,19 @@ def _deconv(sd, name, x):
 
 
 @torch.no_grad()
-def forward(sd, x, align_corners=False, return_intermediates=False):
+def forward(sd, x, align_corners=False, return_intermediates=False, bf16_storage=False):
     """PWCDCNet.forward in eval mode (PWCNet.py:180-273).  x: [B,6,H,W] fp32, H,W multiples of 64.
-    Returns flow2 [B,2,H/4,W/4] (units of px/20, PWCNet.py:272-273); optionally a dict of per-level tensors."""
+    Returns flow2 [B,2,H/4,W/4] (units of px/20, PWCNet.py:272-273); optionally a dict of per-level tensors.
+    bf16_storage=True rounds weights and stored activations to bf16 where the bf16-conv mode of the CUDA path does
+    (fp32 arithmetic everywhere): a test aid that separates precision effects from bugs; not reference behaviour."""
+    _BF16_SIM[0] = bool(bf16_storage)
+    try:
+        return _forward(sd, x, align_corners, return_intermediates)
+    finally:
+        _BF16_SIM[0] = False
+
+
+def _forward(sd, x, align_corners, return_intermediates):
     inter = {}
     im1, im2 = x[:, :3], x[:, 3:]
 
@@ -271,12 +291,12 @@ def forward(sd, x, align_corners=False, return_intermediates=False):
     for lvl in (6, 5, 4, 3, 2):
         f1, f2 = c1[lvl - 1], c2[lvl - 1]
         if lvl == 6:
-            corr = F.leaky_relu(correlation_mean(f1, f2), 0.1)
+            corr = _q(F.leaky_relu(correlation_mean(f1, f2), 0.1))
             xfeat = corr
         else:
             w2 = warp(f2, up_flow * FLOW_SCALE[lvl], align_corners)
-            corr = F.leaky_relu(correlation_mean(f1, w2), 0.1)
-            xfeat = torch.cat((corr, f1, up_flow, up_feat), 1)
+            corr = _q(F.leaky_relu(correlation_mean(f1, w2), 0.1))
+            xfeat = torch.cat((corr, f1, _q(up_flow), _q(up_feat)), 1)
             inter[f"warp{lvl}"] = w2
         inter[f"corr{lvl}"] = corr
         for i in range(5):

@@ -1,0 +1,117 @@
+"""GPU parity of the bf16-conv mode: tcgen05 convolutions, bf16 companions, and the whole forward against the CPU
+oracle.  Bars (BASELINE.json north_star): mean EPE delta <= 0.02 px for the bf16 conv mode; single kernels are
+compared with torch fp32 run on the bf16-rounded operands (tolerance = bf16 output rounding, 2^-8 relative)."""
+import warnings
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import pwcnet_oracle as O
+
+warnings.filterwarnings("ignore")
+pytestmark = pytest.mark.gpu
+
+TC_CASES = [
+    # cin, cout, stride, dil, N, H, W, out_f32
+    (64, 128, 1, 1, 2, 24, 48, 0), (128, 128, 1, 1, 2, 21, 37, 0), (32, 32, 1, 1, 2, 16, 32, 0),
+    (16, 16, 1, 1, 2, 16, 32, 0), (96, 64, 1, 16, 1, 40, 64, 0), (128, 96, 1, 8, 1, 24, 40, 0),
+    (576, 128, 1, 1, 1, 16, 32, 0), (208, 208, 1, 1, 2, 7, 16, 0), (576, 2, 1, 1, 1, 16, 32, 1),
+    (32, 2, 1, 1, 2, 16, 32, 1), (480, 64, 1, 1, 1, 16, 16, 0), (64, 96, 2, 1, 2, 32, 64, 0), (16, 32, 2, 1, 1, 32, 32, 0),
+]
+
+
+@pytest.mark.parametrize("case", TC_CASES)
+def test_conv3x3_tc_matches_torch(case):
+    from opticalflow_b200 import ops
+    cin, cout, stride, dil, N, H, W, of32 = case
+    g = torch.Generator().manual_seed(100 + cin + cout)
+    x = torch.randn(N, cin, H, W, generator=g).bfloat16()
+    w = (torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin ** 0.5)).bfloat16().float()
+    b = torch.randn(cout, generator=g) * 0.1
+    slope = 1.0 if of32 else 0.1
+    ref = F.leaky_relu(F.conv2d(x.float(), w, b, stride=stride, padding=dil, dilation=dil), slope)
+    d = torch.device("cuda:0")
+    out = ops.conv3x3_tc(x.permute(0, 2, 3, 1).contiguous().to(d), w.to(d), b.to(d), stride, dil, slope, out_f32=bool(of32))
+    out = out.float().permute(0, 3, 1, 2).cpu()[:, :cout]
+    tol = (2e-3 if of32 else 1e-2) * ref.abs().max().item()
+    assert (out - ref).abs().max().item() <= tol
+
+
+def test_conv1a_bf16_matches_torch():
+    from opticalflow_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    x = torch.rand(2, 6, 64, 96, generator=g)
+    w = torch.randn(16, 3, 3, 3, generator=g) / 5.0
+    b = torch.randn(16, generator=g) * 0.1
+    d = torch.device("cuda:0")
+    out = ops.conv1a_bf16(x.to(d), w.to(d), b.to(d)).float().permute(0, 3, 1, 2).cpu()
+    ref = torch.cat([F.leaky_relu(F.conv2d(x[:, :3], w, b, stride=2, padding=1), 0.1),
+                     F.leaky_relu(F.conv2d(x[:, 3:], w, b, stride=2, padding=1), 0.1)], 0)
+    assert out.shape == ref.shape
+    assert (out - ref).abs().max().item() <= 8e-3 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("idt,odt", [(torch.bfloat16, torch.bfloat16), (torch.float32, torch.bfloat16), (torch.bfloat16, torch.float32)])
+def test_deconv_dtypes(idt, odt):
+    from opticalflow_b200 import ops
+    g = torch.Generator().manual_seed(13)
+    cin, H, W = 100, 9, 14
+    x = torch.randn(2, H, W, cin, generator=g).to(idt)
+    w = torch.randn(cin, 2, 4, 4, generator=g) / (4 * cin ** 0.5)
+    b = torch.randn(2, generator=g) * 0.1
+    ref = F.conv_transpose2d(x.float().permute(0, 3, 1, 2), w, b, stride=2, padding=1)
+    d = torch.device("cuda:0")
+    out, outb = ops.deconv4x4s2_c2(x.to(d), w.to(d), b.to(d), out_dtype=odt)
+    sc = max(ref.abs().max().item(), 1.0)
+    assert (outb.permute(0, 3, 1, 2).cpu() - ref).abs().max().item() <= 2e-5 * sc       # fp32 copy is exact-ish
+    assert (out.float().permute(0, 3, 1, 2).cpu() - ref).abs().max().item() <= (8e-3 if odt == torch.bfloat16 else 2e-5) * sc
+
+
+def _model(wseed, rbias, **kw):
+    from opticalflow_b200.models.PWCNet import PWCDCNet
+    torch.manual_seed(wseed)
+    m = PWCDCNet(**kw).eval()
+    if rbias:
+        m.load_state_dict(O.randomize_biases(m.state_dict()))
+    return m.cuda()
+
+
+def _epe(a, b):
+    return (a - b).pow(2).sum(1).sqrt()
+
+
+@pytest.mark.parametrize("shape,shift", [((1, 128, 192), 1), ((1, 448, 1024), 0), ((1, 448, 1024), 1)])
+def test_forward_bf16_epe_delta(shape, shift):
+    """north_star bar: mean EPE delta <= 0.02 px against the fp32 reference forward, reference random init
+    (kaiming weights, zero biases: PWCNet.py:134-138) on the synthetic inputs of SURVEY 8(d)."""
+    B, H, W = shape
+    m = _model(0, False, conv_mode="bf16")
+    sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
+    x = O.shifted_pair_input(B, H, W, 3) if shift else O.synthetic_input(B, H, W, 1)
+    ref = 20.0 * O.forward(sd, x)
+    sim = 20.0 * O.forward(sd, x, bf16_storage=True)
+    flow = 20.0 * m(x.cuda()).cpu()
+    e_ref, e_sim, e_simref = _epe(flow, ref), _epe(flow, sim), _epe(sim, ref)
+    print(f"bf16 mode {W}x{H} shift={shift}: mean EPE delta vs fp32 reference {e_ref.mean().item():.4f} px "
+          f"(max {e_ref.max().item():.3f}); vs bf16-storage oracle {e_sim.mean().item():.4f}; "
+          f"bf16-storage oracle vs fp32 {e_simref.mean().item():.4f}; flow absmax {ref.abs().max().item():.2f} px")
+    assert e_ref.mean().item() <= 0.02
+    assert e_sim.mean().item() <= 0.02
+    again = 20.0 * m(x.cuda()).cpu()                 # CUDA-graph replay: bit-identical
+    assert torch.equal(again, flow)
+
+
+def test_forward_bf16_random_bias_tracks_bf16_oracle():
+    """Non-zero biases (a bias bug would hide behind the reference's zero init): the flow is ~40 px and chaotic, so
+    the bar is relative: the CUDA path must be as close to the fp32 reference as the bf16-storage oracle is (x2)."""
+    B, H, W = 1, 128, 192
+    m = _model(0, True, conv_mode="bf16")
+    sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
+    x = O.shifted_pair_input(B, H, W, 3)
+    ref = 20.0 * O.forward(sd, x)
+    sim = 20.0 * O.forward(sd, x, bf16_storage=True)
+    flow = 20.0 * m(x.cuda()).cpu()
+    e_ref, e_simref = _epe(flow, ref).mean().item(), _epe(sim, ref).mean().item()
+    print(f"random-bias: ours vs fp32 {e_ref:.4f} px, bf16-storage oracle vs fp32 {e_simref:.4f} px, absmax {ref.abs().max().item():.1f}")
+    assert e_ref <= 2.0 * e_simref + 1e-3

@@ -1,0 +1,40 @@
+"""Per-launch CUDA-event times of the bf16 plan: python tools/layer_times.py [B] [H] [W] [reps]"""
+import os, sys, json
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from opticalflow_b200 import _lib
+from opticalflow_b200.models.PWCNet import PWCDCNet
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+H = int(sys.argv[2]) if len(sys.argv) > 2 else 448
+W = int(sys.argv[3]) if len(sys.argv) > 3 else 1024
+reps = int(sys.argv[4]) if len(sys.argv) > 4 else 5
+torch.manual_seed(0)
+m = PWCDCNet(conv_mode="bf16").eval().cuda()
+dev = torch.device("cuda")
+plan = m._plan(B, H, W, dev)
+plan.pack_weights(m)
+plan.x_static.copy_(torch.rand(B, 6, H, W, device=dev))
+plan._launch_all(); torch.cuda.synchronize()
+st = _lib.stream_handle()
+tot = [0.0] * len(plan.ops)
+for r in range(reps):
+    for i, op in enumerate(plan.ops):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); op(st); e1.record(); e1.synchronize()
+        tot[i] += e0.elapsed_time(e1) * 1e-3 / reps
+rows = []
+for (name, fl), t in zip(plan.op_info, tot):
+    rows.append((name, t, fl))
+T = sum(tot)
+print(f"B={B} {W}x{H}: sum of launches {T*1e3:.3f} ms -> {B/T:.1f} pairs/s (serialised, with event gaps)")
+for name, t, fl in rows:
+    print(f"{name:18s} {t*1e6:9.1f} us  {100*t/T:5.1f}%  {fl/t/1e12 if t > 0 else 0:8.1f} TFLOP/s")
+# whole-graph time
+for _ in range(3): plan.run()
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(10): plan.run()
+e1.record(); e1.synchronize()
+tg = e0.elapsed_time(e1) * 1e-4
+print(f"graph replay: {tg*1e3:.3f} ms/step -> {B/tg:.1f} pairs/s")
