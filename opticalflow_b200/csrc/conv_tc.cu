@@ -15,8 +15,10 @@
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 #include "tmap.cuh"
+#include "conv_tc_halo.cuh"
 #include "../../include/pwc_b200.h"
 
+#include <cstdlib>
 #include <new>
 
 namespace pwc {
@@ -67,8 +69,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (whole warp converged; one elected lane issues) =====================
+    {
       int s = 0; uint32_t ph = 0;
       for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
         const int n = t / (p.tiles_x * p.tiles_y);
@@ -81,18 +83,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
           const int y = ty0 * p.stride + (ky - 1) * p.dil, x = tx0 * p.stride + (kx - 1) * p.dil;
           for (int ch = 0; ch < p.nchunk; ++ch) {
             ptx::mbar_wait(empty_bar(s), ph ^ 1);
-            const uint32_t sa = base + s * p.stage_bytes;
-            ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (uint32_t)p.coutp * p.kc * 2);
-            ptx::tma_load_4d(sa, tmA, full_bar(s), ch * p.kc, x, y, nn);
-            ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * p.nchunk + ch) * p.coutp);
+            if (ptx::elect_one()) {
+              const uint32_t sa = base + s * p.stage_bytes;
+              ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (uint32_t)p.coutp * p.kc * 2);
+              ptx::tma_load_4d(sa, tmA, full_bar(s), ch * p.kc, x, y, nn);
+              ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * p.nchunk + ch) * p.coutp);
+            }
+            __syncwarp();
             if (++s == p.stages) { s = 0; ph ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer: whole warp converged, ONE elected lane issues (see conv_tc_halo.cuh) =====
+    {
       const uint32_t idesc = ptx::make_idesc_bf16(kTcM, p.coutp);
       const uint32_t row_bytes = p.kc * 2;
       const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
@@ -105,15 +110,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         for (int k = 0; k < ksteps; ++k) {
           ptx::mbar_wait(full_bar(s), ph);
           ptx::tc_fence_after();
-          const uint32_t sa = base + s * p.stage_bytes;
-          const uint64_t da = ptx::make_kmajor_desc(sa, 8 * row_bytes, ltype);
-          const uint64_t db = ptx::make_kmajor_desc(sa + p.a_bytes, 8 * row_bytes, ltype);
-          for (int kk = 0; kk < p.kc / 16; ++kk)
-            ptx::umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (k | kk) ? 1u : 0u);
-          ptx::umma_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
+          if (ptx::elect_one()) {
+            const uint32_t sa = base + s * p.stage_bytes;
+            const uint64_t da = ptx::make_kmajor_desc(sa, 8 * row_bytes, ltype);
+            const uint64_t db = ptx::make_kmajor_desc(sa + p.a_bytes, 8 * row_bytes, ltype);
+            for (int kk = 0; kk < p.kc / 16; ++kk)
+              ptx::umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (k | kk) ? 1u : 0u);
+            ptx::umma_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
+            if (k == ksteps - 1) ptx::umma_commit(tfull_bar(acc));   // accumulator complete -> epilogue
+          }
+          __syncwarp();
           if (++s == p.stages) { s = 0; ph ^= 1; }
         }
-        ptx::umma_commit(tfull_bar(acc));          // accumulator complete -> epilogue
         if (++acc == 2) { acc = 0; aph ^= 1; }
       }
     }
@@ -191,6 +199,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
 struct pwc_tc_conv {
   CUtensorMap tmA0, tmA1, tmB;
   pwc::TcConvParams p;
+  pwc::HaloParams hp;
+  int halo;                 // 1: conv_tc_halo_kernel, 0: conv_tc_kernel (per-tap boxes)
   size_t smem_bytes;
   int grid;
 };
@@ -212,6 +222,82 @@ __global__ void pack_conv_weight_bf16_kernel(const float* __restrict__ wt, __nv_
 
 static int g_num_sms = 0;
 
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
+// Halo kernel: stride 1, dilation <= 8 (TMA elementStrides limit), one input tensor.  PWC_TC_HALO=0 forces the
+// per-tap kernel (debugging / A-B comparisons); PWC_TC_HALO_MINKC (default 16) is the smallest channel chunk it takes.
+static bool halo_eligible(int stride, int dil, bool has_in2, int kc) {
+  if (!env_int("PWC_TC_HALO", 1)) return false;
+  return stride == 1 && dil >= 1 && dil <= 8 && !has_in2 && (kc == 16 || kc == 32 || kc == 64) &&
+         kc >= env_int("PWC_TC_HALO_MINKC", 16);
+}
+
+static int create_halo(pwc_tc_conv** handle, const void* in, long in_pitch, int in_coff, int cin_span, int kc,
+                       const void* w_packed, const float* bias, int cout, int coutp,
+                       void* out, long out_pitch, int out_coff, void* out2, long out2_pitch, int out2_coff, int n_split,
+                       int out_f32, const float* residual, long res_pitch, int N, int H, int W, int dil, float slope) {
+  if (coutp % 16 || coutp < 16 || coutp > 256 || cout > coutp || (in_pitch & 7) || (in_coff & 7) ||
+      (!out_f32 && ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7))))))
+    return (int)cudaErrorInvalidValue;
+  pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
+  if (!h) return (int)cudaErrorMemoryAllocation;
+  h->halo = 1;
+  HaloParams& p = h->hp;
+  p.N = N; p.H = H; p.W = W; p.dil = dil;
+  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc);
+  const int Hd = cdiv(H, dil), Wd = cdiv(W, dil);
+  auto ntiles = [&](int halves) { return (long)N * dil * dil * cdiv(Hd, kHaloTH) * cdiv(Wd, 8 * halves); };
+  int halves = env_int("PWC_TC_HALO_HALVES", 0);
+  if (halves != 1 && halves != 2) halves = (ntiles(2) >= (long)g_num_sms * 3 / 2 && 2 * coutp <= 256) ? 2 : 1;
+  if (2 * halves * coutp > 512) halves = 1;
+  p.halves = halves;
+  const long tiles = ntiles(halves);
+  int nsplit = 1;
+  if (tiles < g_num_sms) {                      // small pyramid levels: also split the output channels over CTAs
+    for (int cand = 2; cand <= 8; cand *= 2)
+      if (coutp % (16 * cand) == 0 && coutp / cand >= 32 && tiles * nsplit < g_num_sms) nsplit = cand;
+  }
+  const int forced = env_int("PWC_TC_HALO_NSPLIT", 0);
+  if (forced > 0 && coutp % (16 * forced) == 0) nsplit = forced;
+  p.nsplit = nsplit; p.nsl = coutp / nsplit;
+  p.tiles_x = cdiv(Wd, 8 * halves); p.tiles_y = cdiv(Hd, kHaloTH);
+  p.tiles_per_img = dil * dil * p.tiles_x * p.tiles_y;
+  p.num_items = (int)(tiles * nsplit);
+  p.pitch_px = 8 * halves + 2;
+  const uint32_t row_bytes = (uint32_t)kc * 2;
+  p.a_bytes_tx = (uint32_t)(kHaloTH + 2) * p.pitch_px * row_bytes;
+  p.a_bytes = (p.a_bytes_tx + 1023u) & ~1023u;
+  p.b_bytes_tx = (uint32_t)p.nsl * row_bytes;
+  p.b_bytes = (p.b_bytes_tx + 1023u) & ~1023u;
+  const uint32_t budget = 216u * 1024u - 2u * p.a_bytes;
+  const uint32_t all_b = 9u * p.nchunk * p.b_bytes;
+  p.b_resident = (nsplit == 1 && all_b <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
+  uint32_t stages = budget / p.b_bytes;
+  p.b_stages = stages > 12 ? 12 : (stages < 2 ? 2 : stages);
+  uint32_t cols = 32; while (cols < 2u * halves * p.nsl) cols <<= 1;
+  p.tmem_cols = cols;
+  p.fp16 = 0; p.bo_mode = env_int("PWC_TC_HALO_BO", 0);
+  p.bias = bias; p.slope = slope;
+  p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
+  p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = out2 ? n_split : N;
+  p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
+  const uint32_t nb = p.b_resident ? 9u * p.nchunk : p.b_stages;
+  h->smem_bytes = 2u * p.a_bytes + (size_t)nb * p.b_bytes + 8 * (10 + 2 * p.b_stages) + 16 + 1024;
+  const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
+  const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
+  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, W, H, N,
+                         kc, p.pitch_px * dil, (kHaloTH + 2) * dil, dil, dil, swz);
+  if (!e) e = make_tmap_2d(&h->tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w_packed, (long)9 * p.nchunk * coutp, kc, kc, p.nsl, swz);
+  if (e || h->smem_bytes > 227u * 1024u) { delete h; return e ? e : (int)cudaErrorInvalidValue; }
+  h->tmA1 = h->tmA0;
+  h->grid = p.num_items < g_num_sms ? p.num_items : g_num_sms;
+  *handle = h;
+  return 0;
+}
+
 }  // namespace pwc
 
 extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
@@ -225,6 +311,17 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   using namespace pwc;
   if (!handle) return (int)cudaErrorInvalidValue;
   *handle = nullptr;
+  if (!g_num_sms) {
+    int dev = 0; cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+    cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  }
+  if (halo_eligible(stride, dil, in2 != nullptr, kc)) {
+    return create_halo(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
+                       out2, out2_pitch, out2_coff, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope);
+  }
   if ((kc != 16 && kc != 32 && kc != 64) || cin_span % kc || coutp % 16 || coutp < 16 || coutp > 256 || cout > coutp ||
       (in_pitch & 7) || (in_coff & 7) || (in2 && ((in2_pitch & 7) || (in2_coff & 7))) ||
       (!out_f32 && ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7))))) ||
@@ -232,6 +329,7 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
     return (int)cudaErrorInvalidValue;
   pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
   if (!h) return (int)cudaErrorMemoryAllocation;
+  h->halo = 0;
   TcConvParams& p = h->p;
   p.N = N; p.Hin = Hin; p.Win = Win; p.stride = stride; p.dil = dil;
   p.Hout = (Hin - 1) / stride + 1; p.Wout = (Win - 1) / stride + 1;
@@ -265,12 +363,6 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   }
   if (!e) e = make_tmap_2d(&h->tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w_packed, (long)9 * p.nchunk * coutp, kc, kc, coutp, swz);
   if (e) { delete h; return e; }
-  if (!g_num_sms) {
-    int dev = 0; cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
-    cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  }
   h->grid = p.num_tiles < g_num_sms ? p.num_tiles : g_num_sms;
   *handle = h;
   return 0;
@@ -278,6 +370,10 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
 
 extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
   if (!h) return (int)cudaErrorInvalidValue;
+  if (h->halo) {
+    pwc::conv_tc_halo_kernel<<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->hp);
+    return (int)cudaGetLastError();
+  }
   pwc::conv_tc_kernel<<<h->grid, pwc::kTcThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmA1, h->tmB, h->p);
   return (int)cudaGetLastError();
 }
@@ -287,11 +383,16 @@ extern "C" void pwc_tc_conv_destroy(pwc_tc_conv* h) { delete h; }
 extern "C" int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, const int* chan_map,
                                          int Cout, int Cin, int cin_span, int kc, int coutp, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
-  if (cin_span % kc) return (int)cudaErrorInvalidValue;
-  const int nchunk = cin_span / kc;
+  const int nchunk = (cin_span + kc - 1) / kc;     // a partial last chunk is zero padded (halo kernel: TMA zero-fills A)
   cudaError_t e = cudaMemsetAsync(w_packed, 0, 2 * (size_t)9 * nchunk * coutp * kc, s);
   if (e != cudaSuccess) return (int)e;
   pwc::pack_conv_weight_bf16_kernel<<<256, 256, 0, s>>>(w_torch, reinterpret_cast<__nv_bfloat16*>(w_packed), chan_map,
                                                         Cout, Cin, nchunk, kc, coutp);
   return (int)cudaGetLastError();
+}
+
+// Debug: copy the halo kernel's timeline buffer (see conv_tc_halo.cuh) to host memory; returns a cudaError.
+extern "C" int pwc_debug_halo_trace(unsigned long long* host_dst, int count) {
+  if (count > 8192) count = 8192;
+  return (int)cudaMemcpyFromSymbol(host_dst, pwc::g_halo_trace, sizeof(unsigned long long) * count);
 }

@@ -14,6 +14,7 @@ import ctypes
 import torch
 
 from . import _lib
+from .ops import pick_kc
 from .engine import (C1_OFF, CORR_OFF, DC, DEC_START, DEC_WRITE, FLOW_SCALE, PYR_CH, UPFEAT_OFF, UPFLOW_OFF, chan_map,
                      concat_width)
 
@@ -22,10 +23,6 @@ BF = torch.bfloat16
 
 def _roundup(a, b):
     return (a + b - 1) // b * b
-
-
-def _kc(span):
-    return 64 if span % 64 == 0 else (32 if span % 32 == 0 else 16)
 
 
 PYR_CP = [4] + [_roundup(c, 16) for c in PYR_CH[1:]]      # 16, 32, 64, 96, 128, 208
@@ -82,10 +79,11 @@ class PlanBF16:
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None):
         L = _TcLayer()
-        L.key, L.cin, L.cout, L.span, L.kc, L.cmap = key, cin, cout, span, _kc(span), cmap
+        L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
+        L.kc = pick_kc(span, stride, dil, src2 is not None)
         L.coutp = _roundup(cout, 16)
         dev = self.device
-        L.w = torch.zeros(9 * span * L.coutp, device=dev, dtype=BF)
+        L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp, device=dev, dtype=BF)
         L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
         h = ctypes.c_void_p()
         e = self.lib.pwc_tc_conv_create(

@@ -86,8 +86,15 @@ def deconv4x4s2_c2_f32(x, weight, bias, in_coff=0, cin_span=None, chan_map=None)
     return out
 
 
-def pick_kc(cin_span):
-    return 64 if cin_span % 64 == 0 else (32 if cin_span % 32 == 0 else 16)
+def pick_kc(cin_span, stride=1, dil=1, has_in2=False):
+    """Channel chunk of the tensor-core conv.  The halo kernel (stride 1, dilation <= 8, one input) takes 64-channel
+    chunks with a zero-padded partial last chunk; the per-tap kernel needs cin_span % kc == 0."""
+    import os
+    exact = 64 if cin_span % 64 == 0 else (32 if cin_span % 32 == 0 else 16)
+    halo = int(os.environ.get("PWC_TC_HALO", "1")) and stride == 1 and 1 <= dil <= 8 and not has_in2
+    if halo and cin_span >= 64:
+        return 64
+    return exact
 
 
 def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=None, out=None, out_coff=0,
@@ -100,9 +107,9 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     assert x.dtype == torch.bfloat16
     cout, cin = weight.shape[:2]
     span = cin_span if cin_span is not None else (cin + 15) // 16 * 16
-    kc = pick_kc(span)
+    kc = pick_kc(span, stride, dil)
     coutp = (cout + 15) // 16 * 16
-    wp = torch.empty(9 * span * coutp, device=x.device, dtype=torch.bfloat16)
+    wp = torch.empty(9 * ((span + kc - 1) // kc) * kc * coutp, device=x.device, dtype=torch.bfloat16)
     mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
     w32 = weight.detach().float().contiguous()
     _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), cout, cin, span, kc, coutp, st), "pack")
@@ -118,8 +125,14 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
                                (residual.shape[-1] if residual is not None else 0), N, H, W, stride, dil, slope)
     _lib.check(e, "pwc_tc_conv_create")
     try:
-        for _ in range(reps):
-            _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
+        _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
+        if reps > 1:        # timing aid for tools/: CUDA-event time of reps-1 further launches
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps - 1):
+                _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
+            e1.record(); e1.synchronize()
+            conv3x3_tc.last_ms = e0.elapsed_time(e1) / (reps - 1)
         torch.cuda.current_stream().synchronize()
     finally:
         lib.pwc_tc_conv_destroy(h)
