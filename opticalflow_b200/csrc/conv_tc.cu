@@ -16,6 +16,7 @@
 #include "ptx_sm100.cuh"
 #include "tmap.cuh"
 #include "conv_tc_halo.cuh"
+#include "conv_tc_wm.cuh"
 #include "../../include/pwc_b200.h"
 
 #include <cstdlib>
@@ -197,10 +198,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
 // host side: descriptor object (tensor maps + parameters), launch, weight packing
 // ------------------------------------------------------------------------------------------------------------------
 struct pwc_tc_conv {
-  CUtensorMap tmA0, tmA1, tmB;
+  CUtensorMap tmA0, tmA1, tmB, tmO, tmO2;
   pwc::TcConvParams p;
   pwc::HaloParams hp;
-  int halo;                 // 1: conv_tc_halo_kernel, 0: conv_tc_kernel (per-tap boxes)
+  pwc::WmParams wp;
+  int halo;                 // 2: conv_tc_wm_kernel, 1: conv_tc_halo_kernel, 0: conv_tc_kernel (per-tap boxes)
   size_t smem_bytes;
   int grid;
 };
@@ -298,6 +300,77 @@ static int create_halo(pwc_tc_conv** handle, const void* in, long in_pitch, int 
   return 0;
 }
 
+static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in_coff, int cin_span, int kc,
+                     const void* w_packed, const float* bias, int cout, int coutp,
+                     void* out, long out_pitch, int out_coff, void* out2, long out2_pitch, int out2_coff, int n_split,
+                     int out_f32, const float* residual, long res_pitch, int N, int H, int W, int dil, float slope) {
+  if (coutp % 16 || coutp < 16 || coutp > 128 || cout > coutp || (in_pitch & 7) || (in_coff & 7))
+    return (int)cudaErrorInvalidValue;
+  pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
+  if (!h) return (int)cudaErrorMemoryAllocation;
+  h->halo = 2;
+  WmParams& p = h->wp;
+  p.N = N; p.H = H; p.W = W; p.dil = dil;
+  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc);
+  const int Hd = cdiv(H, dil), Wd = cdiv(W, dil);
+  const int max_rows = (256 / dil - 2) < 32 ? ((256 / dil - 2) & ~1) : 32;
+  auto even_up = [](int v) { return (v + 1) & ~1; };
+  auto ntiles = [&](int rows) { return (long)N * dil * dil * cdiv(Hd, rows) * cdiv(Wd, 8); };
+  int rows = even_up(cdiv(Hd, cdiv(Hd, max_rows)));           // fewest row tiles, least padding
+  if (rows > max_rows) rows = max_rows;
+  if (rows < 2) rows = 2;
+  while (ntiles(rows) < g_num_sms && rows > 8) rows = even_up(cdiv(rows, 2)) < 8 ? 8 : even_up(cdiv(rows, 2));
+  const int forced = env_int("PWC_TC_WM_ROWS", 0);
+  if (forced >= 2 && forced <= max_rows && !(forced & 1)) rows = forced;
+  p.rows = rows; p.npx = 8 * rows;
+  p.tiles_x = cdiv(Wd, 8); p.tiles_y = cdiv(Hd, rows);
+  p.tiles_per_img = dil * dil * p.tiles_x * p.tiles_y;
+  p.num_items = (int)ntiles(rows);
+  const uint32_t row_bytes = (uint32_t)kc * 2;
+  p.x_bytes_tx = (uint32_t)(rows + 2) * 10u * row_bytes;
+  p.x_bytes = (p.x_bytes_tx + 1023u) & ~1023u;
+  p.w_bytes_tx = (uint32_t)coutp * row_bytes;
+  p.w_bytes = (p.w_bytes_tx + 1023u) & ~1023u;
+  p.w_pad = 128u * row_bytes > p.w_bytes ? 128u * row_bytes - p.w_bytes : 0u;
+  p.tma_store = (!out_f32 && env_int("PWC_TC_WM_TMASTORE", 1)) ? 1 : 0;
+  p.o_bytes = p.tma_store ? (((uint32_t)(rows / 2) * 8u * coutp * 2u + 1023u) & ~1023u) : 0u;
+  const uint32_t budget = 216u * 1024u - 2u * p.x_bytes - p.w_pad - p.o_bytes;
+  const uint32_t all_w = 9u * p.nchunk * p.w_bytes;
+  p.w_resident = (all_w <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
+  uint32_t stages = budget / p.w_bytes;
+  p.w_stages = stages > 12 ? 12 : (stages < 2 ? 2 : stages);
+  uint32_t cols = 32; while (cols < 2u * p.npx) cols <<= 1;
+  p.tmem_cols = cols;
+  p.fp16 = 0; p.dbg = env_int("PWC_TC_HALO_BO", 0);
+  p.bias = bias; p.slope = slope;
+  p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
+  p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = out2 ? n_split : N;
+  p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
+  const uint32_t nw = p.w_resident ? 9u * p.nchunk : p.w_stages;
+  h->smem_bytes = 2u * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + 8 * (10 + 2 * p.w_stages) + 16 + 1024;
+  const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
+  const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
+  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, W, H, N,
+                         kc, 10 * dil, (rows + 2) * dil, dil, dil, swz);
+  if (!e) e = make_tmap_2d(&h->tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w_packed, (long)9 * p.nchunk * coutp, kc, kc, coutp, swz);
+  h->tmO = h->tmA0; h->tmO2 = h->tmA0;
+  if (!e && p.tma_store) {
+    // output slice as a 4-D tensor (CoutP, W, H, images); box = half an item; dilation = element strides; no swizzle
+    if ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7)))) e = (int)cudaErrorInvalidValue;
+    const int n1 = out2 ? p.n_split : N;
+    if (!e) e = make_tmap_nhwc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out) + out_coff,
+                               out_pitch, coutp, W, H, n1, coutp, 8 * dil, (rows / 2) * dil, dil, dil, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (!e && out2) e = make_tmap_nhwc(&h->tmO2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out2) + out2_coff,
+                                       out2_pitch, coutp, W, H, N - n1, coutp, 8 * dil, (rows / 2) * dil, dil, dil,
+                                       CU_TENSOR_MAP_SWIZZLE_NONE);
+  }
+  if (e || h->smem_bytes > 227u * 1024u || cols > 512) { delete h; return e ? e : (int)cudaErrorInvalidValue; }
+  h->tmA1 = h->tmA0;
+  h->grid = p.num_items < g_num_sms ? p.num_items : g_num_sms;
+  *handle = h;
+  return 0;
+}
+
 }  // namespace pwc
 
 extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
@@ -317,6 +390,12 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
     if (g_num_sms <= 0) g_num_sms = 148;
     cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_wm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  }
+  if (halo_eligible(stride, dil, in2 != nullptr, kc) && coutp <= 128 && env_int("PWC_TC_WM", 1) &&
+      !(out_f32 && (cin_span + kc - 1) / kc < 4)) {
+    return create_wm(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
+                     out2, out2_pitch, out2_coff, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope);
   }
   if (halo_eligible(stride, dil, in2 != nullptr, kc)) {
     return create_halo(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
@@ -370,6 +449,10 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
 
 extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
   if (!h) return (int)cudaErrorInvalidValue;
+  if (h->halo == 2) {
+    pwc::conv_tc_wm_kernel<<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp);
+    return (int)cudaGetLastError();
+  }
   if (h->halo) {
     pwc::conv_tc_halo_kernel<<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->hp);
     return (int)cudaGetLastError();

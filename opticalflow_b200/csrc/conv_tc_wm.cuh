@@ -1,0 +1,251 @@
+// Third-generation tcgen05 3x3 convolution: halo tile as in conv_tc_halo.cuh, but with the operand roles swapped --
+// the WEIGHTS are the M operand (M = 128 output channels, zero/garbage rows above CoutP are never read back) and the
+// PIXELS are the N operand (N = 8*rows <= 256 pixels of a rows x 8 tile).  Measured on B200: one tcgen05.mma costs
+// >= ~100-130 cycles to issue/execute whatever its shape, so the tensor pipe only fills when every instruction is as
+// large as the ISA allows (128 x 256 x 16); with pixels on M a Cout = 128 layer tops out near 40% of peak.
+//   D^T[cout, pixel] += W[tap][chunk][cout, 0:64] * X[pixel shifted by tap, 0:64]^T
+//   * X: one TMA box per 64-channel chunk = the (rows+2) x 10 pixel halo (dilation d: sub-lattice via elementStrides);
+//     tap (ky,kx) = N-side descriptor start shifted by (ky*10 + kx) 128-byte rows, SBO = 10 rows.
+//   * W: one TMA box [CoutP x 64] per (tap, chunk) through a ring (or resident when the whole layer fits).
+//   * accumulator: TMEM lanes = output channels, columns = pixels; double buffered (2 x N columns).
+//   * epilogue: thread = one output channel; tcgen05.ld brings 16 pixels of it; a warp stores 32 consecutive channels
+//     of one pixel per instruction (64 contiguous bytes in the NHWC concat slice).
+#pragma once
+#include "conv_tc_halo.cuh"
+
+namespace pwc {
+
+struct WmParams {
+  int N, H, W, dil;
+  int cout, coutp, kc, nchunk, rows, npx;       // npx = 8*rows = MMA N
+  int tiles_x, tiles_y, tiles_per_img, num_items;
+  uint32_t x_bytes_tx, x_bytes, w_bytes_tx, w_bytes, w_stages, w_resident, w_pad, o_bytes, tmem_cols;
+  int tma_store;                                  // 16-bit output through a shared-memory staging tile + TMA store
+  int fp16, dbg;
+  const float* bias; float slope;
+  void* out; long out_pitch; int out_coff;
+  void* out2; long out2_pitch; int out2_coff; int n_split;
+  int out_f32;
+  const float* residual; long res_pitch;
+};
+
+__device__ __forceinline__ void named_bar(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__global__ void __launch_bounds__(kHaloThreads, 1)
+conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+                  const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const WmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = (ptx::smem_addr(smem_raw) + 1023u) & ~1023u;
+  const uint32_t x_base = base;                                   // 2 halo buffers
+  const uint32_t w_base = base + 2u * p.x_bytes;                  // weight ring (or the resident weight set)
+  const uint32_t nw = p.w_resident ? (uint32_t)(9 * p.nchunk) : p.w_stages;
+  const uint32_t o_base = w_base + nw * p.w_bytes + p.w_pad;      // w_pad: the M=128 MMA reads 128 rows from a CoutP-row tile
+  const uint32_t bar_base = o_base + p.o_bytes;                   // o: output staging tile (half an item)
+  auto x_full = [&](int i) { return bar_base + 8u * i; };
+  auto x_empty = [&](int i) { return bar_base + 8u * (2 + i); };
+  auto t_full = [&](int i) { return bar_base + 8u * (4 + i); };
+  auto t_empty = [&](int i) { return bar_base + 8u * (6 + i); };
+  const uint32_t w_all = bar_base + 8u * 8;
+  auto w_full = [&](int s) { return bar_base + 8u * (9 + s); };
+  auto w_empty = [&](int s) { return bar_base + 8u * (9 + p.w_stages + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (9 + 2 * p.w_stages);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_addr(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int d = p.dil;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmX); ptx::prefetch_tmap(&tmW);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(x_full(i), 1); ptx::mbar_init(x_empty(i), 1);
+      ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 4);
+    }
+    ptx::mbar_init(w_all, 1);
+    for (uint32_t s = 0; s < p.w_stages; ++s) { ptx::mbar_init(w_full(s), 1); ptx::mbar_init(w_empty(s), 1); }
+    ptx::fence_barrier_init();
+    ptx::fence_proxy_async();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, p.tmem_cols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  auto decode = [&](int item, int& n, int& ry, int& rx, int& ty0, int& tx0) {
+    n = item / p.tiles_per_img;
+    int r = item - n * p.tiles_per_img;
+    const int per_phase = p.tiles_x * p.tiles_y;
+    const int ph = r / per_phase;
+    r -= ph * per_phase;
+    ry = ph / d; rx = ph - ry * d;
+    ty0 = (r / p.tiles_x) * p.rows; tx0 = (r % p.tiles_x) * 8;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer (whole warp converged; one elected lane issues) =====================
+    if (p.w_resident && ptx::elect_one()) {
+      ptx::mbar_expect_tx(w_all, 9u * p.nchunk * p.w_bytes_tx);
+      for (int j = 0; j < 9 * p.nchunk; ++j) ptx::tma_load_2d(w_base + j * p.w_bytes, &tmW, w_all, 0, j * p.coutp);
+    }
+    __syncwarp();
+    int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      int n, ry, rx, ty0, tx0;
+      decode(item, n, ry, rx, ty0, tx0);
+      const int ya = ry + d * (ty0 - 1), xa = rx + d * (tx0 - 1);
+      for (int ch = 0; ch < p.nchunk; ++ch) {
+        ptx::mbar_wait(x_empty(xb), xph ^ 1);
+        if (ptx::elect_one()) {
+          ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
+          ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, xa, ya, n);
+        }
+        __syncwarp();
+        if (++xb == 2) { xb = 0; xph ^= 1; }
+        if (!p.w_resident) {
+          for (int tap = 0; tap < 9; ++tap) {
+            ptx::mbar_wait(w_empty(s), wph ^ 1);
+            if (ptx::elect_one()) {
+              ptx::mbar_expect_tx(w_full(s), p.w_bytes_tx);
+              ptx::tma_load_2d(w_base + s * p.w_bytes, &tmW, w_full(s), 0, (tap * p.nchunk + ch) * p.coutp);
+            }
+            __syncwarp();
+            if (++s == p.w_stages) { s = 0; wph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer: whole warp converged, one elected lane issues =====================
+    uint32_t idesc = ptx::make_idesc_bf16(128, p.npx);
+    if (p.fp16) idesc &= ~((7u << 7) | (7u << 10));          // A/B format 0 = F16
+    const uint32_t row_bytes = p.kc * 2;
+    const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
+    const uint32_t sbo_x = 10u * row_bytes;
+    int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
+    int acc = 0; uint32_t tph = 0;
+    if (p.w_resident) ptx::mbar_wait(w_all, 0);
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      ptx::mbar_wait(t_empty(acc), tph ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.npx);
+      for (int ch = 0; ch < p.nchunk; ++ch) {
+        ptx::mbar_wait(x_full(xb), xph);
+        ptx::tc_fence_after();
+        const uint32_t sx = x_base + xb * p.x_bytes;
+        for (int tap = 0; tap < 9; ++tap) {
+          const int ky = tap / 3, kx = tap - 3 * ky;
+          uint32_t sw;
+          if (p.w_resident) {
+            sw = w_base + (tap * p.nchunk + ch) * p.w_bytes;
+          } else {
+            ptx::mbar_wait(w_full(s), wph);
+            ptx::tc_fence_after();
+            sw = w_base + s * p.w_bytes;
+          }
+          if (ptx::elect_one()) {
+            const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
+            const uint64_t dx = ptx::make_kmajor_desc(sx + (uint32_t)(ky * 10 + kx) * row_bytes, sbo_x, ltype);
+            for (int kk = 0; kk < p.kc / 16; ++kk)
+              ptx::umma_bf16(d_tmem, dw + 2 * kk, dx + 2 * kk, idesc, (ch | tap | kk) ? 1u : 0u);
+            if (!p.w_resident) ptx::umma_commit(w_empty(s));
+            if (tap == 8) ptx::umma_commit(x_empty(xb));
+            if (tap == 8 && ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
+          }
+          __syncwarp();
+          if (!p.w_resident) { if (++s == p.w_stages) { s = 0; wph ^= 1; } }
+        }
+        if (++xb == 2) { xb = 0; xph ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; tph ^= 1; }
+    }
+  } else {
+    // ===================== epilogue warps 2..5: thread = output channel =====================
+    const int lg = warp & 3;
+    const int co = lg * 32 + lane;
+    const bool co_live = p.out_f32 ? (co < p.cout) : (co < p.coutp);
+    const bool warp_live = lg * 32 < (p.out_f32 ? p.cout : p.coutp);
+    const float bias = (co < p.cout) ? __ldg(p.bias + co) : 0.f;
+    uint8_t* o_gen = smem_raw + (o_base - ptx::smem_addr(smem_raw));
+    const bool issuer = (threadIdx.x == 64);
+    int acc = 0; uint32_t tph = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      int n, ry, rx, ty0, tx0;
+      decode(item, n, ry, rx, ty0, tx0);
+      const bool second = (n >= p.n_split) && (p.out2 != nullptr);
+      const int nn = second ? n - p.n_split : n;
+      ptx::mbar_wait(t_full(acc), tph);
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * p.npx);
+      if (p.tma_store) {
+        const int hpx = p.npx >> 1;                        // pixels per half item (rows/2 tile rows)
+        for (int half = 0; half < 2; ++half) {
+          if (warp_live) {
+            uint16_t* st = reinterpret_cast<uint16_t*>(o_gen) + co;
+            for (int c0 = 0; c0 < hpx; c0 += 16) {
+              uint32_t v[16];
+              ptx::tmem_ld16(taddr + half * hpx + c0, v);
+              ptx::tmem_ld_wait();
+              if (co_live) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  const float val = lrelu(__uint_as_float(v[i]) + bias, p.slope);
+                  uint16_t bits;
+                  if (p.fp16) { __half hv = __float2half_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
+                  else { __nv_bfloat16 hv = __float2bfloat16_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
+                  if (c0 + i < hpx) st[(c0 + i) * p.coutp] = bits;
+                }
+              }
+            }
+          }
+          ptx::fence_proxy_async();                        // generic-proxy smem writes -> visible to the TMA store
+          named_bar(2, 128);
+          if (issuer) {
+            ptx::tma_store_4d(second ? &tmO2 : &tmO, o_base, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
+            ptx::bulk_commit();
+            ptx::bulk_wait_read0();                        // staging tile may be overwritten
+          }
+          named_bar(2, 128);
+        }
+      } else if (warp_live) {
+        for (int c0 = 0; c0 < p.npx; c0 += 16) {           // 16 pixels = 2 tile rows of 8
+          uint32_t v[16];
+          ptx::tmem_ld16(taddr + c0, v);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int py = (c0 + i) >> 3, px = (c0 + i) & 7;
+            const int oy = ry + d * (ty0 + py), ox = rx + d * (tx0 + px);
+            if (co_live && oy < p.H && ox < p.W) {
+              const long pix = ((long)nn * p.H + oy) * p.W + ox;
+              float val = lrelu(__uint_as_float(v[i]) + bias, p.slope);
+              if (p.out_f32) {
+                if (p.residual) val += p.residual[pix * p.res_pitch + co];
+                reinterpret_cast<float*>(p.out)[pix * p.out_pitch + p.out_coff + co] = val;
+              } else {
+                uint16_t* o = second ? reinterpret_cast<uint16_t*>(p.out2) + pix * p.out2_pitch + p.out2_coff
+                                     : reinterpret_cast<uint16_t*>(p.out) + pix * p.out_pitch + p.out_coff;
+                uint16_t bits;
+                if (p.fp16) { __half hv = __float2half_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
+                else { __nv_bfloat16 hv = __float2bfloat16_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
+                o[co] = bits;
+              }
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(t_empty(acc));
+      if (++acc == 2) { acc = 0; tph ^= 1; }
+    }
+    if (issuer) ptx::bulk_wait0();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+}  // namespace pwc

@@ -2,7 +2,7 @@
 python tools/bench_conv.py cin cout dil N H W"""
 import os, subprocess, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-VARIANTS = [{"PWC_TC_HALO": "0"}, {}, {"PWC_TC_HALO_HALVES": "1"}]
+VARIANTS = [{"PWC_TC_HALO": "0"}, {"PWC_TC_WM": "0"}, {}, {"PWC_TC_WM_ROWS": "16"}]
 if __name__ == "__main__":
     if os.environ.get("BENCH_CONV_CHILD"):
         import torch

@@ -11,8 +11,8 @@ CASES = [
     (32, 32, 1, 1, 2, 24, 40, 0), (16, 16, 1, 1, 2, 33, 48, 0),
 ]
 VARIANTS = [
-    {}, {"PWC_TC_HALO_HALVES": "2", "PWC_TC_HALO_RESIDENT": "0"}, {"PWC_TC_HALO_HALVES": "1", "PWC_TC_HALO_NSPLIT": "2"},
-    {"PWC_TC_HALO_HALVES": "1", "PWC_TC_HALO_RESIDENT": "0"},
+    {}, {"PWC_TC_WM_ROWS": "8", "PWC_TC_HALO_RESIDENT": "0"}, {"PWC_TC_WM_ROWS": "16"}, {"PWC_TC_WM_ROWS": "32"},
+    {"PWC_TC_WM": "0"}, {"PWC_TC_WM": "0", "PWC_TC_HALO_HALVES": "1", "PWC_TC_HALO_NSPLIT": "2"},
 ]
 
 
