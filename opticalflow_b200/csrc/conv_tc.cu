@@ -329,15 +329,26 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   const uint32_t row_bytes = (uint32_t)kc * 2;
   p.x_bytes_tx = (uint32_t)(rows + 2) * 10u * row_bytes;
   p.x_bytes = (p.x_bytes_tx + 1023u) & ~1023u;
+  p.cin_span = cin_span;
   p.w_bytes_tx = (uint32_t)coutp * row_bytes;
-  p.w_bytes = (p.w_bytes_tx + 1023u) & ~1023u;
-  p.w_pad = 128u * row_bytes > p.w_bytes ? 128u * row_bytes - p.w_bytes : 0u;
   p.tma_store = (!out_f32 && env_int("PWC_TC_WM_TMASTORE", 1)) ? 1 : 0;
   p.o_bytes = p.tma_store ? (((uint32_t)(rows / 2) * 8u * coutp * 2u + 1023u) & ~1023u) : 0u;
+  // weight-tile replication on M (epilogue parallelism for thin layers): only when the whole weight set stays resident
+  p.cg = cdiv(out_f32 ? cout : coutp, 32); p.rep = 1;
+  const uint32_t full_tile = 128u * row_bytes;
+  const uint32_t budget_rep = 216u * 1024u - 2u * p.x_bytes - p.o_bytes;
+  if (p.tma_store && 4 / p.cg >= 2 && 9u * p.nchunk * full_tile <= budget_rep && env_int("PWC_TC_WM_REP", 1) &&
+      env_int("PWC_TC_HALO_RESIDENT", 1)) p.rep = 4 / p.cg;
+  p.w_bytes = p.rep > 1 ? full_tile : ((p.w_bytes_tx + 1023u) & ~1023u);
+  p.w_pad = full_tile > p.w_bytes ? full_tile - p.w_bytes : 0u;
   const uint32_t budget = 216u * 1024u - 2u * p.x_bytes - p.w_pad - p.o_bytes;
   const uint32_t all_w = 9u * p.nchunk * p.w_bytes;
   p.w_resident = (all_w <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
-  uint32_t stages = budget / p.w_bytes;
+  if (!p.w_resident && p.rep > 1) { delete h; return (int)cudaErrorInvalidValue; }
+  // streamed weights: 3 taps per stage when the pixel tile is small (per-stage handshakes would dominate the MMAs)
+  p.tps = 1;
+  if (!p.w_resident && p.npx <= 128 && budget / (3u * p.w_bytes) >= 3 && env_int("PWC_TC_WM_TPS", 3) == 3) p.tps = 3;
+  uint32_t stages = budget / (p.w_bytes * p.tps);
   p.w_stages = stages > 12 ? 12 : (stages < 2 ? 2 : stages);
   uint32_t cols = 32; while (cols < 2u * p.npx) cols <<= 1;
   p.tmem_cols = cols;
@@ -346,7 +357,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
   p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = out2 ? n_split : N;
   p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
-  const uint32_t nw = p.w_resident ? 9u * p.nchunk : p.w_stages;
+  const uint32_t nw = p.w_resident ? 9u * p.nchunk : p.w_stages * p.tps;
   h->smem_bytes = 2u * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + 8 * (10 + 2 * p.w_stages) + 16 + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;

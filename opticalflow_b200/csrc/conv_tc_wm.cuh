@@ -18,6 +18,8 @@ namespace pwc {
 struct WmParams {
   int N, H, W, dil;
   int cout, coutp, kc, nchunk, rows, npx;       // npx = 8*rows = MMA N
+  int cin_span, tps, rep, cg;                   // tps: taps per weight stage (1|3|9); rep: weight-tile replicas on M
+                                                // (lane groups rep*cg <= 4 hold the same channels -> epilogue splits pixels)
   int tiles_x, tiles_y, tiles_per_img, num_items;
   uint32_t x_bytes_tx, x_bytes, w_bytes_tx, w_bytes, w_stages, w_resident, w_pad, o_bytes, tmem_cols;
   int tma_store;                                  // 16-bit output through a shared-memory staging tile + TMA store
@@ -40,7 +42,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   const uint32_t base = (ptx::smem_addr(smem_raw) + 1023u) & ~1023u;
   const uint32_t x_base = base;                                   // 2 halo buffers
   const uint32_t w_base = base + 2u * p.x_bytes;                  // weight ring (or the resident weight set)
-  const uint32_t nw = p.w_resident ? (uint32_t)(9 * p.nchunk) : p.w_stages;
+  const uint32_t nw = p.w_resident ? (uint32_t)(9 * p.nchunk) : p.w_stages * p.tps;
   const uint32_t o_base = w_base + nw * p.w_bytes + p.w_pad;      // w_pad: the M=128 MMA reads 128 rows from a CoutP-row tile
   const uint32_t bar_base = o_base + p.o_bytes;                   // o: output staging tile (half an item)
   auto x_full = [&](int i) { return bar_base + 8u * i; };
@@ -87,8 +89,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   if (warp == 0) {
     // ===================== TMA producer (whole warp converged; one elected lane issues) =====================
     if (p.w_resident && ptx::elect_one()) {
-      ptx::mbar_expect_tx(w_all, 9u * p.nchunk * p.w_bytes_tx);
-      for (int j = 0; j < 9 * p.nchunk; ++j) ptx::tma_load_2d(w_base + j * p.w_bytes, &tmW, w_all, 0, j * p.coutp);
+      ptx::mbar_expect_tx(w_all, 9u * p.nchunk * p.w_bytes_tx * p.rep);
+      for (int j = 0; j < 9 * p.nchunk; ++j)
+        for (int r = 0; r < p.rep; ++r)
+          ptx::tma_load_2d(w_base + j * p.w_bytes + r * p.cg * 32 * p.kc * 2, &tmW, w_all, 0, j * p.coutp);
     }
     __syncwarp();
     int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
@@ -105,11 +109,12 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         __syncwarp();
         if (++xb == 2) { xb = 0; xph ^= 1; }
         if (!p.w_resident) {
-          for (int tap = 0; tap < 9; ++tap) {
+          for (int tap = 0; tap < 9; tap += p.tps) {
             ptx::mbar_wait(w_empty(s), wph ^ 1);
             if (ptx::elect_one()) {
-              ptx::mbar_expect_tx(w_full(s), p.w_bytes_tx);
-              ptx::tma_load_2d(w_base + s * p.w_bytes, &tmW, w_full(s), 0, (tap * p.nchunk + ch) * p.coutp);
+              ptx::mbar_expect_tx(w_full(s), p.w_bytes_tx * p.tps);
+              for (int q = 0; q < p.tps; ++q)
+                ptx::tma_load_2d(w_base + (s * p.tps + q) * p.w_bytes, &tmW, w_full(s), 0, ((tap + q) * p.nchunk + ch) * p.coutp);
             }
             __syncwarp();
             if (++s == p.w_stages) { s = 0; wph ^= 1; }
@@ -135,27 +140,42 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         ptx::mbar_wait(x_full(xb), xph);
         ptx::tc_fence_after();
         const uint32_t sx = x_base + xb * p.x_bytes;
-        for (int tap = 0; tap < 9; ++tap) {
+        const int nkk = min(p.kc, p.cin_span - ch * p.kc + 15) >> 4;     // K=16 steps holding real channels
+        const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
+        auto issue_tap = [&](uint32_t sw, int tap) {
           const int ky = tap / 3, kx = tap - 3 * ky;
-          uint32_t sw;
-          if (p.w_resident) {
-            sw = w_base + (tap * p.nchunk + ch) * p.w_bytes;
-          } else {
-            ptx::mbar_wait(w_full(s), wph);
-            ptx::tc_fence_after();
-            sw = w_base + s * p.w_bytes;
-          }
+          const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
+          const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * 10 + kx) * row_bytes) >> 4);
+          ptx::umma_bf16(d_tmem, dw, dx, idesc, (ch | tap) ? 1u : 0u);
+          if (nkk > 1) ptx::umma_bf16(d_tmem, dw + 2, dx + 2, idesc, 1u);
+          if (nkk > 2) ptx::umma_bf16(d_tmem, dw + 4, dx + 4, idesc, 1u);
+          if (nkk > 3) ptx::umma_bf16(d_tmem, dw + 6, dx + 6, idesc, 1u);
+        };
+        if (p.w_resident) {
           if (ptx::elect_one()) {
-            const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
-            const uint64_t dx = ptx::make_kmajor_desc(sx + (uint32_t)(ky * 10 + kx) * row_bytes, sbo_x, ltype);
-            for (int kk = 0; kk < p.kc / 16; ++kk)
-              ptx::umma_bf16(d_tmem, dw + 2 * kk, dx + 2 * kk, idesc, (ch | tap | kk) ? 1u : 0u);
-            if (!p.w_resident) ptx::umma_commit(w_empty(s));
-            if (tap == 8) ptx::umma_commit(x_empty(xb));
-            if (tap == 8 && ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
+#pragma unroll 1
+            for (int tap = 0; tap < 9; ++tap) issue_tap(w_base + (tap * p.nchunk + ch) * p.w_bytes, tap);
+            ptx::umma_commit(x_empty(xb));
+            if (ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
           }
           __syncwarp();
-          if (!p.w_resident) { if (++s == p.w_stages) { s = 0; wph ^= 1; } }
+        } else {
+          for (int tap0 = 0; tap0 < 9; tap0 += p.tps) {
+            ptx::mbar_wait(w_full(s), wph);
+            ptx::tc_fence_after();
+            if (ptx::elect_one()) {
+              const uint32_t sw0 = w_base + s * p.tps * p.w_bytes;
+              issue_tap(sw0, tap0);
+              if (p.tps == 3) { issue_tap(sw0 + p.w_bytes, tap0 + 1); issue_tap(sw0 + 2 * p.w_bytes, tap0 + 2); }
+              ptx::umma_commit(w_empty(s));
+              if (tap0 + p.tps >= 9) {
+                ptx::umma_commit(x_empty(xb));
+                if (ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
+              }
+            }
+            __syncwarp();
+            if (++s == p.w_stages) { s = 0; wph ^= 1; }
+          }
         }
         if (++xb == 2) { xb = 0; xph ^= 1; }
       }
@@ -164,9 +184,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   } else {
     // ===================== epilogue warps 2..5: thread = output channel =====================
     const int lg = warp & 3;
-    const int co = lg * 32 + lane;
+    const int part = lg / p.cg;                          // which pixel part this warp stores (weight replicas on M)
+    const int co = (lg - part * p.cg) * 32 + lane;
     const bool co_live = p.out_f32 ? (co < p.cout) : (co < p.coutp);
-    const bool warp_live = lg * 32 < (p.out_f32 ? p.cout : p.coutp);
+    const bool warp_live = (part < p.rep) && (lg - part * p.cg) * 32 < (p.out_f32 ? p.cout : p.coutp);
     const float bias = (co < p.cout) ? __ldg(p.bias + co) : 0.f;
     uint8_t* o_gen = smem_raw + (o_base - ptx::smem_addr(smem_raw));
     const bool issuer = (threadIdx.x == 64);
@@ -184,7 +205,9 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         for (int half = 0; half < 2; ++half) {
           if (warp_live) {
             uint16_t* st = reinterpret_cast<uint16_t*>(o_gen) + co;
-            for (int c0 = 0; c0 < hpx; c0 += 16) {
+            const int ppx = ((hpx / p.rep) + 7) & ~7;         // pixels per part
+            const int cend = min(hpx, (part + 1) * ppx);
+            for (int c0 = part * ppx; c0 < cend; c0 += 16) {
               uint32_t v[16];
               ptx::tmem_ld16(taddr + half * hpx + c0, v);
               ptx::tmem_ld_wait();
@@ -195,7 +218,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
                   uint16_t bits;
                   if (p.fp16) { __half hv = __float2half_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
                   else { __nv_bfloat16 hv = __float2bfloat16_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
-                  if (c0 + i < hpx) st[(c0 + i) * p.coutp] = bits;
+                  if (c0 + i < cend) st[(c0 + i) * p.coutp] = bits;
                 }
               }
             }

@@ -92,8 +92,8 @@ def pick_kc(cin_span, stride=1, dil=1, has_in2=False):
     import os
     exact = 64 if cin_span % 64 == 0 else (32 if cin_span % 32 == 0 else 16)
     halo = int(os.environ.get("PWC_TC_HALO", "1")) and stride == 1 and 1 <= dil <= 8 and not has_in2
-    if halo and cin_span >= 64:
-        return 64
+    if halo:
+        return 64      # thin layers too: 128-byte rows (SWIZZLE_128B) are what the tensor pipe reads fast
     return exact
 
 
