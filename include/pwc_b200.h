@@ -136,6 +136,8 @@ int pwc_unpack_flow_f32(const float* in, long in_pitch, int in_coff, float* out,
  *   w      : packed bf16 [9][cin_span/kc][coutp][kc] (pwc_pack_conv_weight_bf16), coutp % 16 == 0, <= 256
  *   out    : out_f32 == 0: bf16 NHWC+pitch slice (all coutp channels are written; pad channels get 0);
  *            out_f32 == 1: fp32, channels < cout only, plus optional fp32 residual (dc_conv7 + flow2, PWCNet.py:268)
+ *            out_f32 == 2: fused predict_flowL + upfeatL (PWCNet.py:207-209...): cout = 10; channels 0,1 -> out (fp32 flow),
+ *                          channel 2+2*(2a+b)+j -> out2 (bf16) at pixel (2y+a, 2x+b), channel out2_coff + j, spatial 2H x 2W
  * ------------------------------------------------------------------------------------------ */
 typedef struct pwc_tc_conv pwc_tc_conv;
 int pwc_tc_conv_create(pwc_tc_conv** handle,

@@ -320,6 +320,8 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   if (rows > max_rows) rows = max_rows;
   if (rows < 2) rows = 2;
   while (ntiles(rows) < g_num_sms && rows > 8) rows = even_up(cdiv(rows, 2)) < 8 ? 8 : even_up(cdiv(rows, 2));
+  // thin single-chunk layers are epilogue-bound: a smaller tile leaves room for the replicated resident weight set
+  if (cdiv(cin_span, kc) == 1 && coutp <= 64 && rows > 16 && !out_f32) rows = 16;
   const int forced = env_int("PWC_TC_WM_ROWS", 0);
   if (forced >= 2 && forced <= max_rows && !(forced & 1)) rows = forced;
   p.rows = rows; p.npx = 8 * rows;
@@ -355,7 +357,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.fp16 = 0; p.dbg = env_int("PWC_TC_HALO_BO", 0);
   p.bias = bias; p.slope = slope;
   p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
-  p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = out2 ? n_split : N;
+  p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = (out2 && out_f32 != 2) ? n_split : N;
   p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
   const uint32_t nw = p.w_resident ? 9u * p.nchunk : p.w_stages * p.tps;
   h->smem_bytes = 2u * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + 8 * (10 + 2 * p.w_stages) + 16 + 1024;
@@ -403,11 +405,12 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
     cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(conv_tc_wm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   }
-  if (halo_eligible(stride, dil, in2 != nullptr, kc) && coutp <= 128 && env_int("PWC_TC_WM", 1) &&
-      !(out_f32 && (cin_span + kc - 1) / kc < 4)) {
+  if (halo_eligible(stride, dil, in2 != nullptr, kc) && coutp <= 128 && (env_int("PWC_TC_WM", 1) || out_f32 == 2) &&
+      !(out_f32 == 1 && (cin_span + kc - 1) / kc < 4)) {
     return create_wm(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
                      out2, out2_pitch, out2_coff, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope);
   }
+  if (out_f32 == 2) return (int)cudaErrorInvalidValue;     // fused predict_flow+upfeat exists in the WM kernel only
   if (halo_eligible(stride, dil, in2 != nullptr, kc)) {
     return create_halo(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
                        out2, out2_pitch, out2_coff, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope);

@@ -195,7 +195,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
       int n, ry, rx, ty0, tx0;
       decode(item, n, ry, rx, ty0, tx0);
-      const bool second = (n >= p.n_split) && (p.out2 != nullptr);
+      const bool second = (n >= p.n_split) && (p.out2 != nullptr) && (p.out_f32 != 2);
       const int nn = second ? n - p.n_split : n;
       ptx::mbar_wait(t_full(acc), tph);
       ptx::tc_fence_after();
@@ -244,7 +244,13 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
             if (co_live && oy < p.H && ox < p.W) {
               const long pix = ((long)nn * p.H + oy) * p.W + ox;
               float val = lrelu(__uint_as_float(v[i]) + bias, p.slope);
-              if (p.out_f32) {
+              if (p.out_f32 == 2 && co >= 2) {
+                // fused upfeat (ConvTranspose 4x4 s2 as 4 phase 3x3 convs): channel 2 + 2*(2a+b) + j -> pixel (2y+a, 2x+b)
+                const int k = co - 2, j = k & 1, b = (k >> 1) & 1, a = k >> 2;
+                const long up = (((long)n * 2 * p.H + 2 * oy + a) * (2 * p.W) + 2 * ox + b) * p.out2_pitch + p.out2_coff + j;
+                __nv_bfloat16 hv = __float2bfloat16_rn(val);
+                reinterpret_cast<__nv_bfloat16*>(p.out2)[up] = hv;
+              } else if (p.out_f32) {
                 if (p.residual) val += p.residual[pix * p.res_pitch + co];
                 reinterpret_cast<float*>(p.out)[pix * p.out_pitch + p.out_coff + co] = val;
               } else {

@@ -110,6 +110,45 @@ __global__ void __launch_bounds__(256) deconv4x4s2_c2_any_kernel(const TI* __res
   }
 }
 
+// Cin <= 4 (deconvL: flow -> up_flow, PWCNet.py:208,222,236,252): one THREAD per output pixel.
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) deconv4x4s2_c2_small_kernel(const TI* __restrict__ in, long in_pitch, int in_coff,
+                                                                   const float* __restrict__ w, const float* __restrict__ bias,
+                                                                   TO* __restrict__ out, long out_pitch, int out_coff,
+                                                                   float* __restrict__ out_b, long out_b_pitch,
+                                                                   int N, int Hin, int Win, int CinP) {
+  const int Hout = 2 * Hin, Wout = 2 * Win;
+  const long total = (long)N * Hout * Wout;
+  for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+    const int ox = e % Wout; const long t = e / Wout;
+    const int oy = t % Hout; const int n = t / Hout;
+    float s0 = bias[0], s1 = bias[1];
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      const int ky = ((oy + 1) & 1) + 2 * a;
+      const int iy2 = oy + 1 - ky;
+      const int iy = iy2 >> 1;
+      if (iy2 < 0 || iy >= Hin) continue;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int kx = ((ox + 1) & 1) + 2 * b;
+        const int ix2 = ox + 1 - kx;
+        const int ix = ix2 >> 1;
+        if (ix2 < 0 || ix >= Win) continue;
+        const float4 v = ld4(in + (((long)n * Hin + iy) * Win + ix) * in_pitch + in_coff);
+        const float* w0 = w + ((long)(ky * 4 + kx) * 2 + 0) * CinP;
+        const float4 a0 = *reinterpret_cast<const float4*>(w0);
+        const float4 a1 = *reinterpret_cast<const float4*>(w0 + CinP);
+        s0 = fmaf(v.x, a0.x, s0); s0 = fmaf(v.y, a0.y, s0); s0 = fmaf(v.z, a0.z, s0); s0 = fmaf(v.w, a0.w, s0);
+        s1 = fmaf(v.x, a1.x, s1); s1 = fmaf(v.y, a1.y, s1); s1 = fmaf(v.z, a1.z, s1); s1 = fmaf(v.w, a1.w, s1);
+      }
+    }
+    TO* o = out + e * out_pitch + out_coff;
+    st1(o, s0); st1(o + 1, s1);
+    if (out_b) { float* ob = out_b + e * out_b_pitch; ob[0] = s0; ob[1] = s1; }
+  }
+}
+
 }  // namespace pwc
 
 extern "C" int pwc_conv1a_bf16_fwd(const float* x, const float* w, const float* bias, void* out,
@@ -131,6 +170,21 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
   const long warps = (long)N * 4 * Hin * Win;
   const unsigned blocks = (unsigned)((warps * 32 + 255) / 256);
   cudaStream_t s = (cudaStream_t)stream;
+  if (CinP == 4) {
+    const long px = (long)N * 4 * Hin * Win;
+    const unsigned nb = (unsigned)((px + 255) / 256 < 148 * 16 ? (px + 255) / 256 : 148 * 16);
+#define PWC_DECONV_S(TI, TO)                                                                                              \
+  deconv4x4s2_c2_small_kernel<TI, TO><<<nb, 256, 0, s>>>(reinterpret_cast<const TI*>(in), in_pitch, in_coff, w, bias,      \
+                                                         reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b,           \
+                                                         out_b_pitch, N, Hin, Win, CinP)
+    if (in_dtype == PWC_F32 && out_dtype == PWC_F32) PWC_DECONV_S(float, float);
+    else if (in_dtype == PWC_F32 && out_dtype == PWC_BF16) PWC_DECONV_S(float, __nv_bfloat16);
+    else if (in_dtype == PWC_BF16 && out_dtype == PWC_BF16) PWC_DECONV_S(__nv_bfloat16, __nv_bfloat16);
+    else if (in_dtype == PWC_BF16 && out_dtype == PWC_F32) PWC_DECONV_S(__nv_bfloat16, float);
+    else return (int)cudaErrorInvalidValue;
+#undef PWC_DECONV_S
+    return (int)cudaGetLastError();
+  }
 #define PWC_DECONV(TI, TO)                                                                                             \
   deconv4x4s2_c2_any_kernel<TI, TO><<<blocks, 256, 0, s>>>(reinterpret_cast<const TI*>(in), in_pitch, in_coff, CinP, w, \
                                                            bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, \

@@ -28,8 +28,34 @@ def _roundup(a, b):
 PYR_CP = [4] + [_roundup(c, 16) for c in PYR_CH[1:]]      # 16, 32, 64, 96, 128, 208
 
 
+def _pfup_weights(lvl):
+    """predict_flowL [2,Cin,3,3] stacked with upfeatL (ConvTranspose2d(Cin,2,4,2,1), PWCNet.py:35-36) rewritten as a 3x3
+    convolution with 8 outputs: channel 2 + 2*(2a+b) + j is output j at pixel (2y+a, 2x+b);
+    tap (dy,dx) of phase (a,b) uses transposed-conv tap (ky,kx) = (a+1-2dy, b+1-2dx) when inside [0,3]."""
+    def make(sd):
+        wp, bp = sd[f"predict_flow{lvl}.weight"], sd[f"predict_flow{lvl}.bias"]
+        wt, bt = sd[f"upfeat{lvl}.weight"], sd[f"upfeat{lvl}.bias"]          # [Cin, 2, 4, 4]
+        cin = wp.shape[1]
+        w = torch.zeros(10, cin, 3, 3, device=wp.device, dtype=torch.float32)
+        w[0:2] = wp
+        for a in range(2):
+            for b in range(2):
+                for dy in (-1, 0, 1):
+                    ky = a + 1 - 2 * dy
+                    if not 0 <= ky <= 3:
+                        continue
+                    for dx in (-1, 0, 1):
+                        kx = b + 1 - 2 * dx
+                        if not 0 <= kx <= 3:
+                            continue
+                        c0 = 2 + 2 * (2 * a + b)
+                        w[c0:c0 + 2, :, dy + 1, dx + 1] = wt[:, :, ky, kx].t()
+        return w, torch.cat([bp, bt, bt, bt, bt])
+    return make
+
+
 class _TcLayer:
-    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp")
+    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn")
 
 
 class PlanBF16:
@@ -77,8 +103,9 @@ class PlanBF16:
 
     # ------------------------------------------------------------------ layer construction
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
-            cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None):
+            cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None):
         L = _TcLayer()
+        L.wfn = wfn
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
         L.kc = pick_kc(span, stride, dil, src2 is not None)
         L.coutp = _roundup(cout, 16)
@@ -169,10 +196,14 @@ class PlanBF16:
                 self._tc(f"conv{l}_{k}.0", len(cm), [128, 128, 96, 64, 32][k], cat, DEC_START[k], wd - DEC_START[k], cat,
                          DEC_WRITE[k], B, h, w, cmap=cm)
             cm = chan_map(l, 0)
-            self._tc(f"predict_flow{l}", len(cm), 2, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=True)
             if l > 2:
+                # predict_flowL and upfeatL read the same tensor: ONE conv with 2 + 8 output channels (the 4x4 stride-2
+                # transposed conv is 4 phase-shifted 3x3 convs); the epilogue scatters the 8 to the 2x-upsampled slice
+                self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
+                         dst2=self.cat[l - 1], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l))
                 self._deconv(f"deconv{l}", 2, self.flow[l], 0, 4, self.cat[l - 1], UPFLOW_OFF, h, w, dst_b=self.upflow[l - 1])
-                self._deconv(f"upfeat{l}", 448 + nin, cat, 0, wd, self.cat[l - 1], UPFEAT_OFF, h, w)
+            else:
+                self._tc(f"predict_flow{l}", len(cm), 2, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=True)
         h, w = self.hw[2]
         cm = chan_map(2, 0)
         src, cin, span, cmap = self.cat[2], len(cm), concat_width(2), cm
@@ -197,14 +228,15 @@ class PlanBF16:
         sd = {k: v.detach().to(device=dev, dtype=torch.float32).contiguous() for k, v in model.state_dict().items()}
         keep = []
         for key, L in self.layers.items():
-            wt = sd[key + ".weight"]
+            wt, bs = (sd[key + ".weight"], sd[key + ".bias"]) if L.wfn is None else L.wfn(sd)
+            wt = wt.contiguous()
             assert wt.shape[0] == L.cout and wt.shape[1] == L.cin, (key, tuple(wt.shape), L.cin, L.cout)
             mp = None
             if L.cmap is not None:
                 mp = torch.tensor(L.cmap, device=dev, dtype=torch.int32); keep.append(mp)
             _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.cout, L.cin, L.span, L.kc,
                                                      L.coutp, st), f"pack {key}")
-            L.b.copy_(sd[key + ".bias"])
+            L.b.copy_(bs)
         for key, (w, b, cin, cinp) in self.small.items():
             wt = sd[key + ".weight"]
             mp = None
