@@ -272,5 +272,19 @@ class PlanBF16:
         self.graph.replay()
         return self.out
 
+    def time_ops(self, reps=3):
+        """CUDA-event duration of every launch of the forward, one at a time (profiling aid for bench.py / tools):
+        returns [(name, seconds, algorithmic flops)]."""
+        st = _lib.stream_handle()
+        self._launch_all()
+        torch.cuda.current_stream().synchronize()
+        tot = [0.0] * len(self.ops)
+        for _ in range(reps):
+            for i, op in enumerate(self.ops):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); op(st); e1.record(); e1.synchronize()
+                tot[i] += e0.elapsed_time(e1) * 1e-3 / reps
+        return [(n, t, f) for (n, f), t in zip(self.op_info, tot)]
+
     def level_flow(self, lvl):
         return self.flow[lvl][..., :2].permute(0, 3, 1, 2).contiguous()
