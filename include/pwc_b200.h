@@ -152,6 +152,7 @@ int pwc_tc_conv_launch(const pwc_tc_conv* handle, void* stream);
 void pwc_tc_conv_destroy(pwc_tc_conv* handle);
 /* debug aid: timeline of CTA 0 of the halo kernel (enabled by env PWC_TC_HALO_BO bit 16); host memory destination */
 int pwc_debug_halo_trace(unsigned long long* host_dst, int count);
+int pwc_debug_corr_trace(unsigned long long* host_dst, int count);
 int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, const int* chan_map,
                               int Cout, int Cin, int cin_span, int kc, int coutp, void* stream);
 

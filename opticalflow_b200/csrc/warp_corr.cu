@@ -25,6 +25,7 @@
 //   * two stages, mbarrier full/empty handshakes: the gather + TMA of the next tile overlap the FMAs of this one.
 // NCHW kernel (API-compatible Correlation op, correlation_cuda.cc:10-87): one CTA per tile, all threads fill then
 // compute; outputs are stored coalesced along x.
+#include <stdlib.h>
 #include "common.cuh"
 #include "ptx_sm100.cuh"
 #include "tmap.cuh"
@@ -499,6 +500,8 @@ static int launch_nchw(const WarpCorrParams& p, cudaStream_t s) {
 
 }  // namespace pwc
 
+#include "warp_corr_tc.cuh"
+
 extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void* f2, long f2_pitch,
                                        const float* flow, long flow_pitch, float flow_scale,
                                        int align_corners, float mask_thresh, float slope,
@@ -518,7 +521,16 @@ extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void
   if (layout != PWC_LAYOUT_NHWC) return (int)cudaErrorInvalidValue;
   if (C % 4 || f1_pitch % 4 || f2_pitch % 4 || (flow && (flow_pitch % 2))) return (int)cudaErrorInvalidValue;
   if (out_pitch * 32 > 0x7fffffffL) return (int)cudaErrorInvalidValue;
-  if (dtype == PWC_BF16) return dispatch_rows<__nv_bfloat16, false>(p, s);
+  if (dtype == PWC_BF16) {
+    // thin-feature levels (C <= 64: pyramid levels 2 and 3) run the cost volume on the tensor cores
+    static const int use_tc = []() { const char* e = getenv("PWC_CORR_TC"); return e ? atoi(e) : 1; }();
+    const bool tc_ok = use_tc && (C == 16 || C == 32 || C == 64) && f1_pitch % 8 == 0 && f2_pitch % 8 == 0 &&
+                       ((reinterpret_cast<uintptr_t>(f1) | reinterpret_cast<uintptr_t>(f2)) & 15) == 0 &&
+                       (reinterpret_cast<uintptr_t>(out) & 15) == 0 && out_pitch % 8 == 0 && slope >= 0.f && slope <= 1.f &&
+                       get_encode_tiled() != nullptr;
+    if (tc_ok) return launch_warp_corr_tc(p, s);
+    return dispatch_rows<__nv_bfloat16, false>(p, s);
+  }
   if (dtype != PWC_F32) return (int)cudaErrorInvalidValue;
   // TMA needs a 16-byte aligned base and 16-byte multiples as strides; otherwise the producers load the f1 box themselves
   const bool tma_ok = ((reinterpret_cast<uintptr_t>(f1) & 15) == 0) && get_encode_tiled() != nullptr;
@@ -529,4 +541,10 @@ extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void
 extern "C" int pwc_corr_fwd(const void* f1, const void* f2, void* out, int B, int C, int H, int W, int md, void* stream) {
   return pwc_warp_corr_lrelu_fwd(f1, 0, f2, 0, nullptr, 0, 1.0f, 0, 0.9999f, 1.0f, out, 0, B, C, H, W, md,
                                  PWC_LAYOUT_NCHW, PWC_F32, stream);
+}
+
+// debug: timeline marks of the tensor-core cost-volume kernel (CTA 0), see tools/trace_corr.py
+extern "C" int pwc_debug_corr_trace(unsigned long long* host_dst, int count) {
+  if (!host_dst || count < 0 || count > 3 * 64 * 4) return (int)cudaErrorInvalidValue;
+  return (int)cudaMemcpyFromSymbol(host_dst, pwc::g_corr_trace, sizeof(unsigned long long) * count);
 }

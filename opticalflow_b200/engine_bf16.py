@@ -10,6 +10,7 @@ launch list and is captured once into a CUDA graph.
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -25,7 +26,28 @@ def _roundup(a, b):
     return (a + b - 1) // b * b
 
 
+S2D = {} if os.environ.get("PWC_S2D", "1") == "0" else {1: 4, 2: 2}            # pixels per super-pixel for the 16- and 32-channel pyramid levels (64 channels per row)
 PYR_CP = [4] + [_roundup(c, 16) for c in PYR_CH[1:]]      # 16, 32, 64, 96, 128, 208
+
+
+def _s2d_weights(name, g):
+    """Thin layers (C = 16 or 32 channels) as a full-width GEMM: g adjacent pixels of a dense NHWC row are ONE
+    super-pixel with g*C channels (a free view of the same memory), so every 128-byte operand row carries real data.
+    The 3x3 conv becomes a 3x3 conv on [H][W/g] whose weight is block-structured:
+      W'[(dx,co), (dx',ci), ky, KX] = W[co, ci, ky, kx],  kx = g*(KX-1) + dx' - dx + 1  when 0 <= kx <= 2, else 0
+    (input pixel g*(X+KX-1)+dx' = g*X+dx + kx-1).  Same products, zeros added: results are unchanged."""
+    def make(sd):
+        w, b = sd[name + ".weight"], sd[name + ".bias"]
+        co, ci = w.shape[0], w.shape[1]
+        w2 = torch.zeros(g, co, g, ci, 3, 3, device=w.device, dtype=torch.float32)
+        for dx in range(g):
+            for dxp in range(g):
+                for KX in range(3):
+                    kx = g * (KX - 1) + dxp - dx + 1
+                    if 0 <= kx <= 2:
+                        w2[dx, :, dxp, :, :, KX] = w[:, :, :, kx]
+        return w2.reshape(g * co, g * ci, 3, 3), b.repeat(g)
+    return make
 
 
 def _pfup_weights(lvl):
@@ -103,7 +125,8 @@ class PlanBF16:
 
     # ------------------------------------------------------------------ layer construction
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
-            cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None):
+            cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
+            flops=None):
         L = _TcLayer()
         L.wfn = wfn
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
@@ -124,7 +147,7 @@ class PlanBF16:
         self.layers[key] = L
         lib = self.lib
         ho, wo = (hin - 1) // stride + 1, (win - 1) // stride + 1
-        self.op_info.append((key, 2.0 * N * ho * wo * cout * cin * 9))
+        self.op_info.append((key, flops if flops is not None else 2.0 * N * ho * wo * cout * cin * 9))
         self.ops.append(lambda st: _lib.check(lib.pwc_tc_conv_launch(h, st), key))
 
     def _deconv(self, key, cin, src, src_coff, span, dst, dst_coff, hin, win, dst_b=None):
@@ -177,9 +200,19 @@ class PlanBF16:
                 else:
                     self._tc(names[0] + ".0", cin, PYR_CH[l], self.cat[l - 1], C1_OFF, PYR_CP[l - 1], self.pa[l], 0, 2 * B,
                              hin, win, stride=2, src2=self.f2[l - 1], n_split=B)
-            self._tc(names[1] + ".0", PYR_CH[l], PYR_CH[l], self.pa[l], 0, PYR_CP[l], self.pb[l], 0, 2 * B, h, w)
+            g = S2D.get(l, 1)            # thin dense->dense layers run on the space-to-depth view (see _s2d_weights)
+            C = PYR_CH[l]
+            fl = 2.0 * 2 * B * h * w * C * C * 9
+            va = self.pa[l].view(2 * B, h, w // g, g * PYR_CP[l]) if g > 1 else self.pa[l]
+            vb = self.pb[l].view(2 * B, h, w // g, g * PYR_CP[l]) if g > 1 else self.pb[l]
+            if g > 1:
+                self._tc(names[1] + ".0", g * C, g * C, va, 0, g * C, vb, 0, 2 * B, h, w // g,
+                         wfn=_s2d_weights(names[1] + ".0", g), flops=fl)
+            else:
+                self._tc(names[1] + ".0", C, C, self.pa[l], 0, PYR_CP[l], self.pb[l], 0, 2 * B, h, w)
             if l == 1:
-                self._tc(names[2] + ".0", 16, 16, self.pb[1], 0, 16, self.pa[1], 0, 2 * B, h, w)
+                self._tc(names[2] + ".0", g * C, g * C, vb, 0, g * C, va, 0, 2 * B, h, w // g,
+                         wfn=_s2d_weights(names[2] + ".0", g), flops=fl)
             elif l < 6:
                 self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.cat[l], C1_OFF, 2 * B, h, w,
                          dst2=self.f2[l], n_split=B)

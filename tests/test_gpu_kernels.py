@@ -110,6 +110,35 @@ def test_fused_warp_corr_bf16_features():
     assert (out - ref).abs().max().item() <= 8e-3 * ref.abs().max().item()    # bf16 output rounding (2^-8)
 
 
+@pytest.mark.parametrize("case", [
+    # B, C, H, W, with_flow        (C <= 64 bf16 NHWC -> tensor-core cost volume, csrc/warp_corr_tc.cuh)
+    (2, 32, 112, 256, True), (1, 64, 56, 128, True), (2, 32, 30, 72, True), (1, 16, 5, 24, True), (1, 48, 9, 33, True),
+    (2, 64, 19, 40, False), (3, 32, 64, 96, True),
+])
+def test_fused_warp_corr_tensor_core_path(case):
+    """bf16 features inside concat-buffer slices (pitch 544+C: f1 at channel 544, cost volume at 448), ragged shapes, more
+    items than one wave.  Bar: bf16 rounding of the output plus of the warped operand (both 2^-9 relative)."""
+    from opticalflow_b200 import ops
+    B, C, H, W, with_flow = case
+    f1, f2, flow = O.corr_microbench_inputs(2, B, H, W, C, with_flow=with_flow)
+    f1b, f2b = f1.bfloat16(), f2.bfloat16()
+    ref = O.warp_corr_lrelu(f1b.float(), f2b.float(), flow, 5.0)
+    d = _dev()
+    cat = torch.full((B, H, W, 544 + 32 * ((C + 31) // 32)), 7.0, device=d, dtype=torch.bfloat16)
+    cat[..., 544:544 + C] = f1b.permute(0, 2, 3, 1).to(d)
+    f2n = f2b.permute(0, 2, 3, 1).contiguous().to(d)
+    fl = None if flow is None else flow.permute(0, 2, 3, 1).contiguous().to(d)
+    ops.warp_corr_lrelu(cat[..., 544:544 + C], f2n, fl, 5.0, layout="nhwc", out=cat[..., 448:529])
+    torch.cuda.synchronize()
+    out = cat[..., 448:529].float().permute(0, 3, 1, 2).cpu()
+    scale = ref.abs().max().item()
+    err = (out - ref).abs()
+    assert err.max().item() <= 8e-3 * scale, f"max err {err.max().item() / scale:.3e} of scale"
+    assert err.mean().item() <= 1e-3 * scale
+    # neighbours of the slice are untouched
+    assert (cat[..., :448] == 7.0).all() and (cat[..., 529:544] == 7.0).all()
+
+
 CONV_CASES = [
     # cin, cout, stride, dil, H, W
     (4, 16, 2, 1, 32, 48), (16, 16, 1, 1, 17, 23), (32, 64, 2, 1, 16, 32), (96, 128, 2, 1, 14, 18),
