@@ -138,6 +138,11 @@ int pwc_unpack_flow_f32(const float* in, long in_pitch, int in_coff, float* out,
  *            out_f32 == 1: fp32, channels < cout only, plus optional fp32 residual (dc_conv7 + flow2, PWCNet.py:268)
  *            out_f32 == 2: fused predict_flowL + upfeatL (PWCNet.py:207-209...): cout = 10; channels 0,1 -> out (fp32 flow),
  *                          channel 2+2*(2a+b)+j -> out2 (bf16) at pixel (2y+a, 2x+b), channel out2_coff + j, spatial 2H x 2W
+ *            out_f32 | 16: tap-stacked weights for layers with 9*cout <= 128 (predict_flowL, dc_conv7): coutp = 128 and
+ *                          w_packed comes from pwc_pack_conv_weight_bf16 applied to the [128,Cin,3,3] tensor whose row
+ *                          tap*cout + co holds W[co,:,tap/3,tap%3] at kernel position (0,0) (zeros elsewhere); the kernel
+ *                          runs ONE MMA group per 64-channel chunk on the unshifted halo tile and sums the 9 taps in the
+ *                          epilogue.  stride 1, dilation 1, fp32 output modes only.
  * ------------------------------------------------------------------------------------------ */
 typedef struct pwc_tc_conv pwc_tc_conv;
 int pwc_tc_conv_create(pwc_tc_conv** handle,

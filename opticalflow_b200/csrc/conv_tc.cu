@@ -306,10 +306,14 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
                      int out_f32, const float* residual, long res_pitch, int N, int H, int W, int dil, float slope) {
   if (coutp % 16 || coutp < 16 || coutp > 128 || cout > coutp || (in_pitch & 7) || (in_coff & 7))
     return (int)cudaErrorInvalidValue;
+  const int ts = (out_f32 >> 4) & 1;              // tap-stacked weights ([chunk][tap*cout + co][64] in the tap-0 section)
+  out_f32 &= 3;
+  if (ts && (dil != 1 || 9 * cout > 128 || coutp != 128 || !out_f32 || kc != 64)) return (int)cudaErrorInvalidValue;
   pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
   if (!h) return (int)cudaErrorMemoryAllocation;
   h->halo = 2;
   WmParams& p = h->wp;
+  p.ts = ts; p.ntaps = ts ? 1 : 9; p.s_stride = 0; p.s_bytes = 0;
   p.N = N; p.H = H; p.W = W; p.dil = dil;
   p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc);
   const int Hd = cdiv(H, dil), Wd = cdiv(W, dil);
@@ -324,16 +328,26 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   if (cdiv(cin_span, kc) == 1 && coutp <= 64 && rows > 16 && !out_f32) rows = 16;
   const int forced = env_int("PWC_TC_WM_ROWS", 0);
   if (forced >= 2 && forced <= max_rows && !(forced & 1)) rows = forced;
-  p.rows = rows; p.npx = 8 * rows;
+  if (ts) {                                       // N = whole halo tile (rows+2) x 10 <= 256 pixels
+    rows = cdiv(H, cdiv(H, 23));
+    while (ntiles(rows) < g_num_sms && rows > 6) rows = cdiv(rows, 2);
+  }
+  p.rows = rows; p.npx = ts ? (((rows + 2) * 10 + 15) & ~15) : 8 * rows;
   p.tiles_x = cdiv(Wd, 8); p.tiles_y = cdiv(Hd, rows);
   p.tiles_per_img = dil * dil * p.tiles_x * p.tiles_y;
   p.num_items = (int)ntiles(rows);
   const uint32_t row_bytes = (uint32_t)kc * 2;
   p.x_bytes_tx = (uint32_t)(rows + 2) * 10u * row_bytes;
   p.x_bytes = (p.x_bytes_tx + 1023u) & ~1023u;
+  if (ts) {
+    const uint32_t need = (uint32_t)p.npx * row_bytes;        // the MMA reads npx pixel rows (tail rows: don't-care columns)
+    if (p.x_bytes < ((need + 1023u) & ~1023u)) p.x_bytes = (need + 1023u) & ~1023u;
+    p.s_stride = p.npx + 4;                                   // words; == 4 (mod 32) when npx % 32 == 0, else still 16B aligned
+    p.s_bytes = ((uint32_t)(9 * cout) * p.s_stride * 4u + 1023u) & ~1023u;
+  }
   p.cin_span = cin_span;
   p.w_bytes_tx = (uint32_t)coutp * row_bytes;
-  p.tma_store = (!out_f32 && env_int("PWC_TC_WM_TMASTORE", 1)) ? 1 : 0;
+  p.tma_store = (!out_f32 && !ts && env_int("PWC_TC_WM_TMASTORE", 1)) ? 1 : 0;
   p.o_bytes = p.tma_store ? (((uint32_t)(rows / 2) * 8u * coutp * 2u + 1023u) & ~1023u) : 0u;
   // weight-tile replication on M (epilogue parallelism for thin layers): only when the whole weight set stays resident
   p.cg = cdiv(out_f32 ? cout : coutp, 32); p.rep = 1;
@@ -343,16 +357,17 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
       env_int("PWC_TC_HALO_RESIDENT", 1)) p.rep = 4 / p.cg;
   p.w_bytes = p.rep > 1 ? full_tile : ((p.w_bytes_tx + 1023u) & ~1023u);
   p.w_pad = full_tile > p.w_bytes ? full_tile - p.w_bytes : 0u;
-  const uint32_t budget = 216u * 1024u - 2u * p.x_bytes - p.w_pad - p.o_bytes;
+  const uint32_t budget = 216u * 1024u - 2u * p.x_bytes - p.w_pad - p.o_bytes - p.s_bytes;
   const uint32_t all_w = 9u * p.nchunk * p.w_bytes;
-  p.w_resident = (all_w <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
+  p.w_resident = (!ts && all_w <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
   if (!p.w_resident && p.rep > 1) { delete h; return (int)cudaErrorInvalidValue; }
   // streamed weights: 3 taps per stage when the pixel tile is small (per-stage handshakes would dominate the MMAs)
   p.tps = 1;
-  if (!p.w_resident && p.npx <= 128 && budget / (3u * p.w_bytes) >= 3 && env_int("PWC_TC_WM_TPS", 3) == 3) p.tps = 3;
+  if (!ts && !p.w_resident && p.npx <= 128 && budget / (3u * p.w_bytes) >= 3 && env_int("PWC_TC_WM_TPS", 3) == 3) p.tps = 3;
   uint32_t stages = budget / (p.w_bytes * p.tps);
   p.w_stages = stages > 12 ? 12 : (stages < 2 ? 2 : stages);
   uint32_t cols = 32; while (cols < 2u * p.npx) cols <<= 1;
+  if (ts) cols = 512;
   p.tmem_cols = cols;
   p.fp16 = 0; p.dbg = env_int("PWC_TC_HALO_BO", 0);
   p.bias = bias; p.slope = slope;
@@ -360,7 +375,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = (out2 && out_f32 != 2) ? n_split : N;
   p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
   const uint32_t nw = p.w_resident ? 9u * p.nchunk : p.w_stages * p.tps;
-  h->smem_bytes = 2u * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + 8 * (10 + 2 * p.w_stages) + 16 + 1024;
+  h->smem_bytes = 2u * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + p.s_bytes + 8 * (10 + 2 * p.w_stages) + 16 + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
   int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, W, H, N,

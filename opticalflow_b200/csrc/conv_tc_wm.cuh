@@ -24,6 +24,8 @@ struct WmParams {
   uint32_t x_bytes_tx, x_bytes, w_bytes_tx, w_bytes, w_stages, w_resident, w_pad, o_bytes, tmem_cols;
   int tma_store;                                  // 16-bit output through a shared-memory staging tile + TMA store
   int fp16, dbg;
+  int ts, ntaps, s_stride;                        // tap-stacked mode (Cout*9 <= 128): M rows = (tap, cout), ONE MMA group per
+  uint32_t s_bytes;                               // chunk on the unshifted halo tile, taps summed in the epilogue via smem S
   const float* bias; float slope;
   void* out; long out_pitch; int out_coff;
   void* out2; long out2_pitch; int out2_coff; int n_split;
@@ -44,7 +46,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   const uint32_t w_base = base + 2u * p.x_bytes;                  // weight ring (or the resident weight set)
   const uint32_t nw = p.w_resident ? (uint32_t)(9 * p.nchunk) : p.w_stages * p.tps;
   const uint32_t o_base = w_base + nw * p.w_bytes + p.w_pad;      // w_pad: the M=128 MMA reads 128 rows from a CoutP-row tile
-  const uint32_t bar_base = o_base + p.o_bytes;                   // o: output staging tile (half an item)
+  const uint32_t s_base = o_base + p.o_bytes;                     // S: per-tap partial sums [9*cout][s_stride] fp32 (TS mode)
+  const uint32_t bar_base = s_base + p.s_bytes;                   // o: output staging tile (half an item)
   auto x_full = [&](int i) { return bar_base + 8u * i; };
   auto x_empty = [&](int i) { return bar_base + 8u * (2 + i); };
   auto t_full = [&](int i) { return bar_base + 8u * (4 + i); };
@@ -109,7 +112,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         __syncwarp();
         if (++xb == 2) { xb = 0; xph ^= 1; }
         if (!p.w_resident) {
-          for (int tap = 0; tap < 9; tap += p.tps) {
+          for (int tap = 0; tap < p.ntaps; tap += p.tps) {
             ptx::mbar_wait(w_empty(s), wph ^ 1);
             if (ptx::elect_one()) {
               ptx::mbar_expect_tx(w_full(s), p.w_bytes_tx * p.tps);
@@ -128,14 +131,14 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     if (p.fp16) idesc &= ~((7u << 7) | (7u << 10));          // A/B format 0 = F16
     const uint32_t row_bytes = p.kc * 2;
     const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
-    const uint32_t sbo_x = 10u * row_bytes;
+    const uint32_t sbo_x = (p.ts ? 8u : 10u) * row_bytes;     // TS: all halo pixels in order; else 8 of every 10
     int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
     int acc = 0; uint32_t tph = 0;
     if (p.w_resident) ptx::mbar_wait(w_all, 0);
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
       ptx::mbar_wait(t_empty(acc), tph ^ 1);
       ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.npx);
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * (p.ts ? 256 : p.npx));
       for (int ch = 0; ch < p.nchunk; ++ch) {
         ptx::mbar_wait(x_full(xb), xph);
         ptx::tc_fence_after();
@@ -160,7 +163,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           }
           __syncwarp();
         } else {
-          for (int tap0 = 0; tap0 < 9; tap0 += p.tps) {
+          for (int tap0 = 0; tap0 < p.ntaps; tap0 += p.tps) {
             ptx::mbar_wait(w_full(s), wph);
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
@@ -168,7 +171,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
               issue_tap(sw0, tap0);
               if (p.tps == 3) { issue_tap(sw0 + p.w_bytes, tap0 + 1); issue_tap(sw0 + 2 * p.w_bytes, tap0 + 2); }
               ptx::umma_commit(w_empty(s));
-              if (tap0 + p.tps >= 9) {
+              if (tap0 + p.tps >= p.ntaps) {
                 ptx::umma_commit(x_empty(xb));
                 if (ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
               }
@@ -199,7 +202,54 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       const int nn = second ? n - p.n_split : n;
       ptx::mbar_wait(t_full(acc), tph);
       ptx::tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * p.npx);
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * (p.ts ? 256 : p.npx));
+      if (p.ts) {
+        // ---- tap-stacked: TMEM lane m = tap*cout + co holds that tap's partial sums over the whole halo tile ----
+        float* S = reinterpret_cast<float*>(smem_raw + (s_base - ptx::smem_addr(smem_raw)));
+        const int m = lg * 32 + lane, mrows = 9 * p.cout;
+        if (lg * 32 < mrows) {
+          float4* srow = reinterpret_cast<float4*>(S + (size_t)m * p.s_stride);
+          for (int c0 = 0; c0 < p.npx; c0 += 16) {
+            uint32_t v[16];
+            ptx::tmem_ld16(taddr + c0, v);
+            ptx::tmem_ld_wait();
+            if (m < mrows) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                srow[(c0 >> 2) + i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                                  __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+            }
+          }
+        }
+        ptx::tc_fence_before();
+        named_bar(2, 128);
+        if (lane == 0) ptx::mbar_arrive(t_empty(acc));       // accumulator is in S now: the next item may start
+        const int et = threadIdx.x - 64;
+        const int nout = p.cout * p.rows * 8;
+        for (int idx = et; idx < nout; idx += 128) {
+          const int px = idx & 7, r1 = idx >> 3, py = r1 % p.rows, co2 = r1 / p.rows;
+          const int oy = ty0 + py, ox = tx0 + px;
+          if (oy >= p.H || ox >= p.W) continue;
+          const float* sp = S + (size_t)co2 * p.s_stride + py * 10 + px;
+          float a = __ldg(p.bias + co2);
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap)
+            a += sp[(size_t)tap * p.cout * p.s_stride + (tap / 3) * 10 + (tap % 3)];
+          float val = lrelu(a, p.slope);
+          const long pix = ((long)n * p.H + oy) * p.W + ox;
+          if ((p.out_f32 & 3) == 2 && co2 >= 2) {
+            const int k = co2 - 2, j = k & 1, b = (k >> 1) & 1, aa = k >> 2;
+            const long up = (((long)n * 2 * p.H + 2 * oy + aa) * (2 * p.W) + 2 * ox + b) * p.out2_pitch + p.out2_coff + j;
+            reinterpret_cast<__nv_bfloat16*>(p.out2)[up] = __float2bfloat16_rn(val);
+          } else {
+            if (p.residual) val += p.residual[pix * p.res_pitch + co2];
+            reinterpret_cast<float*>(p.out)[pix * p.out_pitch + p.out_coff + co2] = val;
+          }
+        }
+        named_bar(2, 128);                                   // S may be overwritten by the next item
+        if (++acc == 2) { acc = 0; tph ^= 1; }
+        continue;
+      }
       if (p.tma_store) {
         const int hpx = p.npx >> 1;                        // pixels per half item (rows/2 tile rows)
         for (int half = 0; half < 2; ++half) {

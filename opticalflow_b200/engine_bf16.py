@@ -50,6 +50,22 @@ def _s2d_weights(name, g):
     return make
 
 
+def _stacked(wfn_or_key):
+    """Tap-stacked weight tensor for layers with 9*Cout <= 128 (include/pwc_b200.h, out_f32 | 16): row tap*Cout + co of
+    a [128, Cin, 3, 3] tensor holds W[co, :, tap//3, tap%3] at kernel position (0,0)."""
+    def make(sd):
+        w, b = wfn_or_key(sd) if callable(wfn_or_key) else (sd[wfn_or_key + ".weight"], sd[wfn_or_key + ".bias"])
+        cout, cin = w.shape[0], w.shape[1]
+        ws = torch.zeros(128, cin, 3, 3, device=w.device, dtype=torch.float32)
+        for tap in range(9):
+            ws[tap * cout:(tap + 1) * cout, :, 0, 0] = w[:, :, tap // 3, tap % 3]
+        return ws, b
+    return make
+
+
+TS_MODE = os.environ.get("PWC_TC_TS", "1") != "0"
+
+
 def _pfup_weights(lvl):
     """predict_flowL [2,Cin,3,3] stacked with upfeatL (ConvTranspose2d(Cin,2,4,2,1), PWCNet.py:35-36) rewritten as a 3x3
     convolution with 8 outputs: channel 2 + 2*(2a+b) + j is output j at pixel (2y+a, 2x+b);
@@ -77,7 +93,7 @@ def _pfup_weights(lvl):
 
 
 class _TcLayer:
-    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn")
+    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows")
 
 
 class PlanBF16:
@@ -126,12 +142,14 @@ class PlanBF16:
     # ------------------------------------------------------------------ layer construction
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
-            flops=None):
+            flops=None, ts=False):
         L = _TcLayer()
-        L.wfn = wfn
+        ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
+        L.wfn = _stacked(wfn if wfn is not None else key) if ts else wfn
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
         L.kc = pick_kc(span, stride, dil, src2 is not None)
-        L.coutp = _roundup(cout, 16)
+        L.coutp = 128 if ts else _roundup(cout, 16)
+        L.wrows = 128 if ts else cout                   # rows of the weight tensor handed to the packer
         dev = self.device
         L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp, device=dev, dtype=BF)
         L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
@@ -140,7 +158,7 @@ class PlanBF16:
             ctypes.byref(h), _lib.ptr(src), src.shape[-1], src_coff,
             _lib.ptr(src2), (src2.shape[-1] if src2 is not None else 0), src2_coff, n_split, span, L.kc,
             _lib.ptr(L.w), _lib.ptr(L.b), cout, L.coutp, _lib.ptr(dst), dst.shape[-1], dst_coff,
-            _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32),
+            _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32) | (16 if ts else 0),
             _lib.ptr(residual), (residual.shape[-1] if residual is not None else 0), N, hin, win, stride, dil, slope)
         _lib.check(e, f"pwc_tc_conv_create {key}")
         L.handle = h
@@ -233,17 +251,19 @@ class PlanBF16:
                 # predict_flowL and upfeatL read the same tensor: ONE conv with 2 + 8 output channels (the 4x4 stride-2
                 # transposed conv is 4 phase-shifted 3x3 convs); the epilogue scatters the 8 to the 2x-upsampled slice
                 self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
-                         dst2=self.cat[l - 1], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l))
+                         dst2=self.cat[l - 1], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True)
                 self._deconv(f"deconv{l}", 2, self.flow[l], 0, 4, self.cat[l - 1], UPFLOW_OFF, h, w, dst_b=self.upflow[l - 1])
             else:
-                self._tc(f"predict_flow{l}", len(cm), 2, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=True)
+                self._tc(f"predict_flow{l}", len(cm), 2, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=True,
+                         ts=True)
         h, w = self.hw[2]
         cm = chan_map(2, 0)
         src, cin, span, cmap = self.cat[2], len(cm), concat_width(2), cm
         for i, (name, cout, dil) in enumerate(DC):
             self._tc(name + ".0", cin, cout, src, 0, span, self.dc[i], 0, B, h, w, dil=dil, cmap=cmap)
             src, cin, span, cmap = self.dc[i], cout, cout, None
-        self._tc("dc_conv7", 32, 2, src, 0, 32, self.flow_out4, 0, B, h, w, slope=1.0, out_f32=True, residual=self.flow[2])
+        self._tc("dc_conv7", 32, 2, src, 0, 32, self.flow_out4, 0, B, h, w, slope=1.0, out_f32=True, residual=self.flow[2],
+                 ts=True)
         uo = (_lib.ptr(self.flow_out4), 4, 0, _lib.ptr(self.out), B, h, w, 1.0)
         self.op_info.append(("unpack_flow", 0.0))
         self.ops.append(lambda st: _lib.check(lib.pwc_unpack_flow_f32(*uo, st), "unpack_flow"))
@@ -263,11 +283,11 @@ class PlanBF16:
         for key, L in self.layers.items():
             wt, bs = (sd[key + ".weight"], sd[key + ".bias"]) if L.wfn is None else L.wfn(sd)
             wt = wt.contiguous()
-            assert wt.shape[0] == L.cout and wt.shape[1] == L.cin, (key, tuple(wt.shape), L.cin, L.cout)
+            assert wt.shape[0] == L.wrows and wt.shape[1] == L.cin, (key, tuple(wt.shape), L.cin, L.wrows)
             mp = None
             if L.cmap is not None:
                 mp = torch.tensor(L.cmap, device=dev, dtype=torch.int32); keep.append(mp)
-            _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.cout, L.cin, L.span, L.kc,
+            _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.wrows, L.cin, L.span, L.kc,
                                                      L.coutp, st), f"pack {key}")
             L.b.copy_(bs)
         for key, (w, b, cin, cinp) in self.small.items():

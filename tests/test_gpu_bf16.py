@@ -21,6 +21,32 @@ TC_CASES = [
 ]
 
 
+@pytest.mark.parametrize("case", [
+    # cin, cout, N, H, W, residual      tap-stacked mode (9*cout <= 128): predict_flowL / pfupL / dc_conv7 shapes
+    (576, 2, 1, 16, 32, False), (32, 2, 2, 16, 32, True), (565, 2, 2, 112, 256, False), (629, 10, 1, 56, 128, False),
+    (597, 10, 2, 7, 16, False), (80, 14, 1, 23, 41, False), (64, 2, 3, 50, 9, True),
+])
+def test_conv3x3_tc_tap_stacked(case):
+    from opticalflow_b200 import ops
+    cin, cout, N, H, W, with_res = case
+    g = torch.Generator().manual_seed(300 + cin + cout)
+    x = torch.randn(N, cin, H, W, generator=g).bfloat16()
+    w = (torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin ** 0.5)).bfloat16().float()
+    b = torch.randn(cout, generator=g) * 0.1
+    res = torch.randn(N, H, W, 4, generator=g) if with_res else None
+    ref = F.conv2d(x.float(), w, b, padding=1)
+    if with_res:
+        ref = ref + res.permute(0, 3, 1, 2)[:, :cout]
+    d = torch.device("cuda:0")
+    span = (cin + 15) // 16 * 16
+    xn = torch.zeros(N, H, W, span, dtype=torch.bfloat16)
+    xn[..., :cin] = x.permute(0, 2, 3, 1)
+    out = ops.conv3x3_tc(xn.to(d), w.to(d), b.to(d), 1, 1, 1.0, cin_span=span, out_f32=True, ts=True,
+                         residual=None if res is None else res.to(d))
+    out = out.float().permute(0, 3, 1, 2).cpu()[:, :cout]
+    assert (out - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
+
+
 @pytest.mark.parametrize("case", TC_CASES)
 def test_conv3x3_tc_matches_torch(case):
     from opticalflow_b200 import ops
