@@ -501,6 +501,7 @@ static int launch_nchw(const WarpCorrParams& p, cudaStream_t s) {
 }  // namespace pwc
 
 #include "warp_corr_tc.cuh"
+#include "warp_corr_small.cuh"
 
 extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void* f2, long f2_pitch,
                                        const float* flow, long flow_pitch, float flow_scale,
@@ -529,6 +530,14 @@ extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void
                        (reinterpret_cast<uintptr_t>(out) & 15) == 0 && out_pitch % 8 == 0 && slope >= 0.f && slope <= 1.f &&
                        get_encode_tiled() != nullptr;
     if (tc_ok) return launch_warp_corr_tc(p, s);
+    // wide-feature (small) levels 4-6: latency-oriented kernel, one warp per row displacement
+    static const int use_small = []() { const char* e = getenv("PWC_CORR_SMALL"); return e ? atoi(e) : 1; }();
+    // (each CTA re-gathers the 9 warped rows it needs: only worth it while the grid fits the machine once)
+    const bool small_ok = use_small && C > 64 && C % 4 == 0 && C <= 200 && (long)cdiv(W, 32) * H * B <= 160 && f1_pitch % 4 == 0 && f2_pitch % 4 == 0 &&
+                          ((reinterpret_cast<uintptr_t>(f1) | reinterpret_cast<uintptr_t>(f2)) & 7) == 0 &&
+                          (reinterpret_cast<uintptr_t>(out) & 15) == 0 && out_pitch % 8 == 0 && slope >= 0.f &&
+                          slope <= 1.f && get_encode_tiled() != nullptr;
+    if (small_ok) return launch_warp_corr_small(p, s);
     return dispatch_rows<__nv_bfloat16, false>(p, s);
   }
   if (dtype != PWC_F32) return (int)cudaErrorInvalidValue;

@@ -114,6 +114,8 @@ def test_fused_warp_corr_bf16_features():
     # B, C, H, W, with_flow        (C <= 64 bf16 NHWC -> tensor-core cost volume, csrc/warp_corr_tc.cuh)
     (2, 32, 112, 256, True), (1, 64, 56, 128, True), (2, 32, 30, 72, True), (1, 16, 5, 24, True), (1, 48, 9, 33, True),
     (2, 64, 19, 40, False), (3, 32, 64, 96, True),
+    # C > 64: small-level kernel (csrc/warp_corr_small.cuh), the level 4/5/6 shapes and a ragged one
+    (2, 96, 28, 64, True), (2, 128, 14, 32, True), (2, 196, 7, 16, False), (1, 100, 9, 45, True),
 ])
 def test_fused_warp_corr_tensor_core_path(case):
     """bf16 features inside concat-buffer slices (pitch 544+C: f1 at channel 544, cost volume at 448), ragged shapes, more
