@@ -154,6 +154,13 @@ int pwc_tc_conv_create(pwc_tc_conv** handle,
                        const float* residual, long res_pitch,
                        int N, int Hin, int Win, int stride, int dil, float slope);
 int pwc_tc_conv_launch(const pwc_tc_conv* handle, void* stream);
+/* Optional tuning of a created handle (space-to-depth execution of Cout = 32 / 64 layers: g = 128/Cout adjacent pixels
+ * of a dense NHWC buffer are one super-pixel, so all 128 MMA rows carry outputs):
+ *   set_skip       : bit ch of masks[tap] (tap = 3*ky + kx, 9 entries) set <=> the packed weight block of that tap and
+ *                    64-channel chunk ch is all zero; its TMA load and MMAs are dropped.
+ *   set_out_groups : the CoutP output channels are g groups of CoutP/g; group i goes to channel out_coff + i*group_pitch. */
+int pwc_tc_conv_set_skip(pwc_tc_conv* handle, const unsigned long long* masks);
+int pwc_tc_conv_set_out_groups(pwc_tc_conv* handle, int g, long group_pitch);
 void pwc_tc_conv_destroy(pwc_tc_conv* handle);
 /* debug aid: timeline of CTA 0 of the halo kernel (enabled by env PWC_TC_HALO_BO bit 16); host memory destination */
 int pwc_debug_halo_trace(unsigned long long* host_dst, int count);

@@ -29,6 +29,8 @@ SIGNATURES = {
     "pwc_tc_conv_create": (_i, [ctypes.POINTER(_vp), _vp, _l, _i, _vp, _l, _i, _i, _i, _i, _vp, _vp, _i, _i,
                                 _vp, _l, _i, _vp, _l, _i, _i, _vp, _l, _i, _i, _i, _i, _i, _f]),
     "pwc_tc_conv_launch": (_i, [_vp, _vp]),
+    "pwc_tc_conv_set_skip": (_i, [_vp, _vp]),
+    "pwc_tc_conv_set_out_groups": (_i, [_vp, _i, _l]),
     "pwc_tc_conv_destroy": (None, [_vp]),
     "pwc_debug_halo_trace": (_i, [_vp, _i]),
     "pwc_debug_corr_trace": (_i, [_vp, _i]),

@@ -314,6 +314,8 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   h->halo = 2;
   WmParams& p = h->wp;
   p.ts = ts; p.ntaps = ts ? 1 : 9; p.s_stride = 0; p.s_bytes = 0;
+  p.has_skip = 0; p.out_groups = 1;
+  for (int i = 0; i < 9; ++i) p.skip[i] = 0ull;
   p.N = N; p.H = H; p.W = W; p.dil = dil;
   p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc);
   const int Hd = cdiv(H, dil), Wd = cdiv(W, dil);
@@ -473,6 +475,44 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   if (e) { delete h; return e; }
   h->grid = p.num_tiles < g_num_sms ? p.num_tiles : g_num_sms;
   *handle = h;
+  return 0;
+}
+
+// Zero-block skip list: bit ch of masks[tap] set <=> the packed weight block (tap, 64-channel chunk ch) is all zero, so
+// its TMA load and MMAs are dropped.  Only for the streamed-weights tcgen05 kernel with one tap per stage.
+extern "C" int pwc_tc_conv_set_skip(pwc_tc_conv* h, const unsigned long long* masks) {
+  if (!h || !masks || h->halo != 2) return (int)cudaErrorInvalidValue;
+  pwc::WmParams& p = h->wp;
+  if (p.ts || p.nchunk > 64) return (int)cudaErrorInvalidValue;
+  if (p.w_resident) return 0;                    // whole weight set lives in shared memory: nothing to skip loading
+  p.tps = 1;                                     // one tap per ring stage (uses the first w_stages buffers of the ring)
+  bool any = false;
+  for (int i = 0; i < 9; ++i) { p.skip[i] = masks[i]; any = any || masks[i] != 0ull; }
+  p.has_skip = any ? 1 : 0;
+  return 0;
+}
+
+// Grouped output: the CoutP output channels are g groups of CoutP/g; group i is written to channel
+// out_coff + i*group_pitch of the same pixel (space-to-depth views: group = one of the g pixels of a super-pixel).
+extern "C" int pwc_tc_conv_set_out_groups(pwc_tc_conv* h, int g, long group_pitch) {
+  using namespace pwc;
+  if (!h || h->halo != 2 || g < 2 || g > 8) return (int)cudaErrorInvalidValue;
+  WmParams& p = h->wp;
+  if (!p.tma_store || p.coutp % g || p.out2 || p.dil != 1 || (group_pitch & 7)) return (int)cudaErrorInvalidValue;
+  EncodeTiledFn enc = get_encode_tiled();
+  if (!enc) return (int)cudaErrorNotSupported;
+  const int cg = p.coutp / g;
+  cuuint64_t dims[5] = {(cuuint64_t)cg, (cuuint64_t)g, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
+  cuuint64_t strides[4] = {(cuuint64_t)group_pitch * 2, (cuuint64_t)p.out_pitch * 2, (cuuint64_t)p.out_pitch * 2 * p.W,
+                           (cuuint64_t)p.out_pitch * 2 * p.W * p.H};
+  cuuint32_t box[5] = {(cuuint32_t)cg, (cuuint32_t)g, 8, (cuuint32_t)(p.rows / 2), 1};
+  cuuint32_t es[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5,
+                   reinterpret_cast<__nv_bfloat16*>(p.out) + p.out_coff, dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return (int)cudaErrorInvalidValue;
+  p.out_groups = g;
   return 0;
 }
 

@@ -24,6 +24,8 @@ struct WmParams {
   uint32_t x_bytes_tx, x_bytes, w_bytes_tx, w_bytes, w_stages, w_resident, w_pad, o_bytes, tmem_cols;
   int tma_store;                                  // 16-bit output through a shared-memory staging tile + TMA store
   int fp16, dbg;
+  unsigned long long skip[9];                    // bit ch of skip[tap]: weight block (tap, chunk ch) is all zero -> no load, no MMA
+  int has_skip, out_groups;                       // out_groups g > 1: CoutP = g groups written group_pitch apart (5-D TMA store)
   int ts, ntaps, s_stride;                        // tap-stacked mode (Cout*9 <= 128): M rows = (tap, cout), ONE MMA group per
   uint32_t s_bytes;                               // chunk on the unshifted halo tile, taps summed in the epilogue via smem S
   const float* bias; float slope;
@@ -113,6 +115,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         if (++xb == 2) { xb = 0; xph ^= 1; }
         if (!p.w_resident) {
           for (int tap = 0; tap < p.ntaps; tap += p.tps) {
+            if (p.has_skip && ((p.skip[tap] >> ch) & 1ull)) continue;
             ptx::mbar_wait(w_empty(s), wph ^ 1);
             if (ptx::elect_one()) {
               ptx::mbar_expect_tx(w_full(s), p.w_bytes_tx * p.tps);
@@ -139,17 +142,20 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       ptx::mbar_wait(t_empty(acc), tph ^ 1);
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * (p.ts ? 256 : p.npx));
+      bool first = true;                                   // the first MMA of an item overwrites the accumulator
       for (int ch = 0; ch < p.nchunk; ++ch) {
         ptx::mbar_wait(x_full(xb), xph);
         ptx::tc_fence_after();
         const uint32_t sx = x_base + xb * p.x_bytes;
         const int nkk = min(p.kc, p.cin_span - ch * p.kc + 15) >> 4;     // K=16 steps holding real channels
         const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
+        int ftap = 0;                                        // first tap actually issued for this chunk
+        if (p.has_skip) while (ftap < 8 && ((p.skip[ftap] >> ch) & 1ull)) ++ftap;
         auto issue_tap = [&](uint32_t sw, int tap) {
           const int ky = tap / 3, kx = tap - 3 * ky;
           const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
           const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * 10 + kx) * row_bytes) >> 4);
-          ptx::umma_bf16(d_tmem, dw, dx, idesc, (ch | tap) ? 1u : 0u);
+          ptx::umma_bf16(d_tmem, dw, dx, idesc, (first && tap == ftap) ? 0u : 1u);
           if (nkk > 1) ptx::umma_bf16(d_tmem, dw + 2, dx + 2, idesc, 1u);
           if (nkk > 2) ptx::umma_bf16(d_tmem, dw + 4, dx + 4, idesc, 1u);
           if (nkk > 3) ptx::umma_bf16(d_tmem, dw + 6, dx + 6, idesc, 1u);
@@ -164,6 +170,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           __syncwarp();
         } else {
           for (int tap0 = 0; tap0 < p.ntaps; tap0 += p.tps) {
+            if (p.has_skip && ((p.skip[tap0] >> ch) & 1ull)) continue;
             ptx::mbar_wait(w_full(s), wph);
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
@@ -171,15 +178,17 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
               issue_tap(sw0, tap0);
               if (p.tps == 3) { issue_tap(sw0 + p.w_bytes, tap0 + 1); issue_tap(sw0 + 2 * p.w_bytes, tap0 + 2); }
               ptx::umma_commit(w_empty(s));
-              if (tap0 + p.tps >= p.ntaps) {
-                ptx::umma_commit(x_empty(xb));
-                if (ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
-              }
             }
             __syncwarp();
             if (++s == p.w_stages) { s = 0; wph ^= 1; }
           }
+          if (ptx::elect_one()) {
+            ptx::umma_commit(x_empty(xb));
+            if (ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
+          }
+          __syncwarp();
         }
+        if (!p.has_skip || !((p.skip[ftap] >> ch) & 1ull)) first = false;   // some tap of this chunk was issued
         if (++xb == 2) { xb = 0; xph ^= 1; }
       }
       if (++acc == 2) { acc = 0; tph ^= 1; }
@@ -276,7 +285,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           ptx::fence_proxy_async();                        // generic-proxy smem writes -> visible to the TMA store
           named_bar(2, 128);
           if (issuer) {
-            ptx::tma_store_4d(second ? &tmO2 : &tmO, o_base, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
+            if (p.out_groups > 1)
+              ptx::tma_store_5d(&tmO, o_base, 0, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
+            else
+              ptx::tma_store_4d(second ? &tmO2 : &tmO, o_base, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
             ptx::bulk_commit();
             ptx::bulk_wait_read0();                        // staging tile may be overwritten
           }

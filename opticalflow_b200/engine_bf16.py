@@ -64,6 +64,11 @@ def _stacked(wfn_or_key):
 
 
 TS_MODE = os.environ.get("PWC_TC_TS", "1") != "0"
+S2D_DEC = os.environ.get("PWC_TC_S2D_DEC", "1") != "0"
+# measured (B200, batch 8, 1024x448): the super-pixel form halves the MMA count but streams 4x larger weight tiles per item,
+# so it only pays where items are plentiful (level 2) and the M operand was 3/4 empty (Cout = 32): conv2_4 178 -> 153 us
+S2D_DEC_MAXLVL = int(os.environ.get("PWC_TC_S2D_DEC_MAXLVL", "2"))
+S2D_DEC_MAXCOUT = int(os.environ.get("PWC_TC_S2D_DEC_MAXCOUT", "32"))
 
 
 def _pfup_weights(lvl):
@@ -93,7 +98,7 @@ def _pfup_weights(lvl):
 
 
 class _TcLayer:
-    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows")
+    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups")
 
 
 class PlanBF16:
@@ -142,7 +147,7 @@ class PlanBF16:
     # ------------------------------------------------------------------ layer construction
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
-            flops=None, ts=False):
+            flops=None, ts=False, groups=None):
         L = _TcLayer()
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
         L.wfn = _stacked(wfn if wfn is not None else key) if ts else wfn
@@ -161,6 +166,9 @@ class PlanBF16:
             _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32) | (16 if ts else 0),
             _lib.ptr(residual), (residual.shape[-1] if residual is not None else 0), N, hin, win, stride, dil, slope)
         _lib.check(e, f"pwc_tc_conv_create {key}")
+        L.groups = groups
+        if groups is not None and groups[1] != L.coutp // groups[0]:
+            _lib.check(self.lib.pwc_tc_conv_set_out_groups(h, groups[0], groups[1]), f"set_out_groups {key}")
         L.handle = h
         self.layers[key] = L
         lib = self.lib
@@ -244,7 +252,18 @@ class PlanBF16:
             self._corr(l)
             for k in range(5):
                 cm = chan_map(l, DEC_START[k])
-                self._tc(f"conv{l}_{k}.0", len(cm), [128, 128, 96, 64, 32][k], cat, DEC_START[k], wd - DEC_START[k], cat,
+                cout = [128, 128, 96, 64, 32][k]
+                g = 128 // cout
+                if S2D_DEC and cout <= S2D_DEC_MAXCOUT and l <= S2D_DEC_MAXLVL and w % g == 0:
+                    # Cout = 64 / 32: g adjacent pixels form one super-pixel so that all 128 MMA rows carry outputs
+                    # (weight block-structured as in _s2d_weights; all-zero (tap, chunk) blocks are skipped)
+                    v = cat.view(B, h, w // g, g * wd)
+                    cm2 = [dxp * wd + DEC_START[k] + c for dxp in range(g) for c in cm]
+                    self._tc(f"conv{l}_{k}.0", g * len(cm), g * cout, v, 0, g * wd, v, DEC_WRITE[k], B, h, w // g, cmap=cm2,
+                             wfn=_s2d_weights(f"conv{l}_{k}.0", g), flops=2.0 * B * h * w * cout * len(cm) * 9,
+                             groups=(g, wd))
+                    continue
+                self._tc(f"conv{l}_{k}.0", len(cm), cout, cat, DEC_START[k], wd - DEC_START[k], cat,
                          DEC_WRITE[k], B, h, w, cmap=cm)
             cm = chan_map(l, 0)
             if l > 2:
@@ -260,7 +279,13 @@ class PlanBF16:
         cm = chan_map(2, 0)
         src, cin, span, cmap = self.cat[2], len(cm), concat_width(2), cm
         for i, (name, cout, dil) in enumerate(DC):
-            self._tc(name + ".0", cin, cout, src, 0, span, self.dc[i], 0, B, h, w, dil=dil, cmap=cmap)
+            g = 128 // cout if cout <= S2D_DEC_MAXCOUT else 1
+            if S2D_DEC and g > 1 and dil == 1 and cmap is None and w % g == 0 and src.shape[-1] == span:
+                vi, vo = src.view(B, h, w // g, g * span), self.dc[i].view(B, h, w // g, g * cout)
+                self._tc(name + ".0", g * cin, g * cout, vi, 0, g * span, vo, 0, B, h, w // g,
+                         wfn=_s2d_weights(name + ".0", g), flops=2.0 * B * h * w * cout * cin * 9, groups=(g, cout))
+            else:
+                self._tc(name + ".0", cin, cout, src, 0, span, self.dc[i], 0, B, h, w, dil=dil, cmap=cmap)
             src, cin, span, cmap = self.dc[i], cout, cout, None
         self._tc("dc_conv7", 32, 2, src, 0, 32, self.flow_out4, 0, B, h, w, slope=1.0, out_f32=True, residual=self.flow[2],
                  ts=True)
@@ -290,6 +315,20 @@ class PlanBF16:
             _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.wrows, L.cin, L.span, L.kc,
                                                      L.coutp, st), f"pack {key}")
             L.b.copy_(bs)
+            if L.groups is not None:
+                # zero-block skip list of the block-structured space-to-depth weight: (tap, 64-channel chunk) pairs
+                nchunk = (L.span + L.kc - 1) // L.kc
+                cm = torch.tensor(L.cmap, device=dev, dtype=torch.long) if L.cmap is not None else torch.arange(L.cin, device=dev)
+                masks = (ctypes.c_ulonglong * 9)()
+                for tap in range(9):
+                    nz = (wt[:, :, tap // 3, tap % 3] != 0).any(0)
+                    used = torch.zeros(nchunk, dtype=torch.bool, device=dev)
+                    used[(cm[nz] // L.kc).unique()] = True
+                    m = 0
+                    for ch in (~used).nonzero().flatten().tolist():
+                        m |= 1 << ch
+                    masks[tap] = m
+                _lib.check(lib.pwc_tc_conv_set_skip(L.handle, masks), f"set_skip {key}")
         for key, (w, b, cin, cinp) in self.small.items():
             wt = sd[key + ".weight"]
             mp = None
