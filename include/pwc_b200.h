@@ -158,13 +158,17 @@ int pwc_tc_conv_launch(const pwc_tc_conv* handle, void* stream);
  * of a dense NHWC buffer are one super-pixel, so all 128 MMA rows carry outputs):
  *   set_skip       : bit ch of masks[tap] (tap = 3*ky + kx, 9 entries) set <=> the packed weight block of that tap and
  *                    64-channel chunk ch is all zero; its TMA load and MMAs are dropped.
- *   set_out_groups : the CoutP output channels are g groups of CoutP/g; group i goes to channel out_coff + i*group_pitch. */
+ *   set_out_groups : the CoutP output channels are g groups of CoutP/g; group i goes to channel out_coff + i*group_pitch.
+ *   set_kk_skip    : single-chunk layers (Cin span <= 64): bit kk (0..3) of masks[tap] set <=> the 16-channel K step kk of
+ *                    that tap's weight tile is all zero; its MMA is dropped. */
 int pwc_tc_conv_set_skip(pwc_tc_conv* handle, const unsigned long long* masks);
+int pwc_tc_conv_set_kk_skip(pwc_tc_conv* handle, const int* masks);
 int pwc_tc_conv_set_out_groups(pwc_tc_conv* handle, int g, long group_pitch);
 void pwc_tc_conv_destroy(pwc_tc_conv* handle);
 /* debug aid: timeline of CTA 0 of the halo kernel (enabled by env PWC_TC_HALO_BO bit 16); host memory destination */
 int pwc_debug_halo_trace(unsigned long long* host_dst, int count);
 int pwc_debug_corr_trace(unsigned long long* host_dst, int count);
+int pwc_debug_wm_trace(unsigned long long* host_dst, int count);   /* PWC_TC_HALO_BO bit 5 (32) enables the marks */
 int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, const int* chan_map,
                               int Cout, int Cin, int cin_span, int kc, int coutp, void* stream);
 

@@ -30,10 +30,12 @@ SIGNATURES = {
                                 _vp, _l, _i, _vp, _l, _i, _i, _vp, _l, _i, _i, _i, _i, _i, _f]),
     "pwc_tc_conv_launch": (_i, [_vp, _vp]),
     "pwc_tc_conv_set_skip": (_i, [_vp, _vp]),
+    "pwc_tc_conv_set_kk_skip": (_i, [_vp, _vp]),
     "pwc_tc_conv_set_out_groups": (_i, [_vp, _i, _l]),
     "pwc_tc_conv_destroy": (None, [_vp]),
     "pwc_debug_halo_trace": (_i, [_vp, _i]),
     "pwc_debug_corr_trace": (_i, [_vp, _i]),
+    "pwc_debug_wm_trace": (_i, [_vp, _i]),
     "pwc_pack_conv_weight_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "pwc_conv1a_bf16_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "pwc_deconv4x4s2_c2_fwd": (_i, [_vp, _i, _l, _i, _i, _vp, _vp, _vp, _i, _l, _i, _vp, _l, _i, _i, _i, _vp]),

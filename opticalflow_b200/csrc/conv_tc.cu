@@ -314,7 +314,8 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   h->halo = 2;
   WmParams& p = h->wp;
   p.ts = ts; p.ntaps = ts ? 1 : 9; p.s_stride = 0; p.s_bytes = 0;
-  p.has_skip = 0; p.out_groups = 1;
+  p.has_skip = 0; p.out_groups = 1; p.has_kk = 0; p.kk_first_tap = 0; p.kk_first_kk = 0;
+  for (int i = 0; i < 9; ++i) p.kk_mask[i] = 0;
   for (int i = 0; i < 9; ++i) p.skip[i] = 0ull;
   p.N = N; p.H = H; p.W = W; p.dil = dil;
   p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc);
@@ -350,13 +351,35 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.cin_span = cin_span;
   p.w_bytes_tx = (uint32_t)coutp * row_bytes;
   p.tma_store = (!out_f32 && !ts && env_int("PWC_TC_WM_TMASTORE", 1)) ? 1 : 0;
-  p.o_bytes = p.tma_store ? (((uint32_t)(rows / 2) * 8u * coutp * 2u + 1023u) & ~1023u) : 0u;
-  // weight-tile replication on M (epilogue parallelism for thin layers): only when the whole weight set stays resident
+  p.o_half = p.tma_store ? (((uint32_t)(rows / 2) * 8u * coutp * 2u + 1023u) & ~1023u) : 0u;
+  // second staging buffer (store of one half overlaps the fill of the next) while it leaves >= 4 weight stages
+  p.o_nbuf = (p.tma_store && env_int("PWC_TC_WM_OBUF2", 1) &&
+              2u * p.x_bytes + 2u * p.o_half + 4u * 128u * row_bytes <= 200u * 1024u) ? 2 : 1;
+  p.o_bytes = p.o_half * (uint32_t)p.o_nbuf;
+  // weight-tile replication on M (epilogue parallelism for thin layers): only when the whole weight set stays resident.
+  // per-warp output stores (no CTA-wide barrier in the epilogue) need 32-channel groups and rows divisible by the parts;
+  // their staging size depends on the replication factor, so both are chosen together.
   p.cg = cdiv(out_f32 ? cout : coutp, 32); p.rep = 1;
   const uint32_t full_tile = 128u * row_bytes;
-  const uint32_t budget_rep = 216u * 1024u - 2u * p.x_bytes - p.o_bytes;
-  if (p.tma_store && 4 / p.cg >= 2 && 9u * p.nchunk * full_tile <= budget_rep && env_int("PWC_TC_WM_REP", 1) &&
-      env_int("PWC_TC_HALO_RESIDENT", 1)) p.rep = 4 / p.cg;
+  const bool ws_ok = p.tma_store && coutp % 32 == 0 && env_int("PWC_TC_WM_WSTORE", 1);
+  const bool rep_ok = p.tma_store && env_int("PWC_TC_WM_REP", 1) && env_int("PWC_TC_HALO_RESIDENT", 1);
+  p.wstore = 0; p.o_rs = 0;
+  for (int rep = rep_ok ? 4 / p.cg : 1; rep >= 1; rep >>= 1) {
+    if (rep < 1) break;
+    if (ws_ok && rows % rep) continue;
+    uint32_t o_bytes = p.o_bytes, o_half = p.o_half; int rs = 0;
+    if (ws_ok) {
+      const int R = rows / rep;
+      rs = R < 8 ? R : 8;
+      while (R % rs) --rs;
+      o_half = (uint32_t)rs * 8u * 64u;                      // one staging buffer of one warp
+      o_bytes = 4u * 2u * o_half;
+    }
+    if (rep > 1 && 9u * p.nchunk * full_tile > 216u * 1024u - 2u * p.x_bytes - o_bytes) continue;
+    p.rep = rep;
+    if (ws_ok) { p.wstore = 1; p.o_rs = rs; p.o_half = o_half; p.o_nbuf = 2; p.o_bytes = o_bytes; }
+    break;
+  }
   p.w_bytes = p.rep > 1 ? full_tile : ((p.w_bytes_tx + 1023u) & ~1023u);
   p.w_pad = full_tile > p.w_bytes ? full_tile - p.w_bytes : 0u;
   const uint32_t budget = 216u * 1024u - 2u * p.x_bytes - p.w_pad - p.o_bytes - p.s_bytes;
@@ -388,10 +411,11 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     // output slice as a 4-D tensor (CoutP, W, H, images); box = half an item; dilation = element strides; no swizzle
     if ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7)))) e = (int)cudaErrorInvalidValue;
     const int n1 = out2 ? p.n_split : N;
+    const int bc = p.wstore ? 32 : coutp, br = p.wstore ? p.o_rs : rows / 2;
     if (!e) e = make_tmap_nhwc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out) + out_coff,
-                               out_pitch, coutp, W, H, n1, coutp, 8 * dil, (rows / 2) * dil, dil, dil, CU_TENSOR_MAP_SWIZZLE_NONE);
+                               out_pitch, coutp, W, H, n1, bc, 8 * dil, br * dil, dil, dil, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (!e && out2) e = make_tmap_nhwc(&h->tmO2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out2) + out2_coff,
-                                       out2_pitch, coutp, W, H, N - n1, coutp, 8 * dil, (rows / 2) * dil, dil, dil,
+                                       out2_pitch, coutp, W, H, N - n1, bc, 8 * dil, br * dil, dil, dil,
                                        CU_TENSOR_MAP_SWIZZLE_NONE);
   }
   if (e || h->smem_bytes > 227u * 1024u || cols > 512) { delete h; return e ? e : (int)cudaErrorInvalidValue; }
@@ -492,6 +516,26 @@ extern "C" int pwc_tc_conv_set_skip(pwc_tc_conv* h, const unsigned long long* ma
   return 0;
 }
 
+// Single-chunk layers (Cin span <= 64): bit kk (0..3) of masks[tap] set <=> the 16-channel K step kk of that tap's weight
+// tile is all zero, so its MMA is dropped (block structure of space-to-depth weights).
+extern "C" int pwc_tc_conv_set_kk_skip(pwc_tc_conv* h, const int* masks) {
+  if (!h || !masks || h->halo != 2) return (int)cudaErrorInvalidValue;
+  pwc::WmParams& p = h->wp;
+  if (p.nchunk != 1 || p.ts || p.has_skip) return (int)cudaErrorInvalidValue;
+  const int nkk = (p.cin_span + 15) / 16 < 4 ? (p.cin_span + 15) / 16 : 4;
+  int ft = -1, fk = -1, any = 0;
+  for (int t = 0; t < 9; ++t) {
+    p.kk_mask[t] = masks[t] & 15;
+    any |= p.kk_mask[t];
+    for (int kk = 0; kk < nkk && ft < 0; ++kk)
+      if (!((p.kk_mask[t] >> kk) & 1)) { ft = t; fk = kk; }
+  }
+  if (ft < 0) return (int)cudaErrorInvalidValue;      // every step skipped: the accumulator would never be written
+  p.kk_first_tap = ft; p.kk_first_kk = fk;
+  p.has_kk = any ? 1 : 0;
+  return 0;
+}
+
 // Grouped output: the CoutP output channels are g groups of CoutP/g; group i is written to channel
 // out_coff + i*group_pitch of the same pixel (space-to-depth views: group = one of the g pixels of a super-pixel).
 extern "C" int pwc_tc_conv_set_out_groups(pwc_tc_conv* h, int g, long group_pitch) {
@@ -506,6 +550,8 @@ extern "C" int pwc_tc_conv_set_out_groups(pwc_tc_conv* h, int g, long group_pitc
   cuuint64_t strides[4] = {(cuuint64_t)group_pitch * 2, (cuuint64_t)p.out_pitch * 2, (cuuint64_t)p.out_pitch * 2 * p.W,
                            (cuuint64_t)p.out_pitch * 2 * p.W * p.H};
   cuuint32_t box[5] = {(cuuint32_t)cg, (cuuint32_t)g, 8, (cuuint32_t)(p.rows / 2), 1};
+  if (p.wstore) { box[0] = 32; box[1] = 1; box[3] = (cuuint32_t)p.o_rs; }
+  if (p.wstore && cg % 32) return (int)cudaErrorInvalidValue;
   cuuint32_t es[5] = {1, 1, 1, 1, 1};
   CUresult r = enc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5,
                    reinterpret_cast<__nv_bfloat16*>(p.out) + p.out_coff, dims, strides, box, es,
@@ -544,6 +590,11 @@ extern "C" int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, c
 }
 
 // Debug: copy the halo kernel's timeline buffer (see conv_tc_halo.cuh) to host memory; returns a cudaError.
+extern "C" int pwc_debug_wm_trace(unsigned long long* host_dst, int count) {
+  if (!host_dst || count < 0 || count > 3 * 64 * 4) return (int)cudaErrorInvalidValue;
+  return (int)cudaMemcpyFromSymbol(host_dst, pwc::g_wm_trace, sizeof(unsigned long long) * count);
+}
+
 extern "C" int pwc_debug_halo_trace(unsigned long long* host_dst, int count) {
   if (count > 8192) count = 8192;
   return (int)cudaMemcpyFromSymbol(host_dst, pwc::g_halo_trace, sizeof(unsigned long long) * count);

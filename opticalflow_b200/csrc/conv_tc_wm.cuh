@@ -23,8 +23,12 @@ struct WmParams {
   int tiles_x, tiles_y, tiles_per_img, num_items;
   uint32_t x_bytes_tx, x_bytes, w_bytes_tx, w_bytes, w_stages, w_resident, w_pad, o_bytes, tmem_cols;
   int tma_store;                                  // 16-bit output through a shared-memory staging tile + TMA store
+  int o_nbuf; uint32_t o_half;                    // staging buffers (1 | 2) of o_half bytes each
+  int wstore, o_rs;                               // per-warp stores: every epilogue warp owns 2 buffers of o_rs rows x 8 px x 32 ch
   int fp16, dbg;
   unsigned long long skip[9];                    // bit ch of skip[tap]: weight block (tap, chunk ch) is all zero -> no load, no MMA
+  int has_kk, kk_mask[9], kk_first_tap, kk_first_kk;   // single-chunk layers: bit kk of kk_mask[tap] set <=> the K=16 step kk of
+                                                  // tap's weight tile is all zero (space-to-depth block structure) -> no MMA
   int has_skip, out_groups;                       // out_groups g > 1: CoutP = g groups written group_pitch apart (5-D TMA store)
   int ts, ntaps, s_stride;                        // tap-stacked mode (Cout*9 <= 128): M rows = (tap, cout), ONE MMA group per
   uint32_t s_bytes;                               // chunk on the unshifted halo tile, taps summed in the epilogue via smem S
@@ -34,6 +38,12 @@ struct WmParams {
   int out_f32;
   const float* residual; long res_pitch;
 };
+
+// debug timeline of CTA 0 (PWC_TC_HALO_BO bit 5): [role 0 producer | 1 mma | 2 epilogue][item index][4 marks]
+__device__ unsigned long long g_wm_trace[3 * 64 * 4];
+__device__ __forceinline__ void wm_mark(bool on, int role, int idx, int k) {
+  if (on && idx < 64) g_wm_trace[(role * 64 + idx) * 4 + k] = clock64();
+}
 
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -105,8 +115,12 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       int n, ry, rx, ty0, tx0;
       decode(item, n, ry, rx, ty0, tx0);
       const int ya = ry + d * (ty0 - 1), xa = rx + d * (tx0 - 1);
+      const bool trp = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
+      const int it_idx = (item - (int)blockIdx.x) / (int)gridDim.x;
       for (int ch = 0; ch < p.nchunk; ++ch) {
+        if (ch == 0) wm_mark(trp, 0, it_idx, 0);
         ptx::mbar_wait(x_empty(xb), xph ^ 1);
+        if (ch == 0) wm_mark(trp, 0, it_idx, 1);
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
           ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, xa, ya, n);
@@ -139,13 +153,18 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     int acc = 0; uint32_t tph = 0;
     if (p.w_resident) ptx::mbar_wait(w_all, 0);
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      const bool trm = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
+      const int it_idx = (item - (int)blockIdx.x) / (int)gridDim.x;
+      wm_mark(trm, 1, it_idx, 0);
       ptx::mbar_wait(t_empty(acc), tph ^ 1);
       ptx::tc_fence_after();
+      wm_mark(trm, 1, it_idx, 1);
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * (p.ts ? 256 : p.npx));
       bool first = true;                                   // the first MMA of an item overwrites the accumulator
       for (int ch = 0; ch < p.nchunk; ++ch) {
         ptx::mbar_wait(x_full(xb), xph);
         ptx::tc_fence_after();
+        if (ch == 0) wm_mark(trm, 1, it_idx, 2);
         const uint32_t sx = x_base + xb * p.x_bytes;
         const int nkk = min(p.kc, p.cin_span - ch * p.kc + 15) >> 4;     // K=16 steps holding real channels
         const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
@@ -155,6 +174,14 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           const int ky = tap / 3, kx = tap - 3 * ky;
           const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
           const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * 10 + kx) * row_bytes) >> 4);
+          if (p.has_kk) {
+            const int km = p.kk_mask[tap];
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              if (kk < nkk && !((km >> kk) & 1))
+                ptx::umma_bf16(d_tmem, dw + 2 * kk, dx + 2 * kk, idesc, (tap == p.kk_first_tap && kk == p.kk_first_kk) ? 0u : 1u);
+            return;
+          }
           ptx::umma_bf16(d_tmem, dw, dx, idesc, (first && tap == ftap) ? 0u : 1u);
           if (nkk > 1) ptx::umma_bf16(d_tmem, dw + 2, dx + 2, idesc, 1u);
           if (nkk > 2) ptx::umma_bf16(d_tmem, dw + 4, dx + 4, idesc, 1u);
@@ -188,6 +215,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           }
           __syncwarp();
         }
+        if (ch == p.nchunk - 1) wm_mark(trm, 1, it_idx, 3);
         if (!p.has_skip || !((p.skip[ftap] >> ch) & 1ull)) first = false;   // some tap of this chunk was issued
         if (++xb == 2) { xb = 0; xph ^= 1; }
       }
@@ -203,14 +231,19 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     const float bias = (co < p.cout) ? __ldg(p.bias + co) : 0.f;
     uint8_t* o_gen = smem_raw + (o_base - ptx::smem_addr(smem_raw));
     const bool issuer = (threadIdx.x == 64);
+    int obuf = 0, wbuf = 0;
     int acc = 0; uint32_t tph = 0;
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
       int n, ry, rx, ty0, tx0;
       decode(item, n, ry, rx, ty0, tx0);
       const bool second = (n >= p.n_split) && (p.out2 != nullptr) && (p.out_f32 != 2);
       const int nn = second ? n - p.n_split : n;
+      const bool tre = (p.dbg & 32) && blockIdx.x == 0 && threadIdx.x == 64;
+      const int it_idx = (item - (int)blockIdx.x) / (int)gridDim.x;
+      wm_mark(tre, 2, it_idx, 0);
       ptx::mbar_wait(t_full(acc), tph);
       ptx::tc_fence_after();
+      wm_mark(tre, 2, it_idx, 1);
       const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * (p.ts ? 256 : p.npx));
       if (p.ts) {
         // ---- tap-stacked: TMEM lane m = tap*cout + co holds that tap's partial sums over the whole halo tile ----
@@ -259,11 +292,57 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         if (++acc == 2) { acc = 0; tph ^= 1; }
         continue;
       }
-      if (p.tma_store) {
+      if (p.wstore) {
+        // ---- per-warp stores: warp (channel group gc, pixel part) stages [o_rs rows x 8 px][32 ch] and issues its own
+        //      TMA store (box 32 ch x 8 px x o_rs rows); no CTA-wide barrier, two staging buffers per warp ----
+        if (warp_live) {
+          const int gc = lg - part * p.cg;                   // 32-channel group of this warp
+          const int R = p.rows / p.rep;                      // tile rows of this warp's part
+          const uint32_t my_o = o_base + (uint32_t)lg * 2u * p.o_half;
+          int c0g = gc * 32, grp = 0;
+          if (p.out_groups > 1) { const int cgp = p.coutp / p.out_groups; grp = c0g / cgp; c0g -= grp * cgp; }
+          for (int r0 = 0; r0 < R; r0 += p.o_rs) {
+            const uint32_t so = my_o + (uint32_t)wbuf * p.o_half;
+            if (lane == 0) ptx::bulk_wait_read1();           // the store issued two steps ago has released this buffer
+            __syncwarp();
+            uint16_t* st = reinterpret_cast<uint16_t*>(smem_raw + (so - ptx::smem_addr(smem_raw))) + lane;
+            const int col0 = (part * R + r0) * 8, ncol = p.o_rs * 8;
+            for (int c0 = 0; c0 < ncol; c0 += 16) {
+              uint32_t v[16];
+              ptx::tmem_ld16(taddr + col0 + c0, v);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const float val = lrelu(__uint_as_float(v[i]) + bias, p.slope);
+                uint16_t bits;
+                if (p.fp16) { __half hv = __float2half_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
+                else { __nv_bfloat16 hv = __float2bfloat16_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
+                if (c0 + i < ncol) st[(c0 + i) * 32] = bits;
+              }
+            }
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              const int oy = ry + d * (ty0 + part * R + r0), ox = rx + d * tx0;
+              if (p.out_groups > 1) ptx::tma_store_5d(&tmO, so, c0g, grp, ox, oy, nn);
+              else ptx::tma_store_4d(second ? &tmO2 : &tmO, so, c0g, ox, oy, nn);
+              ptx::bulk_commit();
+            }
+            wbuf ^= 1;
+          }
+        }
+        wm_mark(tre, 2, it_idx, 3);
+      } else if (p.tma_store) {
         const int hpx = p.npx >> 1;                        // pixels per half item (rows/2 tile rows)
         for (int half = 0; half < 2; ++half) {
+          // two staging buffers: the TMA store of the previous half keeps reading its buffer while this one is filled
+          const uint32_t ooff = (p.o_nbuf == 2) ? (uint32_t)obuf * p.o_half : 0u;
+          if (p.o_nbuf == 2) {
+            if (issuer) ptx::bulk_wait_read1();            // the store issued two halves ago has released this buffer
+            named_bar(2, 128);
+          }
           if (warp_live) {
-            uint16_t* st = reinterpret_cast<uint16_t*>(o_gen) + co;
+            uint16_t* st = reinterpret_cast<uint16_t*>(o_gen + ooff) + co;
             const int ppx = ((hpx / p.rep) + 7) & ~7;         // pixels per part
             const int cend = min(hpx, (part + 1) * ppx);
             for (int c0 = part * ppx; c0 < cend; c0 += 16) {
@@ -286,13 +365,15 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           named_bar(2, 128);
           if (issuer) {
             if (p.out_groups > 1)
-              ptx::tma_store_5d(&tmO, o_base, 0, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
+              ptx::tma_store_5d(&tmO, o_base + ooff, 0, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
             else
-              ptx::tma_store_4d(second ? &tmO2 : &tmO, o_base, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
+              ptx::tma_store_4d(second ? &tmO2 : &tmO, o_base + ooff, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
             ptx::bulk_commit();
-            ptx::bulk_wait_read0();                        // staging tile may be overwritten
+            if (p.o_nbuf != 2) ptx::bulk_wait_read0();     // single staging tile: wait until it may be overwritten
           }
-          named_bar(2, 128);
+          if (p.o_nbuf != 2) named_bar(2, 128);
+          obuf ^= 1;
+          wm_mark(tre, 2, it_idx, 2 + half);
         }
       } else if (warp_live) {
         for (int c0 = 0; c0 < p.npx; c0 += 16) {           // 16 pixels = 2 tile rows of 8
@@ -332,7 +413,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       if (lane == 0) ptx::mbar_arrive(t_empty(acc));
       if (++acc == 2) { acc = 0; tph ^= 1; }
     }
-    if (issuer) ptx::bulk_wait0();
+    if (issuer || (p.wstore && lane == 0)) ptx::bulk_wait0();
   }
   ptx::tc_fence_before();
   __syncthreads();

@@ -9,10 +9,13 @@
 
 namespace pwc {
 
-__global__ void __launch_bounds__(256) conv1a_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
+// conv1a (3 -> 16, stride 2, PWCNet.py:52) straight from the fp32 NCHW driver tensor, fused with the im1/im2 split.
+// One thread = 4 adjacent output pixels x 16 channels: every broadcast weight read (LDS.128) feeds 16 FMAs, the 9 input
+// columns of a row are loaded once for the 4 pixels.
+__global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                           const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
                                                           int B, int H, int W, float slope) {
-  __shared__ float ws[27][16];
+  __shared__ __align__(16) float ws[27][16];
   __shared__ float bs[16];
   for (int e = threadIdx.x; e < 432; e += blockDim.x) {       // torch [16][3][3][3] -> [ci*9+tap][co]
     const int co = e / 27, r = e - co * 27;
@@ -20,41 +23,64 @@ __global__ void __launch_bounds__(256) conv1a_bf16_kernel(const float* __restric
   }
   if (threadIdx.x < 16) bs[threadIdx.x] = bias[threadIdx.x];
   __syncthreads();
-  const int Ho = H >> 1, Wo = W >> 1;
+  const int Ho = H >> 1, Wo = W >> 1, Wq = (Wo + 3) >> 2;
   const long hw = (long)H * W;
-  const long total = 2L * B * Ho * Wo;
+  const long total = 2L * B * Ho * Wq;
   for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
-    const int ox = e % Wo; const long t = e / Wo;
+    const int qx = e % Wq; const long t = e / Wq;
     const int oy = t % Ho; const int img = t / Ho;
     const int b = img % B, half = img / B;
     const float* src = x + ((long)b * 6 + half * 3) * hw;
-    float acc[16];
+    const int ox0 = 4 * qx, ix0 = 2 * ox0 - 1;
+    float acc[4][16];
 #pragma unroll
-    for (int co = 0; co < 16; ++co) acc[co] = bs[co];
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+      for (int co = 0; co < 16; ++co) acc[p][co] = bs[co];
 #pragma unroll
     for (int ci = 0; ci < 3; ++ci)
 #pragma unroll
       for (int ky = 0; ky < 3; ++ky) {
         const int iy = 2 * oy - 1 + ky;
+        const bool yok = (iy >= 0 && iy < H);
+        const float* row = src + ci * hw + (long)iy * W;
+        float v[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) {
+          const int ix = ix0 + i;
+          v[i] = (yok && ix >= 0 && ix < W) ? __ldg(row + ix) : 0.f;
+        }
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
-          const int ix = 2 * ox - 1 + kx;
-          float v = 0.f;
-          if (iy >= 0 && iy < H && ix >= 0 && ix < W) v = __ldg(src + ci * hw + (long)iy * W + ix);
-          const float* wr = ws[ci * 9 + ky * 3 + kx];
+          const float4* wr = reinterpret_cast<const float4*>(ws[ci * 9 + ky * 3 + kx]);
 #pragma unroll
-          for (int co = 0; co < 16; ++co) acc[co] = fmaf(v, wr[co], acc[co]);
+          for (int c4 = 0; c4 < 4; ++c4) {
+            const float4 wv = wr[c4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+              const float a = v[2 * p + kx];
+              acc[p][4 * c4 + 0] = fmaf(a, wv.x, acc[p][4 * c4 + 0]);
+              acc[p][4 * c4 + 1] = fmaf(a, wv.y, acc[p][4 * c4 + 1]);
+              acc[p][4 * c4 + 2] = fmaf(a, wv.z, acc[p][4 * c4 + 2]);
+              acc[p][4 * c4 + 3] = fmaf(a, wv.w, acc[p][4 * c4 + 3]);
+            }
+          }
         }
       }
-    uint32_t pk[8];
+    __nv_bfloat16* orow = out + (((long)img * Ho + oy) * Wo + ox0) * 16;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      __nv_bfloat162 h = __floats2bfloat162_rn(lrelu(acc[2 * i], slope), lrelu(acc[2 * i + 1], slope));
-      pk[i] = *reinterpret_cast<uint32_t*>(&h);
+    for (int p = 0; p < 4; ++p) {
+      if (ox0 + p >= Wo) break;
+      uint32_t pk[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(lrelu(acc[p][2 * i], slope), lrelu(acc[p][2 * i + 1], slope));
+        pk[i] = *reinterpret_cast<uint32_t*>(&h);
+      }
+      uint4* o = reinterpret_cast<uint4*>(orow + p * 16);
+      o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
     }
-    uint4* o = reinterpret_cast<uint4*>(out + e * 16);
-    o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-    o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
   }
 }
 

@@ -98,7 +98,7 @@ def _pfup_weights(lvl):
 
 
 class _TcLayer:
-    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups")
+    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups", "kkskip")
 
 
 class PlanBF16:
@@ -147,8 +147,9 @@ class PlanBF16:
     # ------------------------------------------------------------------ layer construction
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
-            flops=None, ts=False, groups=None):
+            flops=None, ts=False, groups=None, kkskip=False):
         L = _TcLayer()
+        L.kkskip = bool(kkskip and span <= 64 and cmap is None)
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
         L.wfn = _stacked(wfn if wfn is not None else key) if ts else wfn
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
@@ -233,12 +234,12 @@ class PlanBF16:
             vb = self.pb[l].view(2 * B, h, w // g, g * PYR_CP[l]) if g > 1 else self.pb[l]
             if g > 1:
                 self._tc(names[1] + ".0", g * C, g * C, va, 0, g * C, vb, 0, 2 * B, h, w // g,
-                         wfn=_s2d_weights(names[1] + ".0", g), flops=fl)
+                         wfn=_s2d_weights(names[1] + ".0", g), flops=fl, kkskip=True)
             else:
                 self._tc(names[1] + ".0", C, C, self.pa[l], 0, PYR_CP[l], self.pb[l], 0, 2 * B, h, w)
             if l == 1:
                 self._tc(names[2] + ".0", g * C, g * C, vb, 0, g * C, va, 0, 2 * B, h, w // g,
-                         wfn=_s2d_weights(names[2] + ".0", g), flops=fl)
+                         wfn=_s2d_weights(names[2] + ".0", g), flops=fl, kkskip=True)
             elif l < 6:
                 self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.cat[l], C1_OFF, 2 * B, h, w,
                          dst2=self.f2[l], n_split=B)
@@ -315,6 +316,15 @@ class PlanBF16:
             _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.wrows, L.cin, L.span, L.kc,
                                                      L.coutp, st), f"pack {key}")
             L.b.copy_(bs)
+            if L.kkskip:
+                # single-chunk space-to-depth layer: all-zero 16-channel K steps of each tap's weight tile are not issued
+                km = (ctypes.c_int * 9)()
+                for tap in range(9):
+                    blk = wt[:, :, tap // 3, tap % 3]
+                    for kk in range((L.span + 15) // 16):
+                        if not bool((blk[:, 16 * kk:16 * kk + 16] != 0).any()):
+                            km[tap] |= 1 << kk
+                _lib.check(lib.pwc_tc_conv_set_kk_skip(L.handle, km), f"set_kk_skip {key}")
             if L.groups is not None:
                 # zero-block skip list of the block-structured space-to-depth weight: (tap, 64-channel chunk) pairs
                 nchunk = (L.span + L.kc - 1) // L.kc
