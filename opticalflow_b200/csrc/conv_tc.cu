@@ -361,21 +361,32 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   // their staging size depends on the replication factor, so both are chosen together.
   p.cg = cdiv(out_f32 ? cout : coutp, 32); p.rep = 1;
   const uint32_t full_tile = 128u * row_bytes;
-  const bool ws_ok = p.tma_store && coutp % 32 == 0 && env_int("PWC_TC_WM_WSTORE", 1);
+  const bool ws_ok = p.tma_store && coutp % 32 == 0 && slope >= 0.f && slope <= 1.f && env_int("PWC_TC_WM_WSTORE", 1);
   const bool rep_ok = p.tma_store && env_int("PWC_TC_WM_REP", 1) && env_int("PWC_TC_HALO_RESIDENT", 1);
   p.wstore = 0; p.o_rs = 0;
   for (int rep = rep_ok ? 4 / p.cg : 1; rep >= 1; rep >>= 1) {
     if (rep < 1) break;
     if (ws_ok && rows % rep) continue;
     uint32_t o_bytes = p.o_bytes, o_half = p.o_half; int rs = 0;
+    bool fits = (rep == 1);
     if (ws_ok) {
       const int R = rows / rep;
-      rs = R < 8 ? R : 8;
-      while (R % rs) --rs;
-      o_half = (uint32_t)rs * 8u * 64u;                      // one staging buffer of one warp
-      o_bytes = 4u * 2u * o_half;
+      for (int cap = 8; cap >= 2 && !fits; cap >>= 1) {       // smaller staging steps if that lets the replicas stay resident
+        rs = R < cap ? R : cap;
+        while (R % rs) --rs;
+        o_half = (uint32_t)rs * 8u * 64u;                    // one staging buffer of one warp
+        o_bytes = 4u * 2u * o_half;
+        fits = 9u * p.nchunk * full_tile <= 216u * 1024u - 2u * p.x_bytes - o_bytes;
+      }
+      if (rep == 1) {
+        rs = R < 8 ? R : 8;
+        while (R % rs) --rs;
+        o_half = (uint32_t)rs * 8u * 64u; o_bytes = 4u * 2u * o_half;
+      }
+    } else if (rep > 1) {
+      fits = 9u * p.nchunk * full_tile <= 216u * 1024u - 2u * p.x_bytes - o_bytes;
     }
-    if (rep > 1 && 9u * p.nchunk * full_tile > 216u * 1024u - 2u * p.x_bytes - o_bytes) continue;
+    if (!fits) continue;
     p.rep = rep;
     if (ws_ok) { p.wstore = 1; p.o_rs = rs; p.o_half = o_half; p.o_nbuf = 2; p.o_bytes = o_bytes; }
     break;
@@ -444,7 +455,8 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
     if (g_num_sms <= 0) g_num_sms = 148;
     cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_wm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_wm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_wm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   }
   if (halo_eligible(stride, dil, in2 != nullptr, kc) && coutp <= 128 && (env_int("PWC_TC_WM", 1) || out_f32 == 2) &&
       !(out_f32 == 1 && (cin_span + kc - 1) / kc < 4)) {
@@ -565,7 +577,10 @@ extern "C" int pwc_tc_conv_set_out_groups(pwc_tc_conv* h, int g, long group_pitc
 extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
   if (!h) return (int)cudaErrorInvalidValue;
   if (h->halo == 2) {
-    pwc::conv_tc_wm_kernel<<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp);
+    if (h->wp.ts || h->wp.has_skip || h->wp.has_kk)
+      pwc::conv_tc_wm_kernel<true><<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp);
+    else
+      pwc::conv_tc_wm_kernel<false><<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp);
     return (int)cudaGetLastError();
   }
   if (h->halo) {

@@ -149,7 +149,7 @@ class PlanBF16:
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
             flops=None, ts=False, groups=None, kkskip=False):
         L = _TcLayer()
-        L.kkskip = bool(kkskip and span <= 64 and cmap is None)
+        L.kkskip = bool(kkskip and span <= 64 and cmap is None and os.environ.get("PWC_TC_KKSKIP", "1") != "0")
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
         L.wfn = _stacked(wfn if wfn is not None else key) if ts else wfn
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
