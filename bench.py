@@ -281,11 +281,11 @@ def run_ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.mode == "bf16" else "f32", "data": "synthetic",
         "config": {"workload": f"PWCDCNet forward, batch {B}/GPU, {W}x{H}, random-init weights, conv_mode={args.mode}",
                    "l2": "activation working set per step >> 126 MB L2 (no flush needed)", "parallelism": f"pairs sharded x{world}, no collective"},
-        "e2e": {"value": pairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": x_host.numel() * 4,
-                "d2h_bytes_per_step": out_host.numel() * 4,
+        "e2e": {"value": pairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": x_host.numel() * 4 * world,
+                "d2h_bytes_per_step": out_host.numel() * 4 * world,
                 "api": "opticalflow_b200.driver.FlowPipeline.run (copy/compute overlapped)",
                 "blocking_model_call_value": pairs / t_sync},
-        "gpu_launches": launches_per_step * args.steps,
+        "gpu_launches": launches_per_step * args.steps * world,
         "roofline": roof, "roofline_corr": roof_corr, "roofline_corr_fp32": roof_corr_f32,
         "step_tflops": step_tflops,
         "cpu_baseline": {"value": cpu_v, "unit": "pairs/s", "cores": cpu_cores, "kind": "port", "sample": cpu_sample},
