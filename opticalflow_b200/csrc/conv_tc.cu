@@ -455,8 +455,10 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
     if (g_num_sms <= 0) g_num_sms = 148;
     cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_wm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_wm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_wm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_wm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_wm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(conv_tc_wm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   }
   if (halo_eligible(stride, dil, in2 != nullptr, kc) && coutp <= 128 && (env_int("PWC_TC_WM", 1) || out_f32 == 2) &&
       !(out_f32 == 1 && (cin_span + kc - 1) / kc < 4)) {
@@ -577,10 +579,14 @@ extern "C" int pwc_tc_conv_set_out_groups(pwc_tc_conv* h, int g, long group_pitc
 extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
   if (!h) return (int)cudaErrorInvalidValue;
   if (h->halo == 2) {
-    if (h->wp.ts || h->wp.has_skip || h->wp.has_kk)
-      pwc::conv_tc_wm_kernel<true><<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp);
-    else
-      pwc::conv_tc_wm_kernel<false><<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp);
+    const cudaStream_t st = (cudaStream_t)stream;
+#define PWC_WM_LAUNCH(MODE) \
+  pwc::conv_tc_wm_kernel<MODE><<<h->grid, pwc::kHaloThreads, h->smem_bytes, st>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp)
+    if (h->wp.ts) PWC_WM_LAUNCH(1);
+    else if (h->wp.has_skip) PWC_WM_LAUNCH(2);
+    else if (h->wp.has_kk) PWC_WM_LAUNCH(3);
+    else PWC_WM_LAUNCH(0);
+#undef PWC_WM_LAUNCH
     return (int)cudaGetLastError();
   }
   if (h->halo) {

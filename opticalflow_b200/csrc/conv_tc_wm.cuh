@@ -49,10 +49,11 @@ __device__ __forceinline__ void named_bar(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-// kExt = false: the plain 9-tap path with nothing extra on the MMA issue path (the big layers run at > 90% of the tensor
-// peak only while the issuing thread does no more than descriptor arithmetic); kExt = true adds the tap-stacked mode, the
-// zero-block / K-step skip lists.
-template <bool kExt>
+// kMode = 0: the plain 9-tap path with nothing extra on the MMA issue path (the big layers run at > 90% of the tensor
+// peak only while the issuing thread does no more than descriptor arithmetic); the tap-stacked mode and the zero-block /
+// K-step skip lists are separate instances.
+// kMode: 0 plain | 1 tap-stacked | 2 zero-block skip list | 3 K-step skip masks (one instance each: see above)
+template <int kMode>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                   const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const WmParams p) {
@@ -132,8 +133,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         __syncwarp();
         if (++xb == 2) { xb = 0; xph ^= 1; }
         if (!p.w_resident) {
-          for (int tap = 0; tap < (kExt ? p.ntaps : 9); tap += p.tps) {
-            if ((kExt && p.has_skip) && ((p.skip[tap] >> ch) & 1ull)) continue;
+          for (int tap = 0; tap < (kMode == 1 ? 1 : 9); tap += p.tps) {
+            if ((kMode == 2) && ((p.skip[tap] >> ch) & 1ull)) continue;
             ptx::mbar_wait(w_empty(s), wph ^ 1);
             if (ptx::elect_one()) {
               ptx::mbar_expect_tx(w_full(s), p.w_bytes_tx * p.tps);
@@ -152,7 +153,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     if (p.fp16) idesc &= ~((7u << 7) | (7u << 10));          // A/B format 0 = F16
     const uint32_t row_bytes = p.kc * 2;
     const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
-    const uint32_t sbo_x = ((kExt && p.ts) ? 8u : 10u) * row_bytes;     // TS: all halo pixels in order; else 8 of every 10
+    const uint32_t sbo_x = ((kMode == 1) ? 8u : 10u) * row_bytes;     // TS: all halo pixels in order; else 8 of every 10
     int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
     int acc = 0; uint32_t tph = 0;
     if (p.w_resident) ptx::mbar_wait(w_all, 0);
@@ -163,7 +164,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       ptx::mbar_wait(t_empty(acc), tph ^ 1);
       ptx::tc_fence_after();
       wm_mark(trm, 1, it_idx, 1);
-      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * ((kExt && p.ts) ? 256 : p.npx));
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * ((kMode == 1) ? 256 : p.npx));
       bool first = true;                                   // the first MMA of an item overwrites the accumulator
       for (int ch = 0; ch < p.nchunk; ++ch) {
         ptx::mbar_wait(x_full(xb), xph);
@@ -173,12 +174,12 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         const int nkk = min(p.kc, p.cin_span - ch * p.kc + 15) >> 4;     // K=16 steps holding real channels
         const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
         int ftap = 0;                                        // first tap actually issued for this chunk
-        if ((kExt && p.has_skip)) while (ftap < 8 && ((p.skip[ftap] >> ch) & 1ull)) ++ftap;
+        if ((kMode == 2)) while (ftap < 8 && ((p.skip[ftap] >> ch) & 1ull)) ++ftap;
         auto issue_tap = [&](uint32_t sw, int tap) {
           const int ky = tap / 3, kx = tap - 3 * ky;
           const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
           const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * 10 + kx) * row_bytes) >> 4);
-          if ((kExt && p.has_kk)) {
+          if ((kMode == 3)) {
             const int km = p.kk_mask[tap];
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk)
@@ -200,8 +201,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           }
           __syncwarp();
         } else {
-          for (int tap0 = 0; tap0 < (kExt ? p.ntaps : 9); tap0 += p.tps) {
-            if ((kExt && p.has_skip) && ((p.skip[tap0] >> ch) & 1ull)) continue;
+          for (int tap0 = 0; tap0 < (kMode == 1 ? 1 : 9); tap0 += p.tps) {
+            if ((kMode == 2) && ((p.skip[tap0] >> ch) & 1ull)) continue;
             ptx::mbar_wait(w_full(s), wph);
             ptx::tc_fence_after();
             if (ptx::elect_one()) {
@@ -220,7 +221,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           __syncwarp();
         }
         if (ch == p.nchunk - 1) wm_mark(trm, 1, it_idx, 3);
-        if (!(kExt && p.has_skip) || !((p.skip[ftap] >> ch) & 1ull)) first = false;   // some tap of this chunk was issued
+        if (!(kMode == 2) || !((p.skip[ftap] >> ch) & 1ull)) first = false;   // some tap of this chunk was issued
         if (++xb == 2) { xb = 0; xph ^= 1; }
       }
       if (++acc == 2) { acc = 0; tph ^= 1; }
@@ -248,8 +249,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       ptx::mbar_wait(t_full(acc), tph);
       ptx::tc_fence_after();
       wm_mark(tre, 2, it_idx, 1);
-      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * ((kExt && p.ts) ? 256 : p.npx));
-      if ((kExt && p.ts)) {
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * ((kMode == 1) ? 256 : p.npx));
+      if ((kMode == 1)) {
         // ---- tap-stacked: TMEM lane m = tap*cout + co holds that tap's partial sums over the whole halo tile ----
         float* S = reinterpret_cast<float*>(smem_raw + (s_base - ptx::smem_addr(smem_raw)));
         const int m = lg * 32 + lane, mrows = 9 * p.cout;
