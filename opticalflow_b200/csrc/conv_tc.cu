@@ -66,6 +66,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   if (warp == 1) ptx::tmem_alloc(tmem_slot, p.tmem_cols);
   ptx::tc_fence_before();
   __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -581,7 +583,8 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
   if (h->halo == 2) {
     const cudaStream_t st = (cudaStream_t)stream;
 #define PWC_WM_LAUNCH(MODE) \
-  pwc::conv_tc_wm_kernel<MODE><<<h->grid, pwc::kHaloThreads, h->smem_bytes, st>>>(h->tmA0, h->tmB, h->tmO, h->tmO2, h->wp)
+  pwc::launch_pdl(pwc::conv_tc_wm_kernel<MODE>, dim3(h->grid), dim3(pwc::kHaloThreads), h->smem_bytes, st, h->tmA0, h->tmB, h->tmO, \
+                  h->tmO2, h->wp)
     if (h->wp.ts) PWC_WM_LAUNCH(1);
     else if (h->wp.has_skip) PWC_WM_LAUNCH(2);
     else if (h->wp.has_kk) PWC_WM_LAUNCH(3);
@@ -590,10 +593,12 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
     return (int)cudaGetLastError();
   }
   if (h->halo) {
-    pwc::conv_tc_halo_kernel<<<h->grid, pwc::kHaloThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmB, h->hp);
+    pwc::launch_pdl(pwc::conv_tc_halo_kernel, dim3(h->grid), dim3(pwc::kHaloThreads), h->smem_bytes, (cudaStream_t)stream,
+                    h->tmA0, h->tmB, h->hp);
     return (int)cudaGetLastError();
   }
-  pwc::conv_tc_kernel<<<h->grid, pwc::kTcThreads, h->smem_bytes, (cudaStream_t)stream>>>(h->tmA0, h->tmA1, h->tmB, h->p);
+  pwc::launch_pdl(pwc::conv_tc_kernel, dim3(h->grid), dim3(pwc::kTcThreads), h->smem_bytes, (cudaStream_t)stream, h->tmA0,
+                  h->tmA1, h->tmB, h->p);
   return (int)cudaGetLastError();
 }
 

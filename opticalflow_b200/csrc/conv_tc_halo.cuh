@@ -93,6 +93,8 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 1) ptx::tmem_alloc(tmem_slot, p.tmem_cols);
   ptx::tc_fence_before();
   __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 

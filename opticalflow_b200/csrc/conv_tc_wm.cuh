@@ -115,6 +115,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           ptx::tma_load_2d(w_base + j * p.w_bytes + r * p.cg * 32 * p.kc * 2, &tmW, w_all, 0, j * p.coutp);
     }
     __syncwarp();
+    pdl_wait();                                          // weights above do not depend on the previous kernel; activations do
+    pdl_launch_dependents();
     int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
       int n, ry, rx, ty0, tx0;
@@ -228,6 +230,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     }
   } else {
     // ===================== epilogue warps 2..5: thread = output channel =====================
+    pdl_wait();
     const int lg = warp & 3;
     const int part = lg / p.cg;                          // which pixel part this warp stores (weight replicas on M)
     const int co = (lg - part * p.cg) * 32 + lane;

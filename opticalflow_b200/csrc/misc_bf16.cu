@@ -17,6 +17,8 @@ __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __rest
                                                           int B, int H, int W, float slope) {
   __shared__ __align__(16) float ws[27][16];
   __shared__ float bs[16];
+  pdl_wait();
+  pdl_launch_dependents();
   for (int e = threadIdx.x; e < 432; e += blockDim.x) {       // torch [16][3][3][3] -> [ci*9+tap][co]
     const int co = e / 27, r = e - co * 27;
     ws[r][co] = w[e];
@@ -91,6 +93,8 @@ __global__ void __launch_bounds__(256) deconv4x4s2_c2_any_kernel(const TI* __res
                                                                  TO* __restrict__ out, long out_pitch, int out_coff,
                                                                  float* __restrict__ out_b, long out_b_pitch,
                                                                  int N, int Hin, int Win, int CinP) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int lane = threadIdx.x & 31;
   const long wid = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int Hout = 2 * Hin, Wout = 2 * Win;
@@ -143,6 +147,8 @@ __global__ void __launch_bounds__(256) deconv4x4s2_c2_small_kernel(const TI* __r
                                                                    TO* __restrict__ out, long out_pitch, int out_coff,
                                                                    float* __restrict__ out_b, long out_b_pitch,
                                                                    int N, int Hin, int Win, int CinP) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int Hout = 2 * Hin, Wout = 2 * Win;
   const long total = (long)N * Hout * Wout;
   for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
@@ -180,9 +186,8 @@ __global__ void __launch_bounds__(256) deconv4x4s2_c2_small_kernel(const TI* __r
 extern "C" int pwc_conv1a_bf16_fwd(const float* x, const float* w, const float* bias, void* out,
                                    int B, int H, int W, float slope, void* stream) {
   if (B <= 0 || (H & 1) || (W & 1)) return (int)cudaErrorInvalidValue;
-  pwc::conv1a_bf16_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(x, w, bias, reinterpret_cast<__nv_bfloat16*>(out),
-                                                                      B, H, W, slope);
-  return (int)cudaGetLastError();
+  return (int)pwc::launch_pdl(pwc::conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, (cudaStream_t)stream, x, w, bias,
+                              reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope);
 }
 
 extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
@@ -200,9 +205,8 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
     const long px = (long)N * 4 * Hin * Win;
     const unsigned nb = (unsigned)((px + 255) / 256 < 148 * 16 ? (px + 255) / 256 : 148 * 16);
 #define PWC_DECONV_S(TI, TO)                                                                                              \
-  deconv4x4s2_c2_small_kernel<TI, TO><<<nb, 256, 0, s>>>(reinterpret_cast<const TI*>(in), in_pitch, in_coff, w, bias,      \
-                                                         reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b,           \
-                                                         out_b_pitch, N, Hin, Win, CinP)
+  launch_pdl(deconv4x4s2_c2_small_kernel<TI, TO>, dim3(nb), dim3(256), 0, s, reinterpret_cast<const TI*>(in), in_pitch,    \
+             in_coff, w, bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, out_b_pitch, N, Hin, Win, CinP)
     if (in_dtype == PWC_F32 && out_dtype == PWC_F32) PWC_DECONV_S(float, float);
     else if (in_dtype == PWC_F32 && out_dtype == PWC_BF16) PWC_DECONV_S(float, __nv_bfloat16);
     else if (in_dtype == PWC_BF16 && out_dtype == PWC_BF16) PWC_DECONV_S(__nv_bfloat16, __nv_bfloat16);
@@ -212,7 +216,7 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
     return (int)cudaGetLastError();
   }
 #define PWC_DECONV(TI, TO)                                                                                             \
-  deconv4x4s2_c2_any_kernel<TI, TO><<<blocks, 256, 0, s>>>(reinterpret_cast<const TI*>(in), in_pitch, in_coff, CinP, w, \
+  launch_pdl(deconv4x4s2_c2_any_kernel<TI, TO>, dim3(blocks), dim3(256), 0, s, reinterpret_cast<const TI*>(in), in_pitch, in_coff, CinP, w, \
                                                            bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, \
                                                            out_b_pitch, N, Hin, Win, CinP)
   if (in_dtype == PWC_F32 && out_dtype == PWC_F32) PWC_DECONV(float, float);

@@ -81,6 +81,8 @@ __global__ void pack_input_kernel(const float* __restrict__ x, float4* __restric
 
 __global__ void unpack_flow_kernel(const float* __restrict__ in, long pitch, int coff, float* __restrict__ out,
                                    int B, int H, int W, float scale) {
+  pdl_wait();
+  pdl_launch_dependents();
   const long hw = (long)H * W;
   const long total = (long)B * hw;
   for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
@@ -123,8 +125,8 @@ extern "C" int pwc_pack_input_f32(const float* x, float* out, int B, int H, int 
 
 extern "C" int pwc_unpack_flow_f32(const float* in, long in_pitch, int in_coff, float* out,
                                    int B, int H, int W, float scale, void* stream) {
-  pwc::unpack_flow_kernel<<<148 * 4, 256, 0, (cudaStream_t)stream>>>(in, in_pitch, in_coff, out, B, H, W, scale);
-  return (int)cudaGetLastError();
+  return (int)pwc::launch_pdl(pwc::unpack_flow_kernel, dim3(148 * 4), dim3(256), 0, (cudaStream_t)stream, in, in_pitch, in_coff, out,
+                              B, H, W, scale);
 }
 
 extern "C" int pwc_b200_arch(void) { return 100; }

@@ -174,6 +174,8 @@ warp_corr_nhwc_kernel(const __grid_constant__ CUtensorMap tmF1, const WarpCorrPa
     ptx::fence_proxy_async();
   }
   __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
 
   if (warp >= ROWS) {
     // ============================== producers ==============================
@@ -357,8 +359,7 @@ static int launch_nhwc(WarpCorrParams p, cudaStream_t s, int num_sms) {
   const int per_sm = (227 * 1024) / G::kSmemBytes;     // resident CTAs the shared memory allows (registers: 168/thread)
   const int cap = num_sms * (per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm));
   const int grid = p.num_tiles < cap ? p.num_tiles : cap;
-  kern<<<grid, G::kThreads, G::kSmemBytes, s>>>(tm, p);
-  return (int)cudaGetLastError();
+  return (int)launch_pdl(kern, dim3(grid), dim3(G::kThreads), G::kSmemBytes, s, tm, p);
 }
 
 template <typename T, bool TMA>

@@ -44,6 +44,8 @@ warp_corr_small_kernel(const __grid_constant__ CUtensorMap tmOut, const WarpCorr
   const __nv_bfloat16* f2n = reinterpret_cast<const __nv_bfloat16*>(g.f2) + (long)n * H * W * g.f2_pitch;
   const int ng = C >> 2;                                  // 8-byte channel groups per pixel
 
+  pdl_wait();
+  pdl_launch_dependents();
   const bool tr = p.dbg && blockIdx.x == 0 && blockIdx.y == 3 && blockIdx.z == 0 && tid == 4 * 32;
   tc_mark(tr, 0, 0, 0);
   // ---- image-1 row segment -> shared memory (all warps; coalesced 8-byte loads) ----
@@ -192,8 +194,7 @@ static int launch_warp_corr_small(const WarpCorrParams& g, cudaStream_t s) {
                          80, 32, 1, 1, 1, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (e) return e;
   dim3 grid(cdiv(g.W, 32), g.H, g.B);
-  warp_corr_small_kernel<<<grid, kSmThreads, smem, s>>>(tmo, p);
-  return (int)cudaGetLastError();
+  return (int)launch_pdl(warp_corr_small_kernel, grid, dim3(kSmThreads), smem, s, tmo, p);
 }
 
 }  // namespace pwc

@@ -103,6 +103,8 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();                     // features / flow come from the previous kernels (PDL: see common.cuh)
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ============================== image-1 tile loader ==============================
@@ -429,8 +431,7 @@ static int launch_warp_corr_tc(const WarpCorrParams& g, cudaStream_t s) {
                      80, 32, 1, 1, 1, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (e) return e;
   const int grid = p.num_items < num_sms ? p.num_items : num_sms;
-  warp_corr_tc_kernel<<<grid, kTcThreads, kTcSmemBytes, s>>>(tm, tmo, p);
-  return (int)cudaGetLastError();
+  return (int)launch_pdl(warp_corr_tc_kernel, dim3(grid), dim3(kTcThreads), kTcSmemBytes, s, tm, tmo, p);
 }
 
 }  // namespace pwc
