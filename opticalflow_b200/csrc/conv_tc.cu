@@ -328,7 +328,20 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   int rows = even_up(cdiv(Hd, cdiv(Hd, max_rows)));           // fewest row tiles, least padding
   if (rows > max_rows) rows = max_rows;
   if (rows < 2) rows = 2;
-  while (ntiles(rows) < g_num_sms && rows > 8) rows = even_up(cdiv(rows, 2)) < 8 ? 8 : even_up(cdiv(rows, 2));
+  if (env_int("PWC_TC_WM_ROWMODEL", 1)) {
+    // cost model from tools/micro/mma_issue.cu: one M=128,K=16 MMA takes max(68, N/2) cycles, i.e. tiles below N = 128
+    // pixels are free to grow; time ~ waves x (MMAs per item x cycles per MMA + fixed per-item cost)
+    const long nmma = (long)cdiv(cin_span, kc) * 36;
+    long best = -1;
+    for (int r = 2; r <= max_rows; r += 2) {
+      const long waves = (ntiles(r) + g_num_sms - 1) / g_num_sms;
+      const long cyc = 4L * r > 68 ? 4L * r : 68;
+      const long cost = waves * (nmma * cyc + 2500);
+      if (best < 0 || cost < best || (cost == best && cdiv(Hd, r) * r <= cdiv(Hd, rows) * rows)) { best = cost; rows = r; }
+    }
+  } else {
+    while (ntiles(rows) < g_num_sms && rows > 8) rows = even_up(cdiv(rows, 2)) < 8 ? 8 : even_up(cdiv(rows, 2));
+  }
   // thin single-chunk layers are epilogue-bound: a smaller tile leaves room for the replicated resident weight set
   if (cdiv(cin_span, kc) == 1 && coutp <= 64 && rows > 16 && !out_f32) rows = 16;
   const int forced = env_int("PWC_TC_WM_ROWS", 0);
@@ -350,13 +363,21 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     p.s_stride = p.npx + 4;                                   // words; == 4 (mod 32) when npx % 32 == 0, else still 16B aligned
     p.s_bytes = ((uint32_t)(9 * cout) * p.s_stride * 4u + 1023u) & ~1023u;
   }
+  // small pixel tiles consume a halo tile faster than one TMA round trip: deeper pipeline there
+  p.x_stages = 2;
+  if (!ts && p.npx <= 128 && cdiv(cin_span, kc) >= 3) {
+    p.x_stages = env_int("PWC_TC_WM_XSTAGES", 2);   // measured: 4 stages gain nothing (3374 vs 3400 pairs/s), default stays 2
+    if (p.x_stages < 2) p.x_stages = 2;
+    if (p.x_stages > 4) p.x_stages = 4;
+    while (p.x_stages > 2 && (uint32_t)p.x_stages * p.x_bytes > 64u * 1024u) --p.x_stages;
+  }
   p.cin_span = cin_span;
   p.w_bytes_tx = (uint32_t)coutp * row_bytes;
   p.tma_store = (!out_f32 && !ts && env_int("PWC_TC_WM_TMASTORE", 1)) ? 1 : 0;
   p.o_half = p.tma_store ? (((uint32_t)(rows / 2) * 8u * coutp * 2u + 1023u) & ~1023u) : 0u;
   // second staging buffer (store of one half overlaps the fill of the next) while it leaves >= 4 weight stages
   p.o_nbuf = (p.tma_store && env_int("PWC_TC_WM_OBUF2", 1) &&
-              2u * p.x_bytes + 2u * p.o_half + 4u * 128u * row_bytes <= 200u * 1024u) ? 2 : 1;
+              (uint32_t)p.x_stages * p.x_bytes + 2u * p.o_half + 4u * 128u * row_bytes <= 200u * 1024u) ? 2 : 1;
   p.o_bytes = p.o_half * (uint32_t)p.o_nbuf;
   // weight-tile replication on M (epilogue parallelism for thin layers): only when the whole weight set stays resident.
   // per-warp output stores (no CTA-wide barrier in the epilogue) need 32-channel groups and rows divisible by the parts;
@@ -378,7 +399,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
         while (R % rs) --rs;
         o_half = (uint32_t)rs * 8u * 64u;                    // one staging buffer of one warp
         o_bytes = 4u * 2u * o_half;
-        fits = 9u * p.nchunk * full_tile <= 216u * 1024u - 2u * p.x_bytes - o_bytes;
+        fits = 9u * p.nchunk * full_tile <= 216u * 1024u - (uint32_t)p.x_stages * p.x_bytes - o_bytes;
       }
       if (rep == 1) {
         rs = R < 8 ? R : 8;
@@ -386,7 +407,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
         o_half = (uint32_t)rs * 8u * 64u; o_bytes = 4u * 2u * o_half;
       }
     } else if (rep > 1) {
-      fits = 9u * p.nchunk * full_tile <= 216u * 1024u - 2u * p.x_bytes - o_bytes;
+      fits = 9u * p.nchunk * full_tile <= 216u * 1024u - (uint32_t)p.x_stages * p.x_bytes - o_bytes;
     }
     if (!fits) continue;
     p.rep = rep;
@@ -395,7 +416,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   }
   p.w_bytes = p.rep > 1 ? full_tile : ((p.w_bytes_tx + 1023u) & ~1023u);
   p.w_pad = full_tile > p.w_bytes ? full_tile - p.w_bytes : 0u;
-  const uint32_t budget = 216u * 1024u - 2u * p.x_bytes - p.w_pad - p.o_bytes - p.s_bytes;
+  const uint32_t budget = 216u * 1024u - (uint32_t)p.x_stages * p.x_bytes - p.w_pad - p.o_bytes - p.s_bytes;
   const uint32_t all_w = 9u * p.nchunk * p.w_bytes;
   p.w_resident = (!ts && all_w <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
   if (!p.w_resident && p.rep > 1) { delete h; return (int)cudaErrorInvalidValue; }
@@ -413,7 +434,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = (out2 && out_f32 != 2) ? n_split : N;
   p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
   const uint32_t nw = p.w_resident ? 9u * p.nchunk : p.w_stages * p.tps;
-  h->smem_bytes = 2u * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + p.s_bytes + 8 * (10 + 2 * p.w_stages) + 16 + 1024;
+  h->smem_bytes = (uint32_t)p.x_stages * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + p.s_bytes + 8 * (14 + 2 * p.w_stages) + 16 + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
   int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, W, H, N,

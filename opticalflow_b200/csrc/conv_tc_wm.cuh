@@ -18,6 +18,7 @@ namespace pwc {
 struct WmParams {
   int N, H, W, dil;
   int cout, coutp, kc, nchunk, rows, npx;       // npx = 8*rows = MMA N
+  int x_stages;                                   // halo-tile pipeline depth (2 for big tiles, up to 4 for small ones)
   int cin_span, tps, rep, cg;                   // tps: taps per weight stage (1|3|9); rep: weight-tile replicas on M
                                                 // (lane groups rep*cg <= 4 hold the same channels -> epilogue splits pixels)
   int tiles_x, tiles_y, tiles_per_img, num_items;
@@ -59,20 +60,20 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
                   const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const WmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (ptx::smem_addr(smem_raw) + 1023u) & ~1023u;
-  const uint32_t x_base = base;                                   // 2 halo buffers
-  const uint32_t w_base = base + 2u * p.x_bytes;                  // weight ring (or the resident weight set)
+  const uint32_t x_base = base;                                   // x_stages (2..4) halo buffers
+  const uint32_t w_base = base + (uint32_t)p.x_stages * p.x_bytes;                  // weight ring (or the resident weight set)
   const uint32_t nw = p.w_resident ? (uint32_t)(9 * p.nchunk) : p.w_stages * p.tps;
   const uint32_t o_base = w_base + nw * p.w_bytes + p.w_pad;      // w_pad: the M=128 MMA reads 128 rows from a CoutP-row tile
   const uint32_t s_base = o_base + p.o_bytes;                     // S: per-tap partial sums [9*cout][s_stride] fp32 (TS mode)
   const uint32_t bar_base = s_base + p.s_bytes;                   // o: output staging tile (half an item)
   auto x_full = [&](int i) { return bar_base + 8u * i; };
-  auto x_empty = [&](int i) { return bar_base + 8u * (2 + i); };
-  auto t_full = [&](int i) { return bar_base + 8u * (4 + i); };
-  auto t_empty = [&](int i) { return bar_base + 8u * (6 + i); };
-  const uint32_t w_all = bar_base + 8u * 8;
-  auto w_full = [&](int s) { return bar_base + 8u * (9 + s); };
-  auto w_empty = [&](int s) { return bar_base + 8u * (9 + p.w_stages + s); };
-  const uint32_t tmem_slot = bar_base + 8u * (9 + 2 * p.w_stages);
+  auto x_empty = [&](int i) { return bar_base + 8u * (4 + i); };
+  auto t_full = [&](int i) { return bar_base + 8u * (8 + i); };
+  auto t_empty = [&](int i) { return bar_base + 8u * (10 + i); };
+  const uint32_t w_all = bar_base + 8u * 12;
+  auto w_full = [&](int s) { return bar_base + 8u * (13 + s); };
+  auto w_empty = [&](int s) { return bar_base + 8u * (13 + p.w_stages + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (13 + 2 * p.w_stages);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_addr(smem_raw)));
 
@@ -81,10 +82,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmX); ptx::prefetch_tmap(&tmW);
-    for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(x_full(i), 1); ptx::mbar_init(x_empty(i), 1);
-      ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 4);
-    }
+    for (int i = 0; i < 4; ++i) { ptx::mbar_init(x_full(i), 1); ptx::mbar_init(x_empty(i), 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(t_full(i), 1); ptx::mbar_init(t_empty(i), 4); }
     ptx::mbar_init(w_all, 1);
     for (uint32_t s = 0; s < p.w_stages; ++s) { ptx::mbar_init(w_full(s), 1); ptx::mbar_init(w_empty(s), 1); }
     ptx::fence_barrier_init();
@@ -133,7 +132,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, xa, ya, n);
         }
         __syncwarp();
-        if (++xb == 2) { xb = 0; xph ^= 1; }
+        if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
         if (!p.w_resident) {
           for (int tap = 0; tap < (kMode == 1 ? 1 : 9); tap += p.tps) {
             if ((kMode == 2) && ((p.skip[tap] >> ch) & 1ull)) continue;
@@ -224,7 +223,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         }
         if (ch == p.nchunk - 1) wm_mark(trm, 1, it_idx, 3);
         if (!(kMode == 2) || !((p.skip[ftap] >> ch) & 1ull)) first = false;   // some tap of this chunk was issued
-        if (++xb == 2) { xb = 0; xph ^= 1; }
+        if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
       }
       if (++acc == 2) { acc = 0; tph ^= 1; }
     }
