@@ -207,6 +207,8 @@ struct pwc_tc_conv {
   int halo;                 // 2: conv_tc_wm_kernel, 1: conv_tc_halo_kernel, 0: conv_tc_kernel (per-tap boxes)
   size_t smem_bytes;
   int grid;
+  void* scratch = nullptr;  // split-K partial sums + tile counters (WM kernel, small layers); owned by the handle
+  ~pwc_tc_conv() { if (scratch) cudaFree(scratch); }
 };
 
 namespace pwc {
@@ -454,7 +456,31 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   }
   if (e || h->smem_bytes > 227u * 1024u || cols > 512) { delete h; return e ? e : (int)cudaErrorInvalidValue; }
   h->tmA1 = h->tmA0;
-  h->grid = p.num_items < g_num_sms ? p.num_items : g_num_sms;
+  // split-K for layers whose pixel tiles cannot fill the machine (pyramid levels 5, 6): ksplit CTAs per tile, each a
+  // contiguous range of 64-channel chunks; partial sums meet in an fp32 scratch, the last CTA to arrive finishes the tile.
+  // OPT-IN (PWC_TC_WM_KSPLIT=1): measured on B200 it only pays for >= 8 chunks (conv6_4 24 -> 18 us) and loses on short
+  // K loops (conv5aa 16 -> 34 us: the rendezvous costs ~5 us), and the atomic summation order makes replays differ in
+  // the last bit, which the parity tests do not accept.
+  p.ksplit = 1; p.cps = p.nchunk; p.scratch = nullptr; p.counters = nullptr;
+  if (p.wstore && !ts && p.nchunk >= 2 && env_int("PWC_TC_WM_KSPLIT", 0)) {
+    int ks = g_num_sms / p.num_items;
+    if (ks > 8) ks = 8;
+    if (ks > p.nchunk) ks = p.nchunk;
+    const int forced_ks = env_int("PWC_TC_WM_KSPLIT_N", 0);
+    if (forced_ks > 0) ks = forced_ks < p.nchunk ? forced_ks : p.nchunk;
+    if (ks >= 2) {
+      p.cps = cdiv(p.nchunk, ks);
+      p.ksplit = cdiv(p.nchunk, p.cps);
+      const size_t fl = (size_t)p.num_items * p.npx * 128;
+      const size_t bytes = fl * sizeof(float) + (size_t)p.num_items * sizeof(int);
+      if (cudaMalloc(&h->scratch, bytes) != cudaSuccess || cudaMemset(h->scratch, 0, bytes) != cudaSuccess) {
+        delete h; return (int)cudaErrorMemoryAllocation;
+      }
+      p.scratch = reinterpret_cast<float*>(h->scratch);
+      p.counters = reinterpret_cast<int*>(p.scratch + fl);
+    }
+  }
+  { const int v = p.num_items * p.ksplit; h->grid = v < g_num_sms ? v : g_num_sms; }
   *handle = h;
   return 0;
 }

@@ -18,6 +18,8 @@ namespace pwc {
 struct WmParams {
   int N, H, W, dil;
   int cout, coutp, kc, nchunk, rows, npx;       // npx = 8*rows = MMA N
+  int ksplit, cps;                                // split-K: ksplit CTAs share one pixel tile, cps chunks each; partial sums
+  float* scratch; int* counters;                  // meet in an fp32 scratch (red.add), the last CTA to arrive finishes the tile
   int x_stages;                                   // halo-tile pipeline depth (2 for big tiles, up to 4 for small ones)
   int cin_span, tps, rep, cg;                   // tps: taps per weight stage (1|3|9); rep: weight-tile replicas on M
                                                 // (lane groups rep*cg <= 4 hold the same channels -> epilogue splits pixels)
@@ -76,6 +78,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   const uint32_t tmem_slot = bar_base + 8u * (13 + 2 * p.w_stages);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_addr(smem_raw)));
+  volatile int* ks_flag = reinterpret_cast<volatile int*>(smem_raw + (tmem_slot + 8 - ptx::smem_addr(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int d = p.dil;
@@ -117,16 +120,18 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     pdl_wait();                                          // weights above do not depend on the previous kernel; activations do
     pdl_launch_dependents();
     int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+    for (int vitem = blockIdx.x; vitem < p.num_items * p.ksplit; vitem += gridDim.x) {
+      const int item = vitem / p.ksplit, ks = vitem - item * p.ksplit;
+      const int ch_lo = ks * p.cps, ch_hi = min(p.nchunk, ch_lo + p.cps);
       int n, ry, rx, ty0, tx0;
       decode(item, n, ry, rx, ty0, tx0);
       const int ya = ry + d * (ty0 - 1), xa = rx + d * (tx0 - 1);
       const bool trp = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
-      const int it_idx = (item - (int)blockIdx.x) / (int)gridDim.x;
-      for (int ch = 0; ch < p.nchunk; ++ch) {
-        if (ch == 0) wm_mark(trp, 0, it_idx, 0);
+      const int it_idx = (vitem - (int)blockIdx.x) / (int)gridDim.x;
+      for (int ch = ch_lo; ch < ch_hi; ++ch) {
+        if (ch == ch_lo) wm_mark(trp, 0, it_idx, 0);
         ptx::mbar_wait(x_empty(xb), xph ^ 1);
-        if (ch == 0) wm_mark(trp, 0, it_idx, 1);
+        if (ch == ch_lo) wm_mark(trp, 0, it_idx, 1);
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
           ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, xa, ya, n);
@@ -158,19 +163,21 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
     int acc = 0; uint32_t tph = 0;
     if (p.w_resident) ptx::mbar_wait(w_all, 0);
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+    for (int vitem = blockIdx.x; vitem < p.num_items * p.ksplit; vitem += gridDim.x) {
+      const int item = vitem / p.ksplit, ks = vitem - item * p.ksplit;
+      const int ch_lo = ks * p.cps, ch_hi = min(p.nchunk, ch_lo + p.cps);
       const bool trm = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
-      const int it_idx = (item - (int)blockIdx.x) / (int)gridDim.x;
+      const int it_idx = (vitem - (int)blockIdx.x) / (int)gridDim.x;
       wm_mark(trm, 1, it_idx, 0);
       ptx::mbar_wait(t_empty(acc), tph ^ 1);
       ptx::tc_fence_after();
       wm_mark(trm, 1, it_idx, 1);
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * ((kMode == 1) ? 256 : p.npx));
       bool first = true;                                   // the first MMA of an item overwrites the accumulator
-      for (int ch = 0; ch < p.nchunk; ++ch) {
+      for (int ch = ch_lo; ch < ch_hi; ++ch) {
         ptx::mbar_wait(x_full(xb), xph);
         ptx::tc_fence_after();
-        if (ch == 0) wm_mark(trm, 1, it_idx, 2);
+        if (ch == ch_lo) wm_mark(trm, 1, it_idx, 2);
         const uint32_t sx = x_base + xb * p.x_bytes;
         const int nkk = min(p.kc, p.cin_span - ch * p.kc + 15) >> 4;     // K=16 steps holding real channels
         const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
@@ -198,7 +205,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
 #pragma unroll 1
             for (int tap = 0; tap < 9; ++tap) issue_tap(w_base + (tap * p.nchunk + ch) * p.w_bytes, tap);
             ptx::umma_commit(x_empty(xb));
-            if (ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
+            if (ch == ch_hi - 1) ptx::umma_commit(t_full(acc));
           }
           __syncwarp();
         } else {
@@ -217,11 +224,11 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           }
           if (ptx::elect_one()) {
             ptx::umma_commit(x_empty(xb));
-            if (ch == p.nchunk - 1) ptx::umma_commit(t_full(acc));
+            if (ch == ch_hi - 1) ptx::umma_commit(t_full(acc));
           }
           __syncwarp();
         }
-        if (ch == p.nchunk - 1) wm_mark(trm, 1, it_idx, 3);
+        if (ch == ch_hi - 1) wm_mark(trm, 1, it_idx, 3);
         if (!(kMode == 2) || !((p.skip[ftap] >> ch) & 1ull)) first = false;   // some tap of this chunk was issued
         if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
       }
@@ -240,13 +247,15 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     const bool issuer = (threadIdx.x == 64);
     int obuf = 0, wbuf = 0;
     int acc = 0; uint32_t tph = 0;
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+    for (int vitem = blockIdx.x; vitem < p.num_items * p.ksplit; vitem += gridDim.x) {
+      const int item = vitem / p.ksplit, ks = vitem - item * p.ksplit;
+      const int ch_lo = ks * p.cps, ch_hi = min(p.nchunk, ch_lo + p.cps);
       int n, ry, rx, ty0, tx0;
       decode(item, n, ry, rx, ty0, tx0);
       const bool second = (n >= p.n_split) && (p.out2 != nullptr) && (p.out_f32 != 2);
       const int nn = second ? n - p.n_split : n;
       const bool tre = (p.dbg & 32) && blockIdx.x == 0 && threadIdx.x == 128;     // warp 4 = lane group 0 (always live)
-      const int it_idx = (item - (int)blockIdx.x) / (int)gridDim.x;
+      const int it_idx = (vitem - (int)blockIdx.x) / (int)gridDim.x;
       wm_mark(tre, 2, it_idx, 0);
       ptx::mbar_wait(t_full(acc), tph);
       ptx::tc_fence_after();
@@ -302,9 +311,45 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       if (p.wstore) {
         // ---- per-warp stores: warp (channel group gc, pixel part) stages [o_rs rows x 8 px][32 ch] and issues its own
         //      TMA store (box 32 ch x 8 px x o_rs rows); no CTA-wide barrier, two staging buffers per warp ----
-        if (warp_live) {
-          const int gc = lg - part * p.cg;                   // 32-channel group of this warp
-          const int R = p.rows / p.rep;                      // tile rows of this warp's part
+        const int gc = lg - part * p.cg;                     // 32-channel group of this warp
+        const int R = p.rows / p.rep;                        // tile rows of this warp's part
+        // partial sums of this CTA -> scratch [item][pixel][128 ch] (split-K only); lanes = consecutive channels
+        float* scr = p.scratch + ((size_t)item * p.npx + (size_t)part * R * 8) * 128 + gc * 32 + lane;
+        bool finish = true;
+        if (p.ksplit > 1) {
+          if (warp_live) {
+            for (int c0 = 0; c0 < R * 8; c0 += 64) {
+              uint32_t v[4][16];
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                if (c0 + q * 16 < R * 8) ptx::tmem_ld16(taddr + part * R * 8 + c0 + q * 16, v[q]);
+              ptx::tmem_ld_wait();
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                if (c0 + q * 16 < R * 8) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    if (c0 + q * 16 + i < R * 8) atomicAdd(scr + (size_t)(c0 + q * 16 + i) * 128, __uint_as_float(v[q][i]));
+                }
+            }
+          }
+          // accumulator drained: hand it back before the cross-CTA rendezvous
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(t_empty(acc));
+          __threadfence();
+          named_bar(2, 128);
+          if (threadIdx.x == 64) {
+            const int old = atomicAdd(p.counters + item, 1);
+            *ks_flag = (old == p.ksplit - 1) ? 1 : 0;
+            if (old == p.ksplit - 1) p.counters[item] = 0;   // ready for the next forward
+          }
+          named_bar(2, 128);
+          finish = (*ks_flag != 0);
+          if (finish) __threadfence();
+          named_bar(2, 128);                                 // flag may be rewritten for the next item
+        }
+        if (warp_live && finish) {
           const uint32_t my_o = o_base + (uint32_t)lg * 2u * p.o_half;
           int c0g = gc * 32, grp = 0;
           if (p.out_groups > 1) { const int cgp = p.coutp / p.out_groups; grp = c0g / cgp; c0g -= grp * cgp; }
@@ -317,10 +362,22 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
             // all TMEM loads of the step (<= 64 columns) are issued before the single wait: their latency (several
             // hundred cycles while the next item's MMAs are writing TMEM) is paid once per step, not once per 16 columns
             uint32_t v[4][16];
+            if (p.ksplit > 1) {                              // last CTA of the tile: the sums are complete in the scratch
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-              if (q * 16 < ncol) ptx::tmem_ld16(taddr + col0 + q * 16, v[q]);
-            ptx::tmem_ld_wait();
+              for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                  if (q * 16 + i < ncol) {
+                    float* sp = scr + (size_t)(r0 * 8 + q * 16 + i) * 128;
+                    v[q][i] = __float_as_uint(__ldcg(sp));
+                    __stcg(sp, 0.f);                         // leave the scratch zeroed for the next forward
+                  }
+            } else {
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                if (q * 16 < ncol) ptx::tmem_ld16(taddr + col0 + q * 16, v[q]);
+              ptx::tmem_ld_wait();
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               if (q * 16 < ncol) {
@@ -345,6 +402,11 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
             }
             wbuf ^= 1;
           }
+        }
+        if (p.ksplit > 1) {                                  // t_empty was signalled above
+          wm_mark(tre, 2, it_idx, 3);
+          if (++acc == 2) { acc = 0; tph ^= 1; }
+          continue;
         }
         wm_mark(tre, 2, it_idx, 3);
       } else if (p.tma_store) {
