@@ -235,9 +235,9 @@ static int env_int(const char* name, int dflt) {
 
 // Halo kernel: stride 1, dilation <= 8 (TMA elementStrides limit), one input tensor.  PWC_TC_HALO=0 forces the
 // per-tap kernel (debugging / A-B comparisons); PWC_TC_HALO_MINKC (default 16) is the smallest channel chunk it takes.
-static bool halo_eligible(int stride, int dil, bool has_in2, int kc) {
+static bool halo_eligible(int stride, int dil, bool has_in2, int kc, int max_dil = 8) {
   if (!env_int("PWC_TC_HALO", 1)) return false;
-  return stride == 1 && dil >= 1 && dil <= 8 && !has_in2 && (kc == 16 || kc == 32 || kc == 64) &&
+  return stride == 1 && dil >= 1 && dil <= max_dil && !has_in2 && (kc == 16 || kc == 32 || kc == 64) &&
          kc >= env_int("PWC_TC_HALO_MINKC", 16);
 }
 
@@ -304,6 +304,22 @@ static int create_halo(pwc_tc_conv** handle, const void* in, long in_pitch, int 
   return 0;
 }
 
+// NHWC slice with W split as (W/d, d): 5-D (C, d, W/d, H, N); box (boxC, 1, boxXg, boxH, 1) = one x phase of a tile.
+// For dilations above the TMA element-stride limit of 8; needs W % d == 0.
+static int make_tmap_xsplit(CUtensorMap* m, const void* base, long pitch, int C, int W, int H, int N, int d,
+                            int boxC, int boxXg, int boxH, CUtensorMapSwizzle swz) {
+  EncodeTiledFn enc = get_encode_tiled();
+  if (!enc) return (int)cudaErrorNotSupported;
+  cuuint64_t dims[5] = {(cuuint64_t)C, (cuuint64_t)d, (cuuint64_t)(W / d), (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[4] = {(cuuint64_t)pitch * 2, (cuuint64_t)pitch * 2 * d, (cuuint64_t)pitch * 2 * W,
+                           (cuuint64_t)pitch * 2 * W * H};
+  cuuint32_t box[5] = {(cuuint32_t)boxC, 1, (cuuint32_t)boxXg, (cuuint32_t)boxH, 1};
+  cuuint32_t es[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
 static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in_coff, int cin_span, int kc,
                      const void* w_packed, const float* bias, int cout, int coutp,
                      void* out, long out_pitch, int out_coff, void* out2, long out2_pitch, int out2_coff, int n_split,
@@ -323,10 +339,18 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   for (int i = 0; i < 9; ++i) p.skip[i] = 0ull;
   p.N = N; p.H = H; p.W = W; p.dil = dil;
   p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc);
-  const int Hd = cdiv(H, dil), Wd = cdiv(W, dil);
-  const int max_rows = (256 / dil - 2) < 32 ? ((256 / dil - 2) & ~1) : 32;
+  // large dilations: phases in x only, the y dilation is a row shift inside a (rows + 2*dil)-row halo tile -- 16 x fewer,
+  // 16 x larger items than d x d sub-lattices of a 7 x 16 image (dc_conv5: N = 56 pixels per MMA otherwise)
+  const int ydense = (dil >= env_int("PWC_TC_WM_YDENSE_MINDIL", 8) && !ts) ? 1 : 0;
+  p.dy = ydense ? 1 : dil; p.kyr = ydense ? dil : 1;
+  p.xsplit = dil > 8 ? 1 : 0;
+  if (p.xsplit && (!ydense || W % dil || out2 || out_f32)) { delete h; return (int)cudaErrorInvalidValue; }
+  const int Hd = ydense ? H : cdiv(H, dil), Wd = cdiv(W, dil);
+  const int nph = ydense ? dil : dil * dil;
+  int max_rows = (256 / dil - 2) < 32 ? ((256 / dil - 2) & ~1) : 32;
+  if (ydense) { max_rows = 50 - 2 * dil; if (max_rows > 32) max_rows = 32; max_rows &= ~1; }
   auto even_up = [](int v) { return (v + 1) & ~1; };
-  auto ntiles = [&](int rows) { return (long)N * dil * dil * cdiv(Hd, rows) * cdiv(Wd, 8); };
+  auto ntiles = [&](int rows) { return (long)N * nph * cdiv(Hd, rows) * cdiv(Wd, 8); };
   int rows = even_up(cdiv(Hd, cdiv(Hd, max_rows)));           // fewest row tiles, least padding
   if (rows > max_rows) rows = max_rows;
   if (rows < 2) rows = 2;
@@ -354,10 +378,10 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   }
   p.rows = rows; p.npx = ts ? (((rows + 2) * 10 + 15) & ~15) : 8 * rows;
   p.tiles_x = cdiv(Wd, 8); p.tiles_y = cdiv(Hd, rows);
-  p.tiles_per_img = dil * dil * p.tiles_x * p.tiles_y;
+  p.tiles_per_img = nph * p.tiles_x * p.tiles_y;
   p.num_items = (int)ntiles(rows);
   const uint32_t row_bytes = (uint32_t)kc * 2;
-  p.x_bytes_tx = (uint32_t)(rows + 2) * 10u * row_bytes;
+  p.x_bytes_tx = (uint32_t)(rows + 2 * p.kyr) * 10u * row_bytes;
   p.x_bytes = (p.x_bytes_tx + 1023u) & ~1023u;
   if (ts) {
     const uint32_t need = (uint32_t)p.npx * row_bytes;        // the MMA reads npx pixel rows (tail rows: don't-care columns)
@@ -439,19 +463,29 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   h->smem_bytes = (uint32_t)p.x_stages * p.x_bytes + (size_t)nw * p.w_bytes + p.w_pad + p.o_bytes + p.s_bytes + 8 * (14 + 2 * p.w_stages) + 16 + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
-  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, W, H, N,
-                         kc, 10 * dil, (rows + 2) * dil, dil, dil, swz);
+  int e = 0;
+  if (p.xsplit) {
+    if (!p.wstore) e = (int)cudaErrorInvalidValue;
+    if (!e) e = make_tmap_xsplit(&h->tmA0, a0, in_pitch, cin_span, W, H, N, dil, kc, 10, rows + 2 * dil, swz);
+  } else {
+    e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, W, H, N,
+                       kc, 10 * dil, ydense ? rows + 2 * dil : (rows + 2) * dil, dil, p.dy, swz);
+  }
   if (!e) e = make_tmap_2d(&h->tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w_packed, (long)9 * p.nchunk * coutp, kc, kc, coutp, swz);
   h->tmO = h->tmA0; h->tmO2 = h->tmA0;
-  if (!e && p.tma_store) {
+  if (!e && p.xsplit) {
+    if ((out_pitch & 7) || (out_coff & 7)) e = (int)cudaErrorInvalidValue;
+    if (!e) e = make_tmap_xsplit(&h->tmO, reinterpret_cast<__nv_bfloat16*>(out) + out_coff, out_pitch, coutp, W, H, N, dil,
+                                 32, 8, p.o_rs, CU_TENSOR_MAP_SWIZZLE_NONE);
+  } else if (!e && p.tma_store) {
     // output slice as a 4-D tensor (CoutP, W, H, images); box = half an item; dilation = element strides; no swizzle
     if ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7)))) e = (int)cudaErrorInvalidValue;
     const int n1 = out2 ? p.n_split : N;
     const int bc = p.wstore ? 32 : coutp, br = p.wstore ? p.o_rs : rows / 2;
     if (!e) e = make_tmap_nhwc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out) + out_coff,
-                               out_pitch, coutp, W, H, n1, bc, 8 * dil, br * dil, dil, dil, CU_TENSOR_MAP_SWIZZLE_NONE);
+                               out_pitch, coutp, W, H, n1, bc, 8 * dil, br * p.dy, dil, p.dy, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (!e && out2) e = make_tmap_nhwc(&h->tmO2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out2) + out2_coff,
-                                       out2_pitch, coutp, W, H, N - n1, bc, 8 * dil, br * dil, dil, dil,
+                                       out2_pitch, coutp, W, H, N - n1, bc, 8 * dil, br * p.dy, dil, p.dy,
                                        CU_TENSOR_MAP_SWIZZLE_NONE);
   }
   if (e || h->smem_bytes > 227u * 1024u || cols > 512) { delete h; return e ? e : (int)cudaErrorInvalidValue; }
@@ -509,10 +543,13 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
     cudaFuncSetAttribute(conv_tc_wm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(conv_tc_wm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   }
-  if (halo_eligible(stride, dil, in2 != nullptr, kc) && coutp <= 128 && (env_int("PWC_TC_WM", 1) || out_f32 == 2) &&
+  const int wm_max_dil = env_int("PWC_TC_WM_YDENSE_MINDIL", 8) <= 16 ? 16 : 8;    // y-dense tiles take dilation 16 too
+  if (halo_eligible(stride, dil, in2 != nullptr, kc, wm_max_dil) && coutp <= 128 && (env_int("PWC_TC_WM", 1) || out_f32 == 2) &&
       !(out_f32 == 1 && (cin_span + kc - 1) / kc < 4)) {
-    return create_wm(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
-                     out2, out2_pitch, out2_coff, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope);
+    const int e = create_wm(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
+                            out2, out2_pitch, out2_coff, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope);
+    if (!e || dil <= 8) return e;
+    *handle = nullptr;                                     // dilation 16 outside the y-dense mode's shapes: per-tap kernel
   }
   if (out_f32 == 2) return (int)cudaErrorInvalidValue;     // fused predict_flow+upfeat exists in the WM kernel only
   if (halo_eligible(stride, dil, in2 != nullptr, kc)) {

@@ -17,6 +17,9 @@ namespace pwc {
 
 struct WmParams {
   int N, H, W, dil;
+  int xsplit;                                     // dilation > 8 (TMA element strides stop at 8): W viewed as (W/dil, dil), 5-D maps
+  int dy, kyr;                                    // y step of the pixel lattice and tile rows per ky tap: (dil, 1) = d x d
+                                                  // sub-lattices; (1, dil) = x phases only, dilation in y by in-tile row shift
   int cout, coutp, kc, nchunk, rows, npx;       // npx = 8*rows = MMA N
   int ksplit, cps;                                // split-K: ksplit CTAs share one pixel tile, cps chunks each; partial sums
   float* scratch; int* counters;                  // meet in an fp32 scratch (red.add), the last CTA to arrive finishes the tile
@@ -104,7 +107,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     const int per_phase = p.tiles_x * p.tiles_y;
     const int ph = r / per_phase;
     r -= ph * per_phase;
-    ry = ph / d; rx = ph - ry * d;
+    if (p.dy == 1) { ry = 0; rx = ph; } else { ry = ph / d; rx = ph - ry * d; }
     ty0 = (r / p.tiles_x) * p.rows; tx0 = (r % p.tiles_x) * 8;
   };
 
@@ -125,7 +128,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       const int ch_lo = ks * p.cps, ch_hi = min(p.nchunk, ch_lo + p.cps);
       int n, ry, rx, ty0, tx0;
       decode(item, n, ry, rx, ty0, tx0);
-      const int ya = ry + d * (ty0 - 1), xa = rx + d * (tx0 - 1);
+      const int ya = ry + p.dy * (ty0 - p.kyr), xa = rx + d * (tx0 - 1);
       const bool trp = (p.dbg & 32) && blockIdx.x == 0 && lane == 0;
       const int it_idx = (vitem - (int)blockIdx.x) / (int)gridDim.x;
       for (int ch = ch_lo; ch < ch_hi; ++ch) {
@@ -134,7 +137,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         if (ch == ch_lo) wm_mark(trp, 0, it_idx, 1);
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
-          ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, xa, ya, n);
+          if (p.xsplit) ptx::tma_load_5d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, rx, tx0 - 1, ya, n);
+          else ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, xa, ya, n);
         }
         __syncwarp();
         if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
@@ -186,7 +190,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         auto issue_tap = [&](uint32_t sw, int tap) {
           const int ky = tap / 3, kx = tap - 3 * ky;
           const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
-          const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * 10 + kx) * row_bytes) >> 4);
+          const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * p.kyr * 10 + kx) * row_bytes) >> 4);
           if ((kMode == 3)) {
             const int km = p.kk_mask[tap];
 #pragma unroll
@@ -395,8 +399,9 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
             ptx::fence_proxy_async();
             __syncwarp();
             if (lane == 0) {
-              const int oy = ry + d * (ty0 + part * R + r0), ox = rx + d * tx0;
+              const int oy = ry + p.dy * (ty0 + part * R + r0), ox = rx + d * tx0;
               if (p.out_groups > 1) ptx::tma_store_5d(&tmO, so, c0g, grp, ox, oy, nn);
+              else if (p.xsplit) ptx::tma_store_5d(&tmO, so, c0g, rx, tx0, oy, nn);
               else ptx::tma_store_4d(second ? &tmO2 : &tmO, so, c0g, ox, oy, nn);
               ptx::bulk_commit();
             }
@@ -442,9 +447,9 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           named_bar(2, 128);
           if (issuer) {
             if (p.out_groups > 1)
-              ptx::tma_store_5d(&tmO, o_base + ooff, 0, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
+              ptx::tma_store_5d(&tmO, o_base + ooff, 0, 0, rx + d * tx0, ry + p.dy * (ty0 + half * (p.rows >> 1)), nn);
             else
-              ptx::tma_store_4d(second ? &tmO2 : &tmO, o_base + ooff, 0, rx + d * tx0, ry + d * (ty0 + half * (p.rows >> 1)), nn);
+              ptx::tma_store_4d(second ? &tmO2 : &tmO, o_base + ooff, 0, rx + d * tx0, ry + p.dy * (ty0 + half * (p.rows >> 1)), nn);
             ptx::bulk_commit();
             if (p.o_nbuf != 2) ptx::bulk_wait_read0();     // single staging tile: wait until it may be overwritten
           }
@@ -460,7 +465,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const int py = (c0 + i) >> 3, px = (c0 + i) & 7;
-            const int oy = ry + d * (ty0 + py), ox = rx + d * (tx0 + px);
+            const int oy = ry + p.dy * (ty0 + py), ox = rx + d * (tx0 + px);
             if (co_live && oy < p.H && ox < p.W) {
               const long pix = ((long)nn * p.H + oy) * p.W + ox;
               float val = lrelu(__uint_as_float(v[i]) + bias, p.slope);

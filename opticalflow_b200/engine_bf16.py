@@ -153,8 +153,8 @@ class PlanBF16:
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
         L.wfn = _stacked(wfn if wfn is not None else key) if ts else wfn
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
-        L.kc = pick_kc(span, stride, dil, src2 is not None)
         L.coutp = 128 if ts else _roundup(cout, 16)
+        L.kc = pick_kc(span, stride, dil, src2 is not None, W=win, coutp=L.coutp, out_f32=bool(out_f32) or dst2 is not None)
         L.wrows = 128 if ts else cout                   # rows of the weight tensor handed to the packer
         dev = self.device
         L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp, device=dev, dtype=BF)

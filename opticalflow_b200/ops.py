@@ -86,12 +86,19 @@ def deconv4x4s2_c2_f32(x, weight, bias, in_coff=0, cin_span=None, chan_map=None)
     return out
 
 
-def pick_kc(cin_span, stride=1, dil=1, has_in2=False):
-    """Channel chunk of the tensor-core conv.  The halo kernel (stride 1, dilation <= 8, one input) takes 64-channel
+def pick_kc(cin_span, stride=1, dil=1, has_in2=False, W=None, coutp=None, out_f32=False):
+    """Channel chunk of the tensor-core conv.  The halo kernel (stride 1, dilation <= 16, one input) takes 64-channel
     chunks with a zero-padded partial last chunk; the per-tap kernel needs cin_span % kc == 0."""
     import os
     exact = 64 if cin_span % 64 == 0 else (32 if cin_span % 32 == 0 else 16)
-    halo = int(os.environ.get("PWC_TC_HALO", "1")) and stride == 1 and 1 <= dil <= 8 and not has_in2
+    ydense = int(os.environ.get("PWC_TC_WM_YDENSE_MINDIL", "8")) <= 16 and int(os.environ.get("PWC_TC_WM", "1"))
+    # dilation 9..16: the y-dense mode views W as (W/dil, dil) and stores 32-channel groups
+    wide = ydense and W is not None and W % dil == 0 and coutp is not None and coutp % 32 == 0 and not out_f32
+    halo = int(os.environ.get("PWC_TC_HALO", "1")) and stride == 1 and 1 <= dil <= (16 if wide else 8) and not has_in2
+    # 96 channels at dilation 16: three exact 32-channel chunks halve the halo-tile traffic of two padded 64-channel ones
+    # (dc_conv5 on B200: 100 us per-tap kernel -> 75 us kc 64 -> 52 us kc 32)
+    if halo and dil > 8 and cin_span % 64 and cin_span % 32 == 0 and int(os.environ.get("PWC_DIL16_KC", "32")) == 32:
+        return 32
     if halo:
         return 64      # thin layers too: 128-byte rows (SWIZZLE_128B) are what the tensor pipe reads fast
     return exact
@@ -108,8 +115,8 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     assert x.dtype == torch.bfloat16
     cout, cin = weight.shape[:2]
     span = cin_span if cin_span is not None else (cin + 15) // 16 * 16
-    kc = pick_kc(span, stride, dil)
     coutp = 128 if ts else (cout + 15) // 16 * 16
+    kc = pick_kc(span, stride, dil, W=W, coutp=coutp, out_f32=bool(out_f32))
     wp = torch.empty(9 * ((span + kc - 1) // kc) * kc * coutp, device=x.device, dtype=torch.bfloat16)
     mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
     w32 = weight.detach().float().contiguous()

@@ -18,6 +18,8 @@ TC_CASES = [
     (16, 16, 1, 1, 2, 16, 32, 0), (96, 64, 1, 16, 1, 40, 64, 0), (128, 96, 1, 8, 1, 24, 40, 0),
     (576, 128, 1, 1, 1, 16, 32, 0), (208, 208, 1, 1, 2, 7, 16, 0), (576, 2, 1, 1, 1, 16, 32, 1),
     (32, 2, 1, 1, 2, 16, 32, 1), (480, 64, 1, 1, 1, 16, 16, 0), (64, 96, 2, 1, 2, 32, 64, 0), (16, 32, 2, 1, 1, 32, 32, 0),
+    # dilation 16: y-dense x-split mode (W % 16 == 0), its fallback (ragged W), dilation 8 y-dense with ragged H and W
+    (64, 64, 1, 16, 2, 50, 96, 0), (96, 64, 1, 16, 1, 40, 70, 0), (128, 96, 1, 8, 2, 61, 43, 0), (96, 32, 1, 16, 1, 112, 256, 0),
 ]
 
 
