@@ -503,6 +503,7 @@ static int launch_nchw(const WarpCorrParams& p, cudaStream_t s) {
 
 #include "warp_corr_tc.cuh"
 #include "warp_corr_small.cuh"
+#include "warp_corr_mma.cuh"
 
 extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void* f2, long f2_pitch,
                                        const float* flow, long flow_pitch, float flow_scale,
@@ -524,6 +525,13 @@ extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void
   if (C % 4 || f1_pitch % 4 || f2_pitch % 4 || (flow && (flow_pitch % 2))) return (int)cudaErrorInvalidValue;
   if (out_pitch * 32 > 0x7fffffffL) return (int)cudaErrorInvalidValue;
   if (dtype == PWC_BF16) {
+    // warp-level tensor-core kernel (warp_corr_mma.cuh): PWC_CORR_MMA = 0 off | 1 wide-feature levels (C > 64) | 2 all
+    static const int use_mma = []() { const char* e = getenv("PWC_CORR_MMA"); return e ? atoi(e) : 1; }();
+    const bool mma_ok = use_mma && (use_mma >= 2 || C > 64) && C >= 16 && C <= 256 && f1_pitch % 8 == 0 && f2_pitch % 8 == 0 &&
+                        ((reinterpret_cast<uintptr_t>(f1) | reinterpret_cast<uintptr_t>(f2)) & 15) == 0 &&
+                        (reinterpret_cast<uintptr_t>(out) & 15) == 0 && out_pitch % 8 == 0 && slope >= 0.f && slope <= 1.f &&
+                        get_encode_tiled() != nullptr;
+    if (mma_ok) return launch_warp_corr_mma(p, s);
     // thin-feature levels (C <= 64: pyramid levels 2 and 3) run the cost volume on the tensor cores
     static const int use_tc = []() { const char* e = getenv("PWC_CORR_TC"); return e ? atoi(e) : 1; }();
     const bool tc_ok = use_tc && (C == 16 || C == 32 || C == 64) && f1_pitch % 8 == 0 && f2_pitch % 8 == 0 &&

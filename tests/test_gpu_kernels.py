@@ -116,19 +116,25 @@ def test_fused_warp_corr_bf16_features():
     (2, 64, 19, 40, False), (3, 32, 64, 96, True),
     # C > 64: small-level kernel (csrc/warp_corr_small.cuh), the level 4/5/6 shapes and a ragged one
     (2, 96, 28, 64, True), (2, 128, 14, 32, True), (2, 196, 7, 16, False), (1, 100, 9, 45, True),
+    # image-2 features with the pyramid buffers' padded pitch (C rounded up to 16): warp-level MMA kernel
+    # (csrc/warp_corr_mma.cuh) at every width, incl. the half channel group of C = 196 / 100 and 16-pixel strips
+    (2, 196, 7, 16, False, 16), (2, 196, 7, 16, True, 16), (1, 100, 9, 45, True, 16), (2, 128, 14, 32, True, 16),
+    (1, 96, 28, 64, True, 16), (1, 32, 37, 50, True, 16), (1, 64, 11, 16, True, 16), (8, 32, 112, 256, True, 16),
 ])
 def test_fused_warp_corr_tensor_core_path(case):
     """bf16 features inside concat-buffer slices (pitch 544+C: f1 at channel 544, cost volume at 448), ragged shapes, more
     items than one wave.  Bar: bf16 rounding of the output plus of the warped operand (both 2^-9 relative)."""
     from opticalflow_b200 import ops
-    B, C, H, W, with_flow = case
+    B, C, H, W, with_flow = case[:5]
+    f2_round = case[5] if len(case) > 5 else 1
     f1, f2, flow = O.corr_microbench_inputs(2, B, H, W, C, with_flow=with_flow)
     f1b, f2b = f1.bfloat16(), f2.bfloat16()
     ref = O.warp_corr_lrelu(f1b.float(), f2b.float(), flow, 5.0)
     d = _dev()
     cat = torch.full((B, H, W, 544 + 32 * ((C + 31) // 32)), 7.0, device=d, dtype=torch.bfloat16)
     cat[..., 544:544 + C] = f1b.permute(0, 2, 3, 1).to(d)
-    f2n = f2b.permute(0, 2, 3, 1).contiguous().to(d)
+    f2n = torch.full((B, H, W, (C + f2_round - 1) // f2_round * f2_round), 3.0, device=d, dtype=torch.bfloat16)[..., :C]
+    f2n.copy_(f2b.permute(0, 2, 3, 1))
     fl = None if flow is None else flow.permute(0, 2, 3, 1).contiguous().to(d)
     ops.warp_corr_lrelu(cat[..., 544:544 + C], f2n, fl, 5.0, layout="nhwc", out=cat[..., 448:529])
     torch.cuda.synchronize()
