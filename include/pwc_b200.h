@@ -187,6 +187,32 @@ int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_c
                            float* out_b, long out_b_pitch,
                            int N, int Hin, int Win, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * (8) Driver-side pre/post-processing and metrics on the device.
+ *   pwc_preprocess_u8_fwd : frame_to_tensor + pad_to_multiple_of_64 + torch.cat([t1p, t2p], 1)
+ *       (pwc_extract_flow_video.py:27-42,197-205; inference_kitti.py:53-63,216-217; script_pwc.py:61-71).
+ *       im1, im2 : B uint8 frames [H][W][3] each (interleaved, as cv2 / imageio deliver them), `row_stride` bytes
+ *                  between rows, `img_stride` bytes between frames; swap_rb = 1 reverses the channel order
+ *                  (cv2.COLOR_BGR2RGB / the [:, :, ::-1] of script_pwc.py:63).
+ *       out      : [B,6,Hp,Wp] fp32 NCHW = value / 255 (correctly rounded fp32 division), channels 0-2 frame 1,
+ *                  3-5 frame 2, replicate-padded at the bottom / right to Hp x Wp (Wp % 4 == 0).
+ *   pwc_flow_postprocess_fwd : unpad + flow_resize + scale (inference_kitti.py:66-91,219-223; script_pwc.py:72-81).
+ *       flow : [B,2,h,w] fp32 NCHW; its top-left crop_h x crop_w window (the "unpadded" flow) is resized to H x W with
+ *              bilinear interpolation, align_corners = True (F.interpolate), u scaled by W/crop_w, v by H/crop_h, both by
+ *              `mult` (20.0 for pwc_net.pth.tar flows, script_pwc.py:72).
+ *       out  : [B,2,H,W] NCHW, or [B,H,W,2] when out_hwc = 1 (the [H,W,2] array the .flo / KITTI writers take).
+ *   pwc_flow_metrics_fwd : EPE and Fl-all sums over valid pixels (inference_kitti.py:94-128, inference.py:105-159).
+ *       pred, gt : [B,2,H,W] (layout_hwc = 0) or [B,H,W,2] (1) fp32; valid : [B,H,W] uint8 or NULL (all valid).
+ *       acc      : [B][3] fp64 (zeroed here): sum of EPE over valid pixels, #valid, #outliers with
+ *                  EPE > max(abs_thr, rel_thr * |gt|) (3 px / 5% for KITTI).  EPE = acc[0]/acc[1], Fl = 100*acc[2]/acc[1].
+ * ------------------------------------------------------------------------------------------ */
+int pwc_preprocess_u8_fwd(const uint8_t* im1, const uint8_t* im2, long img_stride, long row_stride,
+                          int B, int H, int W, int Hp, int Wp, int swap_rb, float* out, void* stream);
+int pwc_flow_postprocess_fwd(const float* flow, int B, int h, int w, int crop_h, int crop_w,
+                             float* out, int H, int W, float mult, int out_hwc, void* stream);
+int pwc_flow_metrics_fwd(const float* pred, const float* gt, const uint8_t* valid, int B, int H, int W,
+                         int layout_hwc, float abs_thr, float rel_thr, double* acc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
