@@ -148,3 +148,92 @@ def run_sharded(model, n_pairs, load_batch, sink, B, H, W, device, rank=None, wo
     pipe.run((load_batch(s, c) for s, c in todo),
              sink=lambda i, f: sink(todo[i][0], todo[i][1], f[:todo[i][1]]))
     return hi - lo
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Video stream: uint8 frames in, flows out (pwc_extract_flow_video.py:process_video / process_frame_pair :190-215)
+# ------------------------------------------------------------------------------------------------------------------
+class VideoFlowPipeline:
+    """Consecutive frame pairs (t, t+1) of one uint8 video, batched B pairs at a time, everything after the H2D copy of
+    the raw frames on the GPU: frame_to_tensor + pad_to_multiple_of_64 + cat (ONE kernel, prepost.frames_to_input, reading
+    frames t and t+1 of the same upload through two base pointers), the forward, then unpad (+ optional resize to the
+    frame size) and the x`mult` flow scale (ONE kernel, prepost.postprocess_flow).  Per pair 3 bytes/pixel go up instead
+    of the 24 bytes/pixel of the fp32 [1,6,H,W] tensor the reference uploads.  Three streams as in FlowPipeline."""
+
+    def __init__(self, model, B, H, W, device, swap_rb=True, mult=20.0, full_res=False, depth=2):
+        from . import prepost
+        if device.type != "cuda":
+            raise RuntimeError("VideoFlowPipeline: CUDA device required -- this build has no CPU fallback")
+        self.pp = prepost
+        self.model, self.B, self.H, self.W, self.device, self.depth = model, B, H, W, device, depth
+        self.swap_rb, self.mult, self.full_res = swap_rb, float(mult), full_res
+        self.ph, self.pw = prepost.pad_amounts(H, W)
+        Hp, Wp = H + self.ph, W + self.pw
+        self.Hp, self.Wp = Hp, Wp
+        # the reference cuts the image-pixel pads from the quarter-resolution flow (unpad quirk, see prepost.unpad)
+        self.oh, self.ow = (H, W) if full_res else (Hp // 4 - self.ph, Wp // 4 - self.pw)
+        with torch.cuda.device(device):
+            self.plan = model._plan(B, Hp, Wp, device)
+            self.plan.pack_weights(model)
+            self.s_in, self.s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
+            self.f_dev = [torch.empty(B + 1, H, W, 3, device=device, dtype=torch.uint8) for _ in range(depth)]
+            self.x_dev = self.plan.x_static if hasattr(self.plan, "x_static") else torch.empty(B, 6, Hp, Wp, device=device)
+            self.o_dev = [torch.empty(B, 2, self.oh, self.ow, device=device) for _ in range(depth)]
+            self.o_host = [torch.empty(B, 2, self.oh, self.ow).pin_memory() for _ in range(depth)]
+            ev = lambda: [torch.cuda.Event() for _ in range(depth)]  # noqa: E731
+            self.in_ready, self.in_free, self.out_ready, self.out_free, self.out_done = ev(), ev(), ev(), ev(), ev()
+            self.plan.run(self.x_dev.zero_())
+            torch.cuda.synchronize(device)
+        self.launches_per_batch = self.plan.launches + 2
+
+    def _compute(self, s):
+        f = self.f_dev[s]
+        self.pp.frames_to_input(f[:-1], f[1:], swap_rb=self.swap_rb, out=self.x_dev)
+        flow2 = self.plan.run() if hasattr(self.plan, "x_static") else self.plan.run(self.x_dev)
+        lib, _lib = self.pp._lib.load(), self.pp._lib
+        h, w = self.Hp // 4, self.Wp // 4
+        e = lib.pwc_flow_postprocess_fwd(_lib.ptr(flow2), self.B, h, w, h - self.ph, w - self.pw, _lib.ptr(self.o_dev[s]),
+                                         self.oh, self.ow, self.mult, 0, _lib.stream_handle())
+        _lib.check(e, "pwc_flow_postprocess_fwd")
+
+    @torch.no_grad()
+    def run(self, frames, sink=None):
+        """frames: pinned uint8 tensor [N,H,W,3] (N >= 2).  sink(t0, count, flow_host) receives the flows of pairs
+        (t0+k, t0+k+1), k < count, as [count,2,oh,ow] fp32 (pinned, reused after `depth` batches).  Returns N-1."""
+        if frames.dtype != torch.uint8 or frames.dim() != 4 or tuple(frames.shape[1:]) != (self.H, self.W, 3):
+            raise RuntimeError(f"VideoFlowPipeline: uint8 [N,{self.H},{self.W},3] frames expected, got {tuple(frames.shape)}")
+        n_pairs = frames.shape[0] - 1
+        todo = batches(0, n_pairs, self.B)
+        cs = torch.cuda.current_stream(self.device)
+        pending = []
+
+        def deliver(j, sj):
+            self.out_done[sj].synchronize()
+            if sink is not None:
+                sink(todo[j][0], todo[j][1], self.o_host[sj][:todo[j][1]])
+
+        with torch.cuda.device(self.device):
+            for i, (t0, cnt) in enumerate(todo):
+                s = i % self.depth
+                if len(pending) == self.depth:
+                    deliver(*pending.pop(0))
+                with torch.cuda.stream(self.s_in):
+                    self.s_in.wait_event(self.in_free[s])
+                    self.f_dev[s][:cnt + 1].copy_(frames[t0:t0 + cnt + 1], non_blocking=True)
+                    if cnt < self.B:                      # ragged tail: repeat the last frame (its flows are dropped)
+                        self.f_dev[s][cnt + 1:] = self.f_dev[s][cnt:cnt + 1]
+                    self.in_ready[s].record(self.s_in)
+                cs.wait_event(self.in_ready[s])
+                cs.wait_event(self.out_free[s])
+                self._compute(s)
+                self.in_free[s].record(cs)
+                self.out_ready[s].record(cs)
+                with torch.cuda.stream(self.s_out):
+                    self.s_out.wait_event(self.out_ready[s])
+                    self.o_host[s].copy_(self.o_dev[s], non_blocking=True)
+                    self.out_done[s].record(self.s_out)
+                    self.out_free[s].record(self.s_out)
+                pending.append((i, s))
+            for j, sj in pending:
+                deliver(j, sj)
+        return n_pairs
