@@ -66,10 +66,12 @@ def test_conv3x3_tc_matches_torch(case):
     assert (out - ref).abs().max().item() <= tol
 
 
-def test_conv1a_bf16_matches_torch():
+@pytest.mark.parametrize("shape", [(2, 64, 96), (1, 72, 200), (2, 130, 516), (1, 448, 1024)])
+def test_conv1a_bf16_matches_torch(shape):
+    """tiles of 8 x 128 output pixels: ragged in both directions, one tile, many tiles"""
     from opticalflow_b200 import ops
     g = torch.Generator().manual_seed(5)
-    x = torch.rand(2, 6, 64, 96, generator=g)
+    x = torch.rand(shape[0], 6, shape[1], shape[2], generator=g)
     w = torch.randn(16, 3, 3, 3, generator=g) / 5.0
     b = torch.randn(16, generator=g) * 0.1
     d = torch.device("cuda:0")
