@@ -188,6 +188,23 @@ int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_c
                            int N, int Hin, int Win, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * (7b) 3x3 convolution for the small pyramid levels (5, 6): same operator as (6) -- conv(), PWCNet.py:26-30, call sites
+ *      PWCNet.py:186-195 (conv5a..conv6b) and PWCNet.py:202-206,217-221 (conv6_0..4, conv5_0..4) -- cut three ways
+ *      (pixel tile x output-channel slice x K split inside the CTA) on warp-level bf16 MMA so that layers of a few
+ *      thousand pixels fill the machine; stateless (no handle, no tensor maps).
+ *   in / in2 : bf16 NHWC + pitch; images >= n_split_in read in2 (NULL: one input).  Channels [coff, coff + cin_span).
+ *   w_packed : pwc_pack_conv_weight_bf16(..., kc = 64, coutp): [9][cin_span/64][coutp][64]; coutp % 16 == 0
+ *   out/out2 : bf16 NHWC + pitch, channels [coff, coff + coutp); images >= n_split go to out2 (NULL: one output)
+ *   stride 1 | 2, padding 1; bias + LeakyReLU(slope) fused, 0 <= slope <= 1.
+ * ------------------------------------------------------------------------------------------ */
+int pwc_conv3x3_mma_fwd(const void* in, long in_pitch, int in_coff,
+                        const void* in2, long in2_pitch, int in2_coff, int n_split_in, int cin_span,
+                        const void* w_packed, const float* bias, int cout, int coutp,
+                        void* out, long out_pitch, int out_coff,
+                        void* out2, long out2_pitch, int out2_coff, int n_split,
+                        int N, int H, int W, int stride, float slope, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * (8) Driver-side pre/post-processing and metrics on the device.
  *   pwc_preprocess_u8_fwd : frame_to_tensor + pad_to_multiple_of_64 + torch.cat([t1p, t2p], 1)
  *       (pwc_extract_flow_video.py:27-42,197-205; inference_kitti.py:53-63,216-217; script_pwc.py:61-71).

@@ -97,6 +97,13 @@ def _pfup_weights(lvl):
     return make
 
 
+# Layers routed to the warp-MMA small-level kernel (csrc/conv_mma_small.cu: pixel tile x channel slice x cluster K-split)
+# instead of the tcgen05 kernels.  Measured on B200 (batch 8, 1024x448; ncu): conv6_4 18.9 -> 9.6 us, conv6_3 17.1 ->
+# 12.6 us, conv6a / conv6b 31.3 -> 24.5 us; level-5 layers and the short-K level-6 layers are faster on tcgen05.
+_SMALL_DEFAULT = "conv6_3.0,conv6_4.0,conv6a.0,conv6b.0"
+SMALL_LAYERS = set(x for x in os.environ.get("PWC_MMA_SMALL_LAYERS", _SMALL_DEFAULT).split(",") if x and x != "none")
+
+
 class _TcLayer:
     __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups", "kkskip")
 
@@ -148,6 +155,10 @@ class PlanBF16:
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
             flops=None, ts=False, groups=None, kkskip=False):
+        if key in SMALL_LAYERS and dil == 1 and not out_f32 and not ts and groups is None and residual is None \
+                and (dst2 is None or dst2_coff == 0):
+            return self._small(key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride, slope, cmap, src2,
+                               src2_coff, dst2, dst2_coff, n_split, wfn, flops)
         L = _TcLayer()
         L.kkskip = bool(kkskip and span <= 64 and cmap is None and os.environ.get("PWC_TC_KKSKIP", "1") != "0")
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
@@ -176,6 +187,27 @@ class PlanBF16:
         ho, wo = (hin - 1) // stride + 1, (win - 1) // stride + 1
         self.op_info.append((key, flops if flops is not None else 2.0 * N * ho * wo * cout * cin * 9))
         self.ops.append(lambda st: _lib.check(lib.pwc_tc_conv_launch(h, st), key))
+
+    def _small(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride, slope, cmap, src2, src2_coff,
+               dst2, dst2_coff, n_split, wfn, flops):
+        """Same layer contract as _tc, launched through pwc_conv3x3_mma_fwd (weights packed with kc = 64)."""
+        L = _TcLayer()
+        L.kkskip, L.groups, L.handle = False, None, None
+        L.wfn, L.key, L.cin, L.cout, L.span, L.cmap = wfn, key, cin, cout, span, cmap
+        L.coutp, L.kc, L.wrows = _roundup(cout, 16), 64, cout
+        dev = self.device
+        L.w = torch.zeros(9 * _roundup(span, 64) * L.coutp, device=dev, dtype=BF)
+        L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
+        self.layers[key] = L
+        lib = self.lib
+        n_in = n_split if src2 is not None else N
+        n_out = n_split if dst2 is not None else N
+        args = (_lib.ptr(src), src.shape[-1], src_coff, _lib.ptr(src2), (src2.shape[-1] if src2 is not None else 0), src2_coff,
+                n_in, span, _lib.ptr(L.w), _lib.ptr(L.b), cout, L.coutp, _lib.ptr(dst), dst.shape[-1], dst_coff,
+                _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, n_out, N, hin, win, stride, slope)
+        ho, wo = (hin - 1) // stride + 1, (win - 1) // stride + 1
+        self.op_info.append((key, flops if flops is not None else 2.0 * N * ho * wo * cout * cin * 9))
+        self.ops.append(lambda st: _lib.check(lib.pwc_conv3x3_mma_fwd(*args, st), key))
 
     def _deconv(self, key, cin, src, src_coff, span, dst, dst_coff, hin, win, dst_b=None):
         dev = self.device

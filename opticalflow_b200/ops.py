@@ -188,3 +188,44 @@ def deconv4x4s2_c2(x, weight, bias, out_dtype=torch.float32, in_coff=0, cin_span
     _lib.check(e, "pwc_deconv4x4s2_c2_fwd")
     torch.cuda.current_stream().synchronize()
     return out, outb
+
+
+def conv3x3_mma_small(x, weight, bias, stride=1, slope=0.1, in_coff=0, cin_span=None, chan_map=None, x2=None, n_split_in=0,
+                      reps=1):
+    """Small-level bf16 conv (pwc_conv3x3_mma_fwd) on an NHWC bf16 tensor x [N,H,W,pitch]; weight torch [Cout,Cin,3,3] fp32.
+    x2: second input tensor for images >= n_split_in (as the stride-2 pyramid layers read im1 / im2 features)."""
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    if not x.is_cuda:
+        raise RuntimeError("conv3x3_mma_small: CUDA tensors required (no CPU fallback)")
+    N, H, W, pitch = x.shape
+    if x2 is not None:
+        N = n_split_in + x2.shape[0]
+    assert x.dtype == torch.bfloat16
+    cout, cin = weight.shape[:2]
+    span = cin_span if cin_span is not None else (cin + 7) // 8 * 8
+    coutp = (cout + 15) // 16 * 16
+    nchunk = (span + 63) // 64
+    wp = torch.empty(9 * nchunk * 64 * coutp, device=x.device, dtype=torch.bfloat16)
+    mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
+    w32 = weight.detach().float().contiguous()
+    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), cout, cin, span, 64, coutp, st), "pack")
+    ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    out = torch.full((N, ho, wo, coutp), 7.0, device=x.device, dtype=torch.bfloat16)
+    b32 = bias.detach().float().contiguous()
+
+    def launch():
+        e = lib.pwc_conv3x3_mma_fwd(_lib.ptr(x), pitch, in_coff, _lib.ptr(x2), (x2.shape[-1] if x2 is not None else 0), in_coff,
+                                    n_split_in, span, _lib.ptr(wp), _lib.ptr(b32), cout, coutp, _lib.ptr(out), coutp, 0,
+                                    None, 0, 0, N, N, H, W, stride, slope, st)
+        _lib.check(e, "pwc_conv3x3_mma_fwd")
+    launch()
+    if reps > 1:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps - 1):
+            launch()
+        e1.record(); e1.synchronize()
+        conv3x3_mma_small.last_ms = e0.elapsed_time(e1) / (reps - 1)
+    torch.cuda.current_stream().synchronize()
+    return out

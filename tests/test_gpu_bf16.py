@@ -151,3 +151,37 @@ def test_forward_bf16_random_bias_tracks_bf16_oracle():
     e_ref, e_simref = _epe(flow, ref).mean().item(), _epe(sim, ref).mean().item()
     print(f"random-bias: ours vs fp32 {e_ref:.4f} px, bf16-storage oracle vs fp32 {e_simref:.4f} px, absmax {ref.abs().max().item():.1f}")
     assert e_ref <= 2.0 * e_simref + 1e-3
+
+
+@pytest.mark.parametrize("case", [
+    # cin, cout, stride, N, H, W          (levels 5 / 6 of 1024x448 and ragged shapes; coutp = 208 for 196)
+    (81, 128, 1, 8, 7, 16), (565, 32, 1, 8, 7, 16), (196, 196, 1, 16, 7, 16), (213, 128, 1, 8, 14, 32),
+    (469, 64, 1, 2, 14, 32), (128, 196, 2, 4, 14, 32), (96, 128, 2, 2, 28, 64), (40, 24, 1, 3, 9, 21), (72, 48, 2, 1, 11, 19),
+])
+def test_conv3x3_mma_small_matches_torch(case):
+    """pwc_conv3x3_mma_fwd: every tile configuration the heuristic can pick plus the forced ones, stride 1 and 2."""
+    import os
+    from opticalflow_b200 import ops
+    cin, cout, stride, N, H, W = case
+    g = torch.Generator().manual_seed(cin * 7 + cout)
+    x = (torch.randn(N, cin, H, W, generator=g)).bfloat16()
+    w = torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin ** 0.5)
+    b = torch.randn(cout, generator=g) * 0.1
+    ref = F.leaky_relu(F.conv2d(x.float(), w.bfloat16().float(), b, stride=stride, padding=1), 0.1)
+    d = torch.device("cuda:0")
+    pitch = (cin + 7) // 8 * 8 + 8
+    xn = torch.full((N, H, W, pitch), 3.0, dtype=torch.bfloat16)           # neighbours of the slice must not leak in
+    xn[..., :cin] = x.permute(0, 2, 3, 1)
+    xn = xn.to(d)
+    out = ops.conv3x3_mma_small(xn, w.to(d), b.to(d), stride, 0.1, cin_span=cin)
+    coutp = out.shape[-1]
+    o = out.float().permute(0, 3, 1, 2).cpu()
+    tol = 1e-2 * ref.abs().max().item()
+    assert (o[:, :cout] - ref).abs().max().item() <= tol
+    assert (o[:, cout:] == 0).all()                                        # padded output channels are written as zeros
+    # two inputs (im1 / im2 feature tensors of the stride-2 pyramid layers)
+    if N % 2 == 0:
+        h = N // 2
+        out2 = ops.conv3x3_mma_small(xn[:h].contiguous(), w.to(d), b.to(d), stride, 0.1, cin_span=cin,
+                                     x2=xn[h:].contiguous(), n_split_in=h)
+        assert torch.equal(out2, out)
