@@ -119,6 +119,15 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def ncu_traffic(layer):
+    """DRAM bytes per launch of `layer` from the committed ncu --set full capture (profiles/r1_ncu_traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+    try:
+        return json.load(open(p)).get(layer, {}).get("bytes")
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def corr_microbench(dev, B, iters=20):
     """Fused warp+corr kernel over the 5 pyramid-level shapes of 1024x448 (BASELINE configs[1]); CUDA-event time of
     the kernel alone, L2 flushed between launches.  Algorithmic bytes: 4*B*H*W*(2C+81+(2 if L<6))."""
@@ -240,8 +249,10 @@ def run_ours(args):
         top = max(tc, key=lambda r: r[1])
         peak = peaks["bf16_tflops"]
         roof = {"bound": "tensor", "achieved": tc_f / tc_t / 1e12, "peak": peak, "unit": "TFLOP/s",
-                "frac": tc_f / tc_t / 1e12 / peak, "traffic": None,
-                "kernel": "conv_tc_wm_kernel / conv_tc_halo_kernel / conv_tc_kernel (tcgen05 3x3 convolutions)",
+                "frac": tc_f / tc_t / 1e12 / peak, "traffic": ncu_traffic(top[0]),
+                "traffic_note": f"DRAM bytes of ONE launch of the top layer ({top[0]}), ncu --set full (profiles/r1_ncu_traffic.json)",
+                "kernel": "conv_tc_wm_kernel / conv_tc_halo_kernel / conv_tc_kernel (tcgen05 3x3 convolutions) + "
+                          "conv_mma_small_kernel (level-6 layers)",
                 "launches_per_step": len(tc), "share_of_step": tc_t / all_t,
                 "top_launch": {"layer": top[0], "us": round(top[1] * 1e6, 1), "TFLOPs": round(top[2] / top[1] / 1e12, 1),
                                "frac": top[2] / top[1] / 1e12 / peak},
@@ -266,8 +277,9 @@ def run_ours(args):
                 lv[f"L{l}"] = {"us": round(t_ * 1e6, 2), "GBps": round(by / t_ / 1e9, 1)}
                 cb += by; ct += t_
         roof_corr = {"bound": "hbm", "achieved": cb / ct / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": cb / ct / 1e9 / peaks["hbm_gbs"], "traffic": None, "levels": lv,
-                     "kernel": "warp_corr_tc_kernel (levels 2,3: tcgen05) / warp_corr_nhwc_kernel (levels 4-6)",
+                     "frac": cb / ct / 1e9 / peaks["hbm_gbs"], "traffic": ncu_traffic("warp_corr2"),
+                     "traffic_note": "DRAM bytes of the level-2 launch alone (ncu --set full, profiles/r1_ncu_traffic.json)", "levels": lv,
+                     "kernel": "warp_corr_tc_kernel (levels 2,3: tcgen05) / warp_corr_mma_kernel (levels 4-6: mma.sync)",
                      "note": "the 5 cost-volume launches of one forward (bf16 features in the concat buffers), CUDA events, "
                              "each timed in sequence; algorithmic bytes B*H*W*(2*C*2 + 81*2 + 8)"}
     if roof is None:
