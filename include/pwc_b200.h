@@ -205,6 +205,23 @@ int pwc_conv3x3_mma_fwd(const void* in, long in_pitch, int in_coff,
                         int N, int H, int W, int stride, float slope, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * (7c) 3x3 convolution for the thin feature-pyramid layers (Cin, Cout in {16, 32, 64}): conv1aa, conv1b, conv2a, conv2aa,
+ *      conv2b, conv3a, conv3aa, conv3b (PWCNet.py:52-60, call sites PWCNet.py:184-195).  HBM bound: persistent CTAs,
+ *      weights resident in shared memory, double-buffered cp.async input patches, warp-level bf16 MMA, 16-byte stores.
+ *   in / in2 : bf16 NHWC + pitch, channels [coff, coff + cin); images >= n_split_in read in2 (NULL: one input)
+ *   w_packed : pwc_pack_conv_weight_bf16(..., cin_span = cin, kc = cin, coutp = cout): [9][cout][cin] bf16
+ *   out/out2 : bf16 NHWC + pitch, channels [coff, coff + cout); images >= n_split go to out2 (NULL: one output);
+ *              pitches and offsets multiples of 8 channels, bases 16-byte aligned
+ *   stride 1 | 2, padding 1; bias + LeakyReLU(slope) fused, 0 <= slope <= 1.
+ * ------------------------------------------------------------------------------------------ */
+int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
+                         const void* in2, long in2_pitch, int in2_coff, int n_split_in, int cin,
+                         const void* w_packed, const float* bias, int cout,
+                         void* out, long out_pitch, int out_coff,
+                         void* out2, long out2_pitch, int out2_coff, int n_split,
+                         int N, int H, int W, int stride, float slope, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * (8) Driver-side pre/post-processing and metrics on the device.
  *   pwc_preprocess_u8_fwd : frame_to_tensor + pad_to_multiple_of_64 + torch.cat([t1p, t2p], 1)
  *       (pwc_extract_flow_video.py:27-42,197-205; inference_kitti.py:53-63,216-217; script_pwc.py:61-71).

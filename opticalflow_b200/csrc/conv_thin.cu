@@ -1,0 +1,255 @@
+// 3x3 convolution for the THIN feature-pyramid layers (Cin, Cout in {16, 32, 64}; stride 1 or 2; bf16 NHWC):
+// conv1aa, conv1b, conv2a, conv2aa, conv2b, conv3a, conv3aa, conv3b of /root/reference/models/PWCNet.py:52-60
+// (call sites PWCNet.py:184-195), bias + LeakyReLU fused, second output / second input for the im1 | im2 halves.
+//
+// These layers are HBM bound (0.3-2.4 kFLOP per byte moved... i.e. 18-37 us of traffic at batch 8 against 5-15 us of tensor
+// time): what matters is that every byte is moved once, coalesced, with the copies of the next tile in flight while the
+// current one is multiplied -- not the MMA rate.  On the tcgen05 path their 128 x 256 tiles, TMEM round trip and
+// per-item pipeline fill cost 2-4x the traffic time.  Here:
+//   * persistent CTAs (grid = SMs x resident CTAs), the whole 3x3 x Cin x Cout weight set staged ONCE per CTA in shared
+//     memory (rows padded to an odd number of 16-byte chunks: conflict-free ldmatrix);
+//   * tile = 8 output rows x 32 or 64 pixels; its input patch (10 x 34|66, or 17 x 65 at stride 2) is double buffered
+//     and fetched with cp.async (zero fill = the convolution's padding) one tile ahead, addresses from a per-pixel table;
+//   * warp = one output row = two 16-pixel m-tiles; taps, stride and channel blocks are ldmatrix row addresses into
+//     the patch (implicit GEMM, no im2col); mma.sync.m16n8k16 bf16 with fp32 accumulators in registers;
+//   * epilogue: bias + LeakyReLU + bf16 in registers, a per-warp shared-memory transpose, 16-byte coalesced stores
+//     straight into the concat slice (or the second tensor for the im2 half of the batch).
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+#include "../../include/pwc_b200.h"
+
+namespace pwc {
+
+struct ThinConvParams {
+  const __nv_bfloat16* in; long in_pitch; int in_coff;
+  const __nv_bfloat16* in2; long in2_pitch; int in2_coff; int n_split_in;
+  const __nv_bfloat16* w; const float* bias; int cin, cout;
+  __nv_bfloat16* out; long out_pitch; int out_coff;
+  __nv_bfloat16* out2; long out2_pitch; int out2_coff; int n_split;
+  int N, H, W, Ho, Wo, stride; float slope;
+  int tiles_x, tiles_y, ntiles;
+  int ih, iw, pp, wp;                          // patch rows / columns, bytes per patch pixel, bytes per weight row
+  int off_patch, patch_bytes, off_ostg, off_tab;   // shared-memory layout (weights at 0)
+  int mp;                                      // 32-pixel m-tile pairs per tile row: tile = 8 rows x 32*mp pixels
+};
+
+__device__ __forceinline__ void thin_ldsm4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void thin_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void thin_cp16(uint32_t dst, const void* src, bool ok) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(src), "r"(ok ? 16 : 0) : "memory");
+}
+
+// NT = output-channel n-tiles (Cout = 8 NT), KS = 16-channel k steps per tap (Cin = 16 KS)
+template <int NT, int KS>
+__global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) {
+  extern __shared__ __align__(128) uint8_t thin_smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t sm0 = ptx::smem_addr(thin_smem);
+  const uint32_t w_addr = sm0, patch_addr = sm0 + p.off_patch;
+  constexpr int NCH = 2 * KS;                                   // 16-byte chunks per pixel / per weight row
+  constexpr int OP = NT * 16 + 16;                              // bytes per staged output pixel (padded)
+  uint8_t* ostg = thin_smem + p.off_ostg + warp * 16 * OP;
+
+  // ---- weights: [9 * Cout rows][Cin] bf16, once per CTA (independent of the previous kernel: before pdl_wait)
+  for (int e = tid; e < 9 * NT * 8 * NCH; e += 256) {
+    const int row = e / NCH, ch = e - row * NCH;
+    thin_cp16(w_addr + row * p.wp + ch * 16, p.w + (long)row * p.cin + ch * 8, true);
+  }
+  float bias2[NT][2];
+#pragma unroll
+  for (int j = 0; j < NT; ++j) {
+    bias2[j][0] = p.bias[j * 8 + 2 * (lane & 3)];
+    bias2[j][1] = p.bias[j * 8 + 2 * (lane & 3) + 1];
+  }
+  pdl_wait();
+  pdl_launch_dependents();
+
+  // per patch pixel, fixed for the whole kernel: shared-memory byte offset | (row << 16 | column); built once so that the
+  // per-tile staging loop has no divisions
+  uint2* tab = reinterpret_cast<uint2*>(thin_smem + p.off_tab);
+  const int npx = p.ih * p.iw;
+  for (int e = tid; e < npx; e += 256) {
+    const int r = e / p.iw, c = e - r * p.iw;
+    tab[e] = make_uint2((uint32_t)(e * p.pp), ((uint32_t)r << 16) | (uint32_t)c);
+  }
+  __syncthreads();
+
+  auto stage = [&](int tile, int buf) {
+    const int tx = tile % p.tiles_x; const int t2 = tile / p.tiles_x;
+    const int ty = t2 % p.tiles_y; const int n = t2 / p.tiles_y;
+    const bool sec = p.in2 != nullptr && n >= p.n_split_in;
+    const int sp = (int)(sec ? p.in2_pitch : p.in_pitch);
+    const int iy0 = ty * 8 * p.stride - 1, ix0 = tx * 32 * p.mp * p.stride - 1;
+    const __nv_bfloat16* src = sec ? p.in2 + ((long)(n - p.n_split_in) * p.H * p.W) * p.in2_pitch + p.in2_coff
+                                   : p.in + ((long)n * p.H * p.W) * p.in_pitch + p.in_coff;
+    const __nv_bfloat16* org = src + ((long)iy0 * p.W + ix0) * sp;       // may point before the tensor: only offset from
+    const uint32_t dst0 = patch_addr + buf * p.patch_bytes;
+    for (int e = tid; e < npx * NCH; e += 256) {
+      const uint2 t = tab[e / NCH];                                      // NCH is a power of two
+      const int ch = e & (NCH - 1);
+      const int r = (int)(t.y >> 16), c = (int)(t.y & 0xffffu);
+      const bool ok = (unsigned)(iy0 + r) < (unsigned)p.H && (unsigned)(ix0 + c) < (unsigned)p.W;
+      thin_cp16(dst0 + t.x + ch * 16, ok ? (const void*)(org + (r * p.W + c) * sp + ch * 8) : (const void*)src, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  int tile = blockIdx.x;
+  if (tile < p.ntiles) stage(tile, 0);                           // (commits the weight copies too)
+  const uint32_t a_lane = (uint32_t)(((warp * p.stride) * p.iw + (lane & 15) * p.stride) * p.pp + (lane >> 4) * 16);
+  const uint32_t b_lane = w_addr + (uint32_t)(((lane & 7) + ((lane >> 4) << 3)) * p.wp + ((lane >> 3) & 1) * 16);
+  uint32_t a_off[9];                                             // tap offsets inside the patch, fixed for the kernel
+#pragma unroll
+  for (int tap = 0; tap < 9; ++tap) a_off[tap] = (uint32_t)(((tap / 3) * p.iw + (tap % 3)) * p.pp);
+  const uint32_t a_m1 = (uint32_t)(16 * p.stride * p.pp), b_tap = (uint32_t)(NT * 8 * p.wp);
+  for (int it = 0; tile < p.ntiles; tile += gridDim.x, ++it) {
+    const int buf = it & 1;
+    const int next = tile + gridDim.x;
+    if (next < p.ntiles) {
+      stage(next, buf ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();                                             // patch of this tile (and the weights) visible to all warps
+
+    const int tx = tile % p.tiles_x; const int t2 = tile / p.tiles_x;
+    const int ty = t2 % p.tiles_y; const int n = t2 / p.tiles_y;
+    const int oy = ty * 8 + warp;
+    for (int pr = 0; pr < p.mp && oy < p.Ho; ++pr) {             // 32 pixels (two m-tiles) at a time
+      float acc[2][NT][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
+      const uint32_t a_base = patch_addr + buf * p.patch_bytes + a_lane + (uint32_t)pr * 2u * a_m1;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const uint32_t a_tap = a_base + a_off[tap];
+        const uint32_t bt = b_lane + tap * b_tap;
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          uint32_t a[2][4];
+          thin_ldsm4(a[0], a_tap + ks * 32);
+          thin_ldsm4(a[1], a_tap + a_m1 + ks * 32);
+#pragma unroll
+          for (int j = 0; j < NT; j += 2) {
+            uint32_t b[4];
+            thin_ldsm4(b, bt + (uint32_t)(j * 8 * p.wp) + ks * 32);
+            thin_mma(acc[0][j], a[0], b[0], b[1]); thin_mma(acc[0][j + 1], a[0], b[2], b[3]);
+            thin_mma(acc[1][j], a[1], b[0], b[1]); thin_mma(acc[1][j + 1], a[1], b[2], b[3]);
+          }
+        }
+      }
+      // ---- epilogue: registers -> per-warp staging [16 px][Cout] -> 16-byte coalesced stores
+      const bool second = p.out2 != nullptr && n >= p.n_split;
+      __nv_bfloat16* dst = second ? p.out2 + ((long)(n - p.n_split) * p.Ho * p.Wo) * p.out2_pitch + p.out2_coff
+                                  : p.out + ((long)n * p.Ho * p.Wo) * p.out_pitch + p.out_coff;
+      const long dp = second ? p.out2_pitch : p.out_pitch;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const float v0 = acc[m][j][2 * h] + bias2[j][0], v1 = acc[m][j][2 * h + 1] + bias2[j][1];
+            const __nv_bfloat162 hv = __floats2bfloat162_rn(fmaxf(v0, v0 * p.slope), fmaxf(v1, v1 * p.slope));
+            *reinterpret_cast<__nv_bfloat162*>(ostg + ((lane >> 2) + 8 * h) * OP + j * 16 + 4 * (lane & 3)) = hv;
+          }
+        __syncwarp();
+        const int ox0 = (tx * p.mp + pr) * 32 + m * 16;
+#pragma unroll
+        for (int c = lane; c < 16 * NT; c += 32) {
+          const int px = c / NT, part = c - px * NT;
+          if (ox0 + px < p.Wo) {
+            const uint4 v = *reinterpret_cast<const uint4*>(ostg + px * OP + part * 16);
+            *reinterpret_cast<uint4*>(dst + ((long)oy * p.Wo + ox0 + px) * dp + part * 8) = v;
+          }
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();                                             // every warp is done with this buffer before it is refilled
+  }
+}
+
+template <int NT, int KS>
+static int launch_thin(ThinConvParams& p, cudaStream_t s) {
+  static int attr_dev = -1, num_sms = 0, max_ctas = 1;
+  int dev = 0; cudaGetDevice(&dev);
+  if (attr_dev != dev) {
+    cudaError_t e = cudaFuncSetAttribute(conv_thin_kernel<NT, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (num_sms <= 0) num_sms = 148;
+    attr_dev = dev;
+  }
+  const int wbytes = 9 * NT * 8 * p.wp;
+  int smem = 0;
+  static const int mp_env = []() { const char* e = getenv("PWC_THIN_MP"); return e ? atoi(e) : 0; }();
+  for (p.mp = (mp_env == 1 || p.Wo <= 32) ? 1 : 2; p.mp >= 1; --p.mp) {   // 64-pixel tiles when two patch buffers fit
+    p.tiles_x = cdiv(p.Wo, 32 * p.mp);
+    p.iw = (32 * p.mp - 1) * p.stride + 3;
+    p.off_patch = (wbytes + 127) & ~127;
+    p.patch_bytes = (p.ih * p.iw * p.pp + 127) & ~127;
+    p.off_ostg = p.off_patch + 2 * p.patch_bytes;
+    p.off_tab = p.off_ostg + 8 * 16 * (NT * 16 + 16);
+    smem = p.off_tab + p.ih * p.iw * 8;
+    if (smem <= 113 * 1024 || (p.mp == 1 && smem <= 227 * 1024)) break;   // keep two CTAs per SM if the wide tile allows it
+  }
+  if (p.mp < 1) return (int)cudaErrorInvalidValue;
+  const long nt = (long)p.N * p.tiles_x * p.tiles_y;
+  if (nt > 0x7fffffffL) return (int)cudaErrorInvalidValue;
+  p.ntiles = (int)nt;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_ctas, conv_thin_kernel<NT, KS>, 256, smem) != cudaSuccess || max_ctas < 1)
+    max_ctas = 1;
+  const long slots = (long)num_sms * max_ctas;
+  const int grid = (int)(p.ntiles < slots ? p.ntiles : slots);
+  return (int)launch_pdl(conv_thin_kernel<NT, KS>, dim3(grid), dim3(256), smem, s, p);
+}
+
+}  // namespace pwc
+
+extern "C" int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
+                                    const void* in2, long in2_pitch, int in2_coff, int n_split_in, int cin,
+                                    const void* w_packed, const float* bias, int cout,
+                                    void* out, long out_pitch, int out_coff,
+                                    void* out2, long out2_pitch, int out2_coff, int n_split,
+                                    int N, int H, int W, int stride, float slope, void* stream) {
+  using namespace pwc;
+  const bool cin_ok = cin == 16 || cin == 32 || cin == 64, cout_ok = cout == 16 || cout == 32 || cout == 64;
+  if (N <= 0 || H <= 0 || W <= 0 || (stride != 1 && stride != 2) || !cin_ok || !cout_ok ||
+      (in_pitch & 7) || (in_coff & 7) || (in2 && ((in2_pitch & 7) || (in2_coff & 7))) ||
+      (out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7))) || slope < 0.f || slope > 1.f ||
+      ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(in2) | reinterpret_cast<uintptr_t>(out) |
+        reinterpret_cast<uintptr_t>(out2) | reinterpret_cast<uintptr_t>(w_packed)) & 15))
+    return (int)cudaErrorInvalidValue;
+  ThinConvParams p;
+  p.in = reinterpret_cast<const __nv_bfloat16*>(in); p.in_pitch = in_pitch; p.in_coff = in_coff;
+  p.in2 = reinterpret_cast<const __nv_bfloat16*>(in2); p.in2_pitch = in2_pitch; p.in2_coff = in2_coff; p.n_split_in = n_split_in;
+  p.w = reinterpret_cast<const __nv_bfloat16*>(w_packed); p.bias = bias; p.cin = cin; p.cout = cout;
+  p.out = reinterpret_cast<__nv_bfloat16*>(out); p.out_pitch = out_pitch; p.out_coff = out_coff;
+  p.out2 = reinterpret_cast<__nv_bfloat16*>(out2); p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = n_split;
+  p.N = N; p.H = H; p.W = W; p.stride = stride; p.slope = slope;
+  p.Ho = (H - 1) / stride + 1; p.Wo = (W - 1) / stride + 1;
+  p.tiles_y = cdiv(p.Ho, 8);
+  p.ih = 7 * stride + 3;
+  p.pp = 2 * cin + 16; p.wp = 2 * cin + 16;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int nt8 = cout / 8, ks = cin / 16;
+#define PWC_THIN(NTv, KSv) if (nt8 == NTv && ks == KSv) return launch_thin<NTv, KSv>(p, s)
+  PWC_THIN(2, 1); PWC_THIN(4, 1); PWC_THIN(8, 1);
+  PWC_THIN(2, 2); PWC_THIN(4, 2); PWC_THIN(8, 2);
+  PWC_THIN(2, 4); PWC_THIN(4, 4); PWC_THIN(8, 4);
+#undef PWC_THIN
+  return (int)cudaErrorInvalidValue;
+}

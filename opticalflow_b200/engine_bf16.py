@@ -104,6 +104,12 @@ _SMALL_DEFAULT = "conv6_3.0,conv6_4.0,conv6a.0,conv6b.0"
 SMALL_LAYERS = set(x for x in os.environ.get("PWC_MMA_SMALL_LAYERS", _SMALL_DEFAULT).split(",") if x and x != "none")
 
 
+# Thin pyramid layers routed to the persistent warp-MMA kernel (csrc/conv_thin.cu).  Measured on B200 (batch 8): conv2a
+# (16 -> 32, stride 2) 62.7 -> 41.6 us, conv2b 44 -> 41 us; the other stride-1 layers are on par with or slower than the tcgen05
+# space-to-depth path (conv1aa 60.8 vs 58.7 us, conv3aa 37 vs 23 us).
+THIN_LAYERS = set(x for x in os.environ.get("PWC_THIN_LAYERS", "conv2a.0,conv2b.0").split(",") if x and x != "none")
+
+
 class _TcLayer:
     __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups", "kkskip")
 
@@ -155,6 +161,10 @@ class PlanBF16:
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
             flops=None, ts=False, groups=None, kkskip=False):
+        if key in THIN_LAYERS and dil == 1 and not out_f32 and not ts and groups is None and residual is None and cmap is None \
+                and wfn is None and cin == span and cin in (16, 32, 64) and cout in (16, 32, 64) and not (stride == 2 and cin > 16):
+            return self._thin(key, cin, cout, src, src_coff, dst, dst_coff, N, hin, win, stride, slope, src2, src2_coff, dst2,
+                              dst2_coff, n_split)
         if key in SMALL_LAYERS and dil == 1 and not out_f32 and not ts and groups is None and residual is None \
                 and (dst2 is None or dst2_coff == 0):
             return self._small(key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride, slope, cmap, src2,
@@ -187,6 +197,26 @@ class PlanBF16:
         ho, wo = (hin - 1) // stride + 1, (win - 1) // stride + 1
         self.op_info.append((key, flops if flops is not None else 2.0 * N * ho * wo * cout * cin * 9))
         self.ops.append(lambda st: _lib.check(lib.pwc_tc_conv_launch(h, st), key))
+
+    def _thin(self, key, cin, cout, src, src_coff, dst, dst_coff, N, hin, win, stride, slope, src2, src2_coff, dst2, dst2_coff,
+              n_split):
+        """Same layer contract as _tc, launched through pwc_conv3x3_thin_fwd (weights [9][cout][cin])."""
+        L = _TcLayer()
+        L.kkskip, L.groups, L.handle, L.wfn, L.cmap = False, None, None, None, None
+        L.key, L.cin, L.cout, L.span, L.coutp, L.kc, L.wrows = key, cin, cout, cin, cout, cin, cout
+        dev = self.device
+        L.w = torch.zeros(9 * cin * cout, device=dev, dtype=BF)
+        L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
+        self.layers[key] = L
+        lib = self.lib
+        n_in = n_split if src2 is not None else N
+        n_out = n_split if dst2 is not None else N
+        args = (_lib.ptr(src), src.shape[-1], src_coff, _lib.ptr(src2), (src2.shape[-1] if src2 is not None else 0), src2_coff,
+                n_in, cin, _lib.ptr(L.w), _lib.ptr(L.b), cout, _lib.ptr(dst), dst.shape[-1], dst_coff,
+                _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, n_out, N, hin, win, stride, slope)
+        ho, wo = (hin - 1) // stride + 1, (win - 1) // stride + 1
+        self.op_info.append((key, 2.0 * N * ho * wo * cout * cin * 9))
+        self.ops.append(lambda st: _lib.check(lib.pwc_conv3x3_thin_fwd(*args, st), key))
 
     def _small(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride, slope, cmap, src2, src2_coff,
                dst2, dst2_coff, n_split, wfn, flops):

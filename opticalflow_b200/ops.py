@@ -229,3 +229,39 @@ def conv3x3_mma_small(x, weight, bias, stride=1, slope=0.1, in_coff=0, cin_span=
         conv3x3_mma_small.last_ms = e0.elapsed_time(e1) / (reps - 1)
     torch.cuda.current_stream().synchronize()
     return out
+
+
+def conv3x3_thin(x, weight, bias, stride=1, slope=0.1, in_coff=0, x2=None, n_split_in=0, out=None, out_coff=0, reps=1):
+    """Thin-layer bf16 conv (pwc_conv3x3_thin_fwd): x [N,H,W,pitch] bf16 NHWC, weight torch [Cout,Cin,3,3] fp32 with
+    Cin, Cout in {16, 32, 64}; x2: second input for images >= n_split_in."""
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    if not x.is_cuda:
+        raise RuntimeError("conv3x3_thin: CUDA tensors required (no CPU fallback)")
+    N, H, W, pitch = x.shape
+    if x2 is not None:
+        N = n_split_in + x2.shape[0]
+    cout, cin = weight.shape[:2]
+    wp = torch.empty(9 * cout * cin, device=x.device, dtype=torch.bfloat16)
+    w32 = weight.detach().float().contiguous()
+    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(w32), _lib.ptr(wp), None, cout, cin, cin, cin, cout, st), "pack")
+    ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    if out is None:
+        out = torch.full((N, ho, wo, cout), 7.0, device=x.device, dtype=torch.bfloat16)
+    b32 = bias.detach().float().contiguous()
+
+    def launch():
+        e = lib.pwc_conv3x3_thin_fwd(_lib.ptr(x), pitch, in_coff, _lib.ptr(x2), (x2.shape[-1] if x2 is not None else 0), in_coff,
+                                     n_split_in, cin, _lib.ptr(wp), _lib.ptr(b32), cout, _lib.ptr(out), out.shape[-1], out_coff,
+                                     None, 0, 0, N, N, H, W, stride, slope, st)
+        _lib.check(e, "pwc_conv3x3_thin_fwd")
+    launch()
+    if reps > 1:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps - 1):
+            launch()
+        e1.record(); e1.synchronize()
+        conv3x3_thin.last_ms = e0.elapsed_time(e1) / (reps - 1)
+    torch.cuda.current_stream().synchronize()
+    return out

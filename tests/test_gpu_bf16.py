@@ -185,3 +185,47 @@ def test_conv3x3_mma_small_matches_torch(case):
         out2 = ops.conv3x3_mma_small(xn[:h].contiguous(), w.to(d), b.to(d), stride, 0.1, cin_span=cin,
                                      x2=xn[h:].contiguous(), n_split_in=h)
         assert torch.equal(out2, out)
+
+
+@pytest.mark.parametrize("case", [
+    # cin, cout, stride, N, H, W     (the 8 pyramid layers' channel pairs; ragged tiles; more tiles than resident CTAs)
+    (16, 16, 1, 2, 24, 40), (16, 32, 2, 2, 30, 70), (32, 32, 1, 1, 9, 33), (16, 64, 2, 3, 17, 31), (64, 64, 1, 2, 16, 64),
+    (16, 16, 1, 4, 224, 512), (16, 32, 2, 2, 224, 512), (64, 32, 1, 1, 8, 32), (16, 16, 2, 1, 5, 7), (32, 64, 1, 2, 56, 128),
+])
+def test_conv3x3_thin_matches_torch(case):
+    """pwc_conv3x3_thin_fwd against torch conv2d on the same bf16-rounded operands; channel slices of wider tensors."""
+    from opticalflow_b200 import ops
+    cin, cout, stride, N, H, W = case
+    g = torch.Generator().manual_seed(cin * 3 + cout + stride)
+    x = torch.randn(N, cin, H, W, generator=g).bfloat16()
+    w = torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin ** 0.5)
+    b = torch.randn(cout, generator=g) * 0.1
+    ref = F.leaky_relu(F.conv2d(x.float(), w.bfloat16().float(), b, stride=stride, padding=1), 0.1)
+    d = torch.device("cuda:0")
+    xn = torch.full((N, H, W, cin + 16), 3.0, dtype=torch.bfloat16)           # input slice at channel offset 8
+    xn[..., 8:8 + cin] = x.permute(0, 2, 3, 1)
+    ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    out = torch.full((N, ho, wo, cout + 24), 7.0, device=d, dtype=torch.bfloat16)   # output slice at channel offset 16
+    ops.conv3x3_thin(xn.to(d), w.to(d), b.to(d), stride, 0.1, in_coff=8, out=out, out_coff=16)
+    o = out[..., 16:16 + cout].float().permute(0, 3, 1, 2).cpu()
+    assert (o - ref).abs().max().item() <= 1e-2 * ref.abs().max().item()
+    assert (out[..., :16] == 7.0).all() and (out[..., 16 + cout:] == 7.0).all()  # neighbours of the slice untouched
+    if N % 2 == 0:                                                               # im1 | im2 halves from two tensors
+        h = N // 2
+        xd = xn.to(d)
+        out2 = torch.full_like(out, 7.0)
+        ops.conv3x3_thin(xd[:h].contiguous(), w.to(d), b.to(d), stride, 0.1, in_coff=8, x2=xd[h:].contiguous(), n_split_in=h,
+                         out=out2, out_coff=16)
+        assert torch.equal(out2, out)
+
+
+def test_conv3x3_thin_rejects_what_it_cannot_stage():
+    """stride 2 with Cin >= 32 needs two 17 x 65 patches of > 88 KB: the entry point returns an error code (no fallback)."""
+    from opticalflow_b200 import ops
+    d = torch.device("cuda:0")
+    x = torch.zeros(1, 16, 32, 32, device=d, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError):
+        ops.conv3x3_thin(x, torch.zeros(64, 32, 3, 3, device=d), torch.zeros(64, device=d), 2, 0.1)
+    with pytest.raises(RuntimeError):
+        ops.conv3x3_thin(torch.zeros(1, 8, 8, 24, device=d, dtype=torch.bfloat16), torch.zeros(16, 24, 3, 3, device=d),
+                         torch.zeros(16, device=d), 1, 0.1)
