@@ -71,19 +71,28 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
   pdl_wait();
   pdl_launch_dependents();
 
-  // per patch pixel, fixed for the whole kernel: shared-memory byte offset | (row << 16 | column); built once so that the
-  // per-tile staging loop has no divisions
-  uint2* tab = reinterpret_cast<uint2*>(thin_smem + p.off_tab);
-  const int npx = p.ih * p.iw;
-  for (int e = tid; e < npx; e += 256) {
-    const int r = e / p.iw, c = e - r * p.iw;
-    tab[e] = make_uint2((uint32_t)(e * p.pp), ((uint32_t)r << 16) | (uint32_t)c);
+  // The copies a thread issues for a patch are the same for every tile up to the tile origin: element e = tid + 256 k is
+  // (patch pixel e / NCH, 16-byte chunk e % NCH).  The pixel's shared-memory offset, its offset from the tile origin and its
+  // (row, column) are computed ONCE (table in shared memory), so that the per-tile staging loop is a table read, a bounds
+  // test and one address add per copy.
+  uint4* tab = reinterpret_cast<uint4*>(thin_smem + p.off_tab);
+  const int nel = p.ih * p.iw * NCH;
+  for (int px = tid; px < p.ih * p.iw; px += 256) {
+    const int r = px / p.iw, c = px - r * p.iw;
+    tab[px] = make_uint4((uint32_t)(px * p.pp), (uint32_t)(r * p.W + c), ((uint32_t)r << 16) | (uint32_t)c, 0u);
   }
   __syncthreads();
+  // tile walk without divisions: (n, ty, tx) advance by the decomposition of gridDim.x
+  const int per_img = p.tiles_x * p.tiles_y;
+  const int g_n = gridDim.x / per_img, g_r = gridDim.x - g_n * per_img;
+  const int g_y = g_r / p.tiles_x, g_x = g_r - g_y * p.tiles_x;
+  auto advance = [&](int& n, int& ty, int& tx) {
+    tx += g_x; ty += g_y; n += g_n;
+    if (tx >= p.tiles_x) { tx -= p.tiles_x; ++ty; }
+    if (ty >= p.tiles_y) { ty -= p.tiles_y; ++n; }
+  };
 
-  auto stage = [&](int tile, int buf) {
-    const int tx = tile % p.tiles_x; const int t2 = tile / p.tiles_x;
-    const int ty = t2 % p.tiles_y; const int n = t2 / p.tiles_y;
+  auto stage = [&](int n, int ty, int tx, int buf) {
     const bool sec = p.in2 != nullptr && n >= p.n_split_in;
     const int sp = (int)(sec ? p.in2_pitch : p.in_pitch);
     const int iy0 = ty * 8 * p.stride - 1, ix0 = tx * 32 * p.mp * p.stride - 1;
@@ -91,18 +100,19 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
                                    : p.in + ((long)n * p.H * p.W) * p.in_pitch + p.in_coff;
     const __nv_bfloat16* org = src + ((long)iy0 * p.W + ix0) * sp;       // may point before the tensor: only offset from
     const uint32_t dst0 = patch_addr + buf * p.patch_bytes;
-    for (int e = tid; e < npx * NCH; e += 256) {
-      const uint2 t = tab[e / NCH];                                      // NCH is a power of two
+#pragma unroll 2
+    for (int e = tid; e < nel; e += 256) {
+      const uint4 t = tab[e / NCH];                                      // NCH is a power of two
       const int ch = e & (NCH - 1);
-      const int r = (int)(t.y >> 16), c = (int)(t.y & 0xffffu);
-      const bool ok = (unsigned)(iy0 + r) < (unsigned)p.H && (unsigned)(ix0 + c) < (unsigned)p.W;
-      thin_cp16(dst0 + t.x + ch * 16, ok ? (const void*)(org + (r * p.W + c) * sp + ch * 8) : (const void*)src, ok);
+      const bool ok = (unsigned)(iy0 + (int)(t.z >> 16)) < (unsigned)p.H && (unsigned)(ix0 + (int)(t.z & 0xffffu)) < (unsigned)p.W;
+      thin_cp16(dst0 + t.x + ch * 16, ok ? (const void*)(org + (int)t.y * sp + ch * 8) : (const void*)src, ok);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
   int tile = blockIdx.x;
-  if (tile < p.ntiles) stage(tile, 0);                           // (commits the weight copies too)
+  int cn = tile / per_img, cty = (tile - cn * per_img) / p.tiles_x, ctx = tile - cn * per_img - cty * p.tiles_x;   // current tile
+  if (tile < p.ntiles) stage(cn, cty, ctx, 0);                   // (commits the weight copies too)
   const uint32_t a_lane = (uint32_t)(((warp * p.stride) * p.iw + (lane & 15) * p.stride) * p.pp + (lane >> 4) * 16);
   const uint32_t b_lane = w_addr + (uint32_t)(((lane & 7) + ((lane >> 4) << 3)) * p.wp + ((lane >> 3) & 1) * 16);
   uint32_t a_off[9];                                             // tap offsets inside the patch, fixed for the kernel
@@ -112,16 +122,17 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
   for (int it = 0; tile < p.ntiles; tile += gridDim.x, ++it) {
     const int buf = it & 1;
     const int next = tile + gridDim.x;
+    int nn = cn, nty = cty, ntx = ctx;
+    advance(nn, nty, ntx);
     if (next < p.ntiles) {
-      stage(next, buf ^ 1);
+      stage(nn, nty, ntx, buf ^ 1);
       asm volatile("cp.async.wait_group 1;" ::: "memory");
     } else {
       asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();                                             // patch of this tile (and the weights) visible to all warps
 
-    const int tx = tile % p.tiles_x; const int t2 = tile / p.tiles_x;
-    const int ty = t2 % p.tiles_y; const int n = t2 / p.tiles_y;
+    const int tx = ctx, ty = cty, n = cn;
     const int oy = ty * 8 + warp;
     for (int pr = 0; pr < p.mp && oy < p.Ho; ++pr) {             // 32 pixels (two m-tiles) at a time
       float acc[2][NT][4];
@@ -179,6 +190,7 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
       }
     }
     __syncthreads();                                             // every warp is done with this buffer before it is refilled
+    cn = nn; cty = nty; ctx = ntx;
   }
 }
 
@@ -203,7 +215,7 @@ static int launch_thin(ThinConvParams& p, cudaStream_t s) {
     p.patch_bytes = (p.ih * p.iw * p.pp + 127) & ~127;
     p.off_ostg = p.off_patch + 2 * p.patch_bytes;
     p.off_tab = p.off_ostg + 8 * 16 * (NT * 16 + 16);
-    smem = p.off_tab + p.ih * p.iw * 8;
+    smem = p.off_tab + p.ih * p.iw * 16;
     if (smem <= 113 * 1024 || (p.mp == 1 && smem <= 227 * 1024)) break;   // keep two CTAs per SM if the wide tile allows it
   }
   if (p.mp < 1) return (int)cudaErrorInvalidValue;
