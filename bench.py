@@ -286,7 +286,8 @@ def run_ours(args):
         roof = {"bound": "tensor", "achieved": step_tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": step_tflops / peaks["bf16_tflops_sustained"], "traffic": None,
                 "note": "whole forward (fp32 CUDA-core mode): conv FLOPs / step time"}
-    cpu_v, cpu_cores, cpu_sample = cpu_reference_forward_timer(H, W, reps=5)
+    # host-core baseline: rank 0 at N = 1 only (under torchrun the other ranks' processes share the cores)
+    cpu_v, cpu_cores, cpu_sample = cpu_reference_forward_timer(H, W, reps=5) if world == 1 else (None, None, "not measured at N > 1")
     line = {
         "metric": "pwcnet_frame_pairs_per_s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,

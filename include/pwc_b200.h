@@ -242,6 +242,12 @@ int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
  * ------------------------------------------------------------------------------------------ */
 int pwc_preprocess_u8_fwd(const uint8_t* im1, const uint8_t* im2, long img_stride, long row_stride,
                           int B, int H, int W, int Hp, int Wp, int swap_rb, float* out, void* stream);
+/* frame-stack variants for consecutive pairs of one video (pair k = frames k, k+1: every frame is converted and run through
+ * the feature pyramid ONCE): N uint8 frames -> [N,3,Hp,Wp] fp32, and conv1a on such a stack (N frames -> [N,H/2,W/2,16] bf16). */
+int pwc_preprocess_frames_u8_fwd(const uint8_t* frames, long img_stride, long row_stride,
+                                 int N, int H, int W, int Hp, int Wp, int swap_rb, float* out, void* stream);
+int pwc_conv1a_frames_bf16_fwd(const float* frames, const float* w, const float* bias, void* out,
+                               int N, int H, int W, float slope, void* stream);
 int pwc_flow_postprocess_fwd(const float* flow, int B, int h, int w, int crop_h, int crop_w,
                              float* out, int H, int W, float mult, int out_hwc, void* stream);
 int pwc_flow_metrics_fwd(const float* pred, const float* gt, const uint8_t* valid, int B, int H, int W,

@@ -14,7 +14,9 @@ namespace pwc {
 // columns of a row are loaded once for the 4 pixels.
 __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                           const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
-                                                          int B, int H, int W, float slope) {
+                                                          int B, int H, int W, float slope, int frames) {
+  // frames = 0: x is the driver tensor [B,6,H,W] (image b of half h at planes 6b + 3h), 2B output images (im1 half first);
+  // frames = 1: x is a frame stack [B,3,H,W], B output images (shared-pyramid video plan)
   __shared__ __align__(16) float ws[27][16];
   __shared__ float bs[16];
   pdl_wait();
@@ -27,12 +29,12 @@ __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __rest
   __syncthreads();
   const int Ho = H >> 1, Wo = W >> 1, Wq = (Wo + 3) >> 2;
   const long hw = (long)H * W;
-  const long total = 2L * B * Ho * Wq;
+  const long total = (frames ? 1L : 2L) * B * Ho * Wq;
   for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
     const int qx = e % Wq; const long t = e / Wq;
     const int oy = t % Ho; const int img = t / Ho;
     const int b = img % B, half = img / B;
-    const float* src = x + ((long)b * 6 + half * 3) * hw;
+    const float* src = frames ? x + (long)img * 3 * hw : x + ((long)b * 6 + half * 3) * hw;
     const int ox0 = 4 * qx, ix0 = 2 * ox0 - 1;
     float acc[4][16];
 #pragma unroll
@@ -187,7 +189,15 @@ extern "C" int pwc_conv1a_bf16_fwd(const float* x, const float* w, const float* 
                                    int B, int H, int W, float slope, void* stream) {
   if (B <= 0 || (H & 1) || (W & 1)) return (int)cudaErrorInvalidValue;
   return (int)pwc::launch_pdl(pwc::conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, (cudaStream_t)stream, x, w, bias,
-                              reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope);
+                              reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, 0);
+}
+
+// conv1a on a stack of N frames [N,3,H,W] fp32 -> [N,H/2,W/2,16] bf16 (video plan: every frame goes through the pyramid once)
+extern "C" int pwc_conv1a_frames_bf16_fwd(const float* frames, const float* w, const float* bias, void* out,
+                                          int N, int H, int W, float slope, void* stream) {
+  if (N <= 0 || (H & 1) || (W & 1)) return (int)cudaErrorInvalidValue;
+  return (int)pwc::launch_pdl(pwc::conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, (cudaStream_t)stream, frames, w, bias,
+                              reinterpret_cast<__nv_bfloat16*>(out), N, H, W, slope, 1);
 }
 
 extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,

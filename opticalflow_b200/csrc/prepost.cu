@@ -14,13 +14,14 @@ namespace pwc {
 // one thread = 4 consecutive output x of one (n, image, y) row, all 3 colour planes: 12 source bytes -> 3 float4 stores
 __global__ void __launch_bounds__(256)
 preprocess_u8_kernel(const uint8_t* __restrict__ im1, const uint8_t* __restrict__ im2, long img_stride, long row_stride,
-                     int B, int H, int W, int Hp, int Wp, int swap_rb, float* __restrict__ out) {
+                     int B, int H, int W, int Hp, int Wp, int swap_rb, float* __restrict__ out, int pairs) {
+  // pairs = 1: out [B,6,Hp,Wp] (frame 1 | frame 2 of pair n); pairs = 0: out [B,3,Hp,Wp], a plain frame stack from im1
   const int Wq = Wp >> 2;
-  const long total = (long)B * 2 * Hp * Wq;
+  const long total = (long)B * (pairs ? 2 : 1) * Hp * Wq;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     const int xq = (int)(i % Wq); long t = i / Wq;
     const int y = (int)(t % Hp); t /= Hp;
-    const int im = (int)(t & 1); const int n = (int)(t >> 1);
+    const int im = pairs ? (int)(t & 1) : 0; const int n = pairs ? (int)(t >> 1) : (int)t;
     const uint8_t* src = (im ? im2 : im1) + (long)n * img_stride + (long)min(y, H - 1) * row_stride;   // replicate rows
     float v[3][4];
 #pragma unroll
@@ -30,7 +31,7 @@ preprocess_u8_kernel(const uint8_t* __restrict__ im1, const uint8_t* __restrict_
 #pragma unroll
       for (int c = 0; c < 3; ++c) v[c][k] = __fdiv_rn((float)px[swap_rb ? 2 - c : c], 255.0f);        // arr.astype(float32) / 255.0
     }
-    float* dst = out + (((long)n * 6 + 3 * im) * Hp + y) * Wp + 4 * xq;
+    float* dst = out + (((long)n * (pairs ? 6 : 3) + 3 * im) * Hp + y) * Wp + 4 * xq;
 #pragma unroll
     for (int c = 0; c < 3; ++c)
       *reinterpret_cast<float4*>(dst + (long)c * Hp * Wp) = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
@@ -129,7 +130,18 @@ extern "C" int pwc_preprocess_u8_fwd(const uint8_t* im1, const uint8_t* im2, lon
     return (int)cudaErrorInvalidValue;
   const long work = (long)B * 2 * Hp * (Wp >> 2);
   pwc::preprocess_u8_kernel<<<pwc::grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(
-      im1, im2, img_stride, row_stride, B, H, W, Hp, Wp, swap_rb, out);
+      im1, im2, img_stride, row_stride, B, H, W, Hp, Wp, swap_rb, out, 1);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int pwc_preprocess_frames_u8_fwd(const uint8_t* frames, long img_stride, long row_stride,
+                                            int N, int H, int W, int Hp, int Wp, int swap_rb, float* out, void* stream) {
+  if (N <= 0 || H <= 0 || W <= 0 || Hp < H || Wp < W || (Wp & 3) || row_stride < 3L * W ||
+      (reinterpret_cast<uintptr_t>(out) & 15))
+    return (int)cudaErrorInvalidValue;
+  const long work = (long)N * Hp * (Wp >> 2);
+  pwc::preprocess_u8_kernel<<<pwc::grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(
+      frames, frames, img_stride, row_stride, N, H, W, Hp, Wp, swap_rb, out, 0);
   return (int)cudaGetLastError();
 }
 

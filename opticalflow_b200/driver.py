@@ -160,7 +160,10 @@ class VideoFlowPipeline:
     frame size) and the x`mult` flow scale (ONE kernel, prepost.postprocess_flow).  Per pair 3 bytes/pixel go up instead
     of the 24 bytes/pixel of the fp32 [1,6,H,W] tensor the reference uploads.  Three streams as in FlowPipeline."""
 
-    def __init__(self, model, B, H, W, device, swap_rb=True, mult=20.0, full_res=False, depth=2):
+    def __init__(self, model, B, H, W, device, swap_rb=True, mult=20.0, full_res=False, depth=2, share_pyramid=None):
+        """share_pyramid (default: on for conv_mode='bf16'): frame t is image 2 of pair t-1 and image 1 of pair t, so the plan
+        runs the feature pyramid once per frame (B+1 images per batch instead of 2B) and the cost volumes read frame t+1's
+        features in place (engine_bf16.PlanBF16(video=True))."""
         from . import prepost
         if device.type != "cuda":
             raise RuntimeError("VideoFlowPipeline: CUDA device required -- this build has no CPU fallback")
@@ -173,7 +176,8 @@ class VideoFlowPipeline:
         # the reference cuts the image-pixel pads from the quarter-resolution flow (unpad quirk, see prepost.unpad)
         self.oh, self.ow = (H, W) if full_res else (Hp // 4 - self.ph, Wp // 4 - self.pw)
         with torch.cuda.device(device):
-            self.plan = model._plan(B, Hp, Wp, device)
+            self.share = (getattr(model, "conv_mode", "") == "bf16") if share_pyramid is None else bool(share_pyramid)
+            self.plan = model._plan(B, Hp, Wp, device, video=True) if self.share else model._plan(B, Hp, Wp, device)
             self.plan.pack_weights(model)
             self.s_in, self.s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
             self.f_dev = [torch.empty(B + 1, H, W, 3, device=device, dtype=torch.uint8) for _ in range(depth)]
@@ -188,7 +192,10 @@ class VideoFlowPipeline:
 
     def _compute(self, s):
         f = self.f_dev[s]
-        self.pp.frames_to_input(f[:-1], f[1:], swap_rb=self.swap_rb, out=self.x_dev)
+        if self.share:
+            self.pp.frames_to_stack(f, swap_rb=self.swap_rb, out=self.x_dev)
+        else:
+            self.pp.frames_to_input(f[:-1], f[1:], swap_rb=self.swap_rb, out=self.x_dev)
         flow2 = self.plan.run() if hasattr(self.plan, "x_static") else self.plan.run(self.x_dev)
         lib, _lib = self.pp._lib.load(), self.pp._lib
         h, w = self.Hp // 4, self.Wp // 4

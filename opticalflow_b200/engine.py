@@ -248,10 +248,12 @@ class Plan:
         return self.flow[lvl][..., :2].permute(0, 3, 1, 2).contiguous()
 
 
-def make_plan(model, B, H, W, device, conv_mode="fp32", align_corners=False):
+def make_plan(model, B, H, W, device, conv_mode="fp32", align_corners=False, video=False):
     if conv_mode == "fp32":
+        if video:
+            raise ValueError("the shared-pyramid video plan exists for conv_mode='bf16' only")
         return Plan(model, B, H, W, device, align_corners)
     if conv_mode == "bf16":
         from .engine_bf16 import PlanBF16
-        return PlanBF16(model, B, H, W, device, align_corners)
+        return PlanBF16(model, B, H, W, device, align_corners, video=video)
     raise ValueError(f"unknown conv_mode {conv_mode!r} (expected 'fp32' or 'bf16')")

@@ -115,7 +115,10 @@ class _TcLayer:
 
 
 class PlanBF16:
-    def __init__(self, model, B, H, W, device, align_corners=False, use_graph=True):
+    def __init__(self, model, B, H, W, device, align_corners=False, use_graph=True, video=False):
+        """video=True: the B pairs are CONSECUTIVE frames (t, t+1) of one stream: the input is B+1 frames [B+1,3,H,W], the
+        feature pyramid runs ONCE per frame (B+1 images instead of 2B) and pair k reads frame k+1's features in place --
+        image k+1 of the same concat buffer -- as its image-2 features."""
         if H % 64 or W % 64:
             raise ValueError(f"H and W must be multiples of 64 (6 stride-2 levels), got {H}x{W}")
         self.lib = _lib.load()
@@ -124,19 +127,22 @@ class PlanBF16:
         self.use_graph = use_graph
         zb = lambda *s: torch.zeros(*s, device=device, dtype=BF)            # noqa: E731
         zf = lambda *s: torch.zeros(*s, device=device, dtype=torch.float32)  # noqa: E731
-        self.x_static = zf(B, 6, H, W)
+        self.video = bool(video)
+        NP = self.NP = (B + 1) if video else 2 * B            # images through the pyramid
+        NC = (B + 1) if video else B                          # images holding pyramid features in the concat buffers
+        self.x_static = zf(B + 1, 3, H, W) if video else zf(B, 6, H, W)
         self.hw = {l: (H >> l, W >> l) for l in range(1, 7)}
-        self.pa = {l: zb(2 * B, *self.hw[l], PYR_CP[l]) for l in range(1, 7)}
-        self.pb = {l: zb(2 * B, *self.hw[l], PYR_CP[l]) for l in range(1, 7)}
+        self.pa = {l: zb(NP, *self.hw[l], PYR_CP[l]) for l in range(1, 7)}
+        self.pb = {l: zb(NP, *self.hw[l], PYR_CP[l]) for l in range(1, 7)}
         self.cat, self.f2, self.flow, self.upflow = {}, {}, {}, {}
         for l in range(2, 7):
             h, w = self.hw[l]
-            self.cat[l] = zb(B, h, w, concat_width(l))
-            self.f2[l] = zb(B, h, w, PYR_CP[l])
+            self.cat[l] = zb(NC, h, w, concat_width(l))
+            self.f2[l] = None if video else zb(B, h, w, PYR_CP[l])
             self.flow[l] = zf(B, h, w, 4)
             if l < 6:
                 self.upflow[l] = zf(B, h, w, 2)
-        self.f1_6 = zb(B, *self.hw[6], PYR_CP[6])
+        self.f1_6 = zb(NC, *self.hw[6], PYR_CP[6])
         h2, w2 = self.hw[2]
         self.dc = [zb(B, h2, w2, c) for (_, c, _) in DC]
         self.flow_out4 = zf(B, h2, w2, 4)
@@ -264,7 +270,13 @@ class PlanBF16:
             f1_pitch, flow, fp, scale = cat.shape[-1], self.upflow[lvl], 2, FLOW_SCALE[lvl]
         outp = ctypes.c_void_p(cat.data_ptr() + 2 * CORR_OFF)
         lib = self.lib
-        args = (f1p, f1_pitch, _lib.ptr(self.f2[lvl]), PYR_CP[lvl], _lib.ptr(flow), fp, scale, self.align_corners,
+        f2p, f2_pitch = _lib.ptr(self.f2[lvl]), PYR_CP[lvl]
+        if self.video:                      # image-2 features of pair k = image-1 features of frame k+1, read in place
+            if lvl == 6:
+                f2p = ctypes.c_void_p(self.f1_6.data_ptr() + 2 * h * w * PYR_CP[6])
+            else:
+                f2p, f2_pitch = ctypes.c_void_p(cat.data_ptr() + 2 * h * w * cat.shape[-1] + 2 * C1_OFF), cat.shape[-1]
+        args = (f1p, f1_pitch, f2p, f2_pitch, _lib.ptr(flow), fp, scale, self.align_corners,
                 0.9999, 0.1, outp, cat.shape[-1], self.B, C, h, w, 4, _lib.NHWC, _lib.BF16)
         self.op_info.append((f"warp_corr{lvl}", 2.0 * self.B * h * w * 81 * C))
         self.ops.append(lambda st: _lib.check(lib.pwc_warp_corr_lrelu_fwd(*args, st), f"warp_corr{lvl}"))
@@ -275,9 +287,12 @@ class PlanBF16:
         # conv1a on CUDA cores, straight from the NCHW fp32 input
         self.w1a = torch.zeros(16, 3, 3, 3, device=dev)
         self.b1a = torch.zeros(16, device=dev)
-        a1 = (_lib.ptr(self.x_static), _lib.ptr(self.w1a), _lib.ptr(self.b1a), _lib.ptr(self.pa[1]), B, self.H, self.W, 0.1)
-        self.op_info.append(("conv1a.0", 2.0 * 2 * B * (self.H // 2) * (self.W // 2) * 16 * 27))
-        self.ops.append(lambda st: _lib.check(lib.pwc_conv1a_bf16_fwd(*a1, st), "conv1a"))
+        NP, vid = self.NP, self.video
+        a1 = (_lib.ptr(self.x_static), _lib.ptr(self.w1a), _lib.ptr(self.b1a), _lib.ptr(self.pa[1]), (NP if vid else B), self.H,
+              self.W, 0.1)
+        self.op_info.append(("conv1a.0", 2.0 * NP * (self.H // 2) * (self.W // 2) * 16 * 27))
+        c1a = lib.pwc_conv1a_frames_bf16_fwd if vid else lib.pwc_conv1a_bf16_fwd
+        self.ops.append(lambda st: _lib.check(c1a(*a1, st), "conv1a"))
         for l in range(1, 7):
             names = (f"conv{l}a", f"conv{l}aa", f"conv{l}b") if l < 6 else ("conv6aa", "conv6a", "conv6b")
             h, w = self.hw[l]
@@ -285,29 +300,32 @@ class PlanBF16:
                 hin, win = self.hw[l - 1]
                 cin = PYR_CH[l - 1]
                 if l == 2:
-                    self._tc(names[0] + ".0", cin, PYR_CH[l], self.pa[1], 0, PYR_CP[1], self.pa[l], 0, 2 * B, hin, win, stride=2)
+                    self._tc(names[0] + ".0", cin, PYR_CH[l], self.pa[1], 0, PYR_CP[1], self.pa[l], 0, NP, hin, win, stride=2)
+                elif vid:
+                    self._tc(names[0] + ".0", cin, PYR_CH[l], self.cat[l - 1], C1_OFF, PYR_CP[l - 1], self.pa[l], 0, NP,
+                             hin, win, stride=2)
                 else:
-                    self._tc(names[0] + ".0", cin, PYR_CH[l], self.cat[l - 1], C1_OFF, PYR_CP[l - 1], self.pa[l], 0, 2 * B,
+                    self._tc(names[0] + ".0", cin, PYR_CH[l], self.cat[l - 1], C1_OFF, PYR_CP[l - 1], self.pa[l], 0, NP,
                              hin, win, stride=2, src2=self.f2[l - 1], n_split=B)
             g = S2D.get(l, 1)            # thin dense->dense layers run on the space-to-depth view (see _s2d_weights)
             C = PYR_CH[l]
-            fl = 2.0 * 2 * B * h * w * C * C * 9
-            va = self.pa[l].view(2 * B, h, w // g, g * PYR_CP[l]) if g > 1 else self.pa[l]
-            vb = self.pb[l].view(2 * B, h, w // g, g * PYR_CP[l]) if g > 1 else self.pb[l]
+            fl = 2.0 * NP * h * w * C * C * 9
+            va = self.pa[l].view(NP, h, w // g, g * PYR_CP[l]) if g > 1 else self.pa[l]
+            vb = self.pb[l].view(NP, h, w // g, g * PYR_CP[l]) if g > 1 else self.pb[l]
             if g > 1:
-                self._tc(names[1] + ".0", g * C, g * C, va, 0, g * C, vb, 0, 2 * B, h, w // g,
+                self._tc(names[1] + ".0", g * C, g * C, va, 0, g * C, vb, 0, NP, h, w // g,
                          wfn=_s2d_weights(names[1] + ".0", g), flops=fl, kkskip=True)
             else:
-                self._tc(names[1] + ".0", C, C, self.pa[l], 0, PYR_CP[l], self.pb[l], 0, 2 * B, h, w)
+                self._tc(names[1] + ".0", C, C, self.pa[l], 0, PYR_CP[l], self.pb[l], 0, NP, h, w)
             if l == 1:
-                self._tc(names[2] + ".0", g * C, g * C, vb, 0, g * C, va, 0, 2 * B, h, w // g,
+                self._tc(names[2] + ".0", g * C, g * C, vb, 0, g * C, va, 0, NP, h, w // g,
                          wfn=_s2d_weights(names[2] + ".0", g), flops=fl, kkskip=True)
             elif l < 6:
-                self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.cat[l], C1_OFF, 2 * B, h, w,
-                         dst2=self.f2[l], n_split=B)
+                self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.cat[l], C1_OFF, NP, h, w,
+                         dst2=self.f2[l], n_split=(NP if vid else B))
             else:
-                self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.f1_6, 0, 2 * B, h, w,
-                         dst2=self.f2[l], n_split=B)
+                self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.f1_6, 0, NP, h, w,
+                         dst2=self.f2[l], n_split=(NP if vid else B))
         for l in (6, 5, 4, 3, 2):
             h, w = self.hw[l]
             cat, wd = self.cat[l], concat_width(l)
@@ -320,7 +338,7 @@ class PlanBF16:
                 if S2D_DEC and cout <= S2D_DEC_MAXCOUT and l <= S2D_DEC_MAXLVL and w % g == 0:
                     # Cout = 64 / 32: g adjacent pixels form one super-pixel so that all 128 MMA rows carry outputs
                     # (weight block-structured as in _s2d_weights; all-zero (tap, chunk) blocks are skipped)
-                    v = cat.view(B, h, w // g, g * wd)
+                    v = cat[:B].view(B, h, w // g, g * wd)
                     cm2 = [dxp * wd + DEC_START[k] + c for dxp in range(g) for c in cm]
                     self._tc(f"conv{l}_{k}.0", g * len(cm), g * cout, v, 0, g * wd, v, DEC_WRITE[k], B, h, w // g, cmap=cm2,
                              wfn=_s2d_weights(f"conv{l}_{k}.0", g), flops=2.0 * B * h * w * cout * len(cm) * 9,
@@ -344,7 +362,7 @@ class PlanBF16:
         for i, (name, cout, dil) in enumerate(DC):
             g = 128 // cout if cout <= S2D_DEC_MAXCOUT else 1
             if S2D_DEC and g > 1 and dil == 1 and cmap is None and w % g == 0 and src.shape[-1] == span:
-                vi, vo = src.view(B, h, w // g, g * span), self.dc[i].view(B, h, w // g, g * cout)
+                vi, vo = src[:B].view(B, h, w // g, g * span), self.dc[i].view(B, h, w // g, g * cout)
                 self._tc(name + ".0", g * cin, g * cout, vi, 0, g * span, vo, 0, B, h, w // g,
                          wfn=_s2d_weights(name + ".0", g), flops=2.0 * B * h * w * cout * cin * 9, groups=(g, cout))
             else:

@@ -84,11 +84,11 @@ class PWCDCNet(nn.Module):
         self._plans = {}
 
     # -- execution ---------------------------------------------------------------------------------
-    def _plan(self, B, H, W, device):
-        key = (B, H, W, str(device), self.conv_mode, bool(self.align_corners))
+    def _plan(self, B, H, W, device, video=False):
+        key = (B, H, W, str(device), self.conv_mode, bool(self.align_corners), bool(video))
         plan = self._plans.get(key)
         if plan is None:
-            plan = engine.make_plan(self, B, H, W, device, self.conv_mode, self.align_corners)
+            plan = engine.make_plan(self, B, H, W, device, self.conv_mode, self.align_corners, video=video)
             self._plans[key] = plan
         return plan
 

@@ -50,6 +50,25 @@ def frames_to_input(frames1, frames2, swap_rb=True, multiple=64, out=None):
     return out, ph, pw
 
 
+def frames_to_stack(frames, swap_rb=True, multiple=64, out=None):
+    """frames: uint8 CUDA tensor [N,H,W,3] -> (x [N,3,Hp,Wp] fp32 = frame / 255, replicate-padded; pad_h, pad_w): the input
+    of the shared-pyramid video plan (pair k = frames k and k+1)."""
+    _need_cuda(frames, "frames_to_stack")
+    if frames.dtype != torch.uint8 or frames.dim() != 4 or frames.shape[-1] != 3:
+        raise RuntimeError("frames_to_stack: a uint8 [N,H,W,3] tensor expected")
+    frames = frames.contiguous()
+    N, H, W, _ = frames.shape
+    ph, pw = pad_amounts(H, W, multiple)
+    Hp, Wp = H + ph, W + pw
+    if out is None:
+        out = torch.empty(N, 3, Hp, Wp, device=frames.device, dtype=torch.float32)
+    lib = _lib.load()
+    e = lib.pwc_preprocess_frames_u8_fwd(_lib.ptr(frames), H * W * 3, W * 3, N, H, W, Hp, Wp, int(bool(swap_rb)), _lib.ptr(out),
+                                         _lib.stream_handle())
+    _lib.check(e, "pwc_preprocess_frames_u8_fwd")
+    return out, ph, pw
+
+
 def unpad(flow, pad_h, pad_w):
     """The reference's unpad (a view; no kernel)."""
     H, W = flow.shape[-2], flow.shape[-1]

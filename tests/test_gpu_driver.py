@@ -63,8 +63,9 @@ def test_run_sharded_ragged_tail():
     assert epe <= 0.02
 
 
+@pytest.mark.parametrize("share", [True, False])
 @pytest.mark.parametrize("full_res", [False, True])
-def test_video_pipeline_matches_reference_steps(full_res):
+def test_video_pipeline_matches_reference_steps(full_res, share):
     """uint8 frames -> flows through VideoFlowPipeline == the reference's per-pair steps (frame_to_tensor, pad, cat,
     model, unpad[, flow_resize], x20) with each step done by its own oracle / blocking call."""
     from opticalflow_b200 import driver, prepost
@@ -76,7 +77,8 @@ def test_video_pipeline_matches_reference_steps(full_res):
     B, H, W, N = 3, 100, 150, 8                              # pads to 128 x 192; 7 pairs = 2 full batches + ragged tail
     g = torch.Generator().manual_seed(9)
     frames = torch.randint(0, 256, (N, H, W, 3), dtype=torch.uint8, generator=g).pin_memory()
-    pipe = driver.VideoFlowPipeline(m, B, H, W, dev, swap_rb=True, mult=20.0, full_res=full_res)
+    pipe = driver.VideoFlowPipeline(m, B, H, W, dev, swap_rb=True, mult=20.0, full_res=full_res, share_pyramid=share)
+    assert pipe.plan.video == share and pipe.plan.NP == (B + 1 if share else 2 * B)
     got = {}
     n = pipe.run(frames, sink=lambda t0, c, f: got.update({t0 + k: f[k].clone() for k in range(c)}))
     assert n == N - 1 and sorted(got) == list(range(N - 1))
