@@ -221,6 +221,14 @@ int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
                          void* out2, long out2_pitch, int out2_coff, int n_split,
                          int N, int H, int W, int stride, float slope, void* stream);
 
+/* Flow head on the same kernel: dc_conv7 (3x3, Cin -> 2, no activation; PWCNet.py:132) fused with the residual add
+ * `flow2 + dc_conv7(x)` (PWCNet.py:268) and the NHWC -> NCHW unpack: out_nchw[N,2,H,W] fp32 = conv + bias2 + residual[...,0:2].
+ *   w_packed16 : pwc_pack_conv_weight_bf16 of the [2,Cin,3,3] weight zero-padded to 16 output rows (kc = cin, coutp = 16)
+ *   residual   : fp32 [N,H,W,res_pitch], channels 0,1 */
+int pwc_conv3x3_flow_head_fwd(const void* in, long in_pitch, int in_coff, int cin,
+                              const void* w_packed16, const float* bias2, const float* residual, long res_pitch,
+                              float* out_nchw, int N, int H, int W, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (8) Driver-side pre/post-processing and metrics on the device.
  *   pwc_preprocess_u8_fwd : frame_to_tensor + pad_to_multiple_of_64 + torch.cat([t1p, t2p], 1)

@@ -31,6 +31,7 @@ struct ThinConvParams {
   int ih, iw, pp, wp;                          // patch rows / columns, bytes per patch pixel, bytes per weight row
   int off_patch, patch_bytes, off_ostg, off_tab;   // shared-memory layout (weights at 0)
   int mp;                                      // 32-pixel m-tile pairs per tile row: tile = 8 rows x 32*mp pixels
+  float* flow_out; const float* residual; long res_pitch;   // flow head: channels 0,1 + residual -> fp32 NCHW [N,2,Ho,Wo]
 };
 
 __device__ __forceinline__ void thin_ldsm4(uint32_t (&r)[4], uint32_t addr) {
@@ -65,8 +66,9 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
   float bias2[NT][2];
 #pragma unroll
   for (int j = 0; j < NT; ++j) {
-    bias2[j][0] = p.bias[j * 8 + 2 * (lane & 3)];
-    bias2[j][1] = p.bias[j * 8 + 2 * (lane & 3) + 1];
+    const int c0 = j * 8 + 2 * (lane & 3);
+    bias2[j][0] = c0 < p.cout ? p.bias[c0] : 0.f;
+    bias2[j][1] = c0 + 1 < p.cout ? p.bias[c0 + 1] : 0.f;
   }
   pdl_wait();
   pdl_launch_dependents();
@@ -166,6 +168,26 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
       __nv_bfloat16* dst = second ? p.out2 + ((long)(n - p.n_split) * p.Ho * p.Wo) * p.out2_pitch + p.out2_coff
                                   : p.out + ((long)n * p.Ho * p.Wo) * p.out_pitch + p.out_coff;
       const long dp = second ? p.out2_pitch : p.out_pitch;
+      if (p.flow_out != nullptr) {
+        // flow head (dc_conv7 + the residual add of PWCNet.py:268): output channels 0,1 live in the lanes with lane % 4 == 0
+        // of n-tile 0; they leave as fp32 straight into the NCHW result, no activation
+        if ((lane & 3) == 0) {
+#pragma unroll
+          for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int ox = (tx * p.mp + pr) * 32 + m * 16 + (lane >> 2) + 8 * h;
+              if (ox < p.Wo) {
+                const long pix = ((long)n * p.Ho + oy) * p.Wo + ox;
+                const float2 r = *reinterpret_cast<const float2*>(p.residual + pix * p.res_pitch);
+                float* o = p.flow_out + ((long)n * 2 * p.Ho + oy) * p.Wo + ox;
+                o[0] = acc[m][0][2 * h] + bias2[0][0] + r.x;
+                o[(long)p.Ho * p.Wo] = acc[m][0][2 * h + 1] + bias2[0][1] + r.y;
+              }
+            }
+        }
+        continue;
+      }
 #pragma unroll
       for (int m = 0; m < 2; ++m) {
 #pragma unroll
@@ -231,6 +253,37 @@ static int launch_thin(ThinConvParams& p, cudaStream_t s) {
 
 }  // namespace pwc
 
+static int thin_dispatch(pwc::ThinConvParams& p, int nt8, int ks, cudaStream_t s) {
+  using namespace pwc;
+#define PWC_THIN(NTv, KSv) if (nt8 == NTv && ks == KSv) return launch_thin<NTv, KSv>(p, s)
+  PWC_THIN(2, 1); PWC_THIN(4, 1); PWC_THIN(8, 1);
+  PWC_THIN(2, 2); PWC_THIN(4, 2); PWC_THIN(8, 2);
+  PWC_THIN(2, 4); PWC_THIN(4, 4); PWC_THIN(8, 4);
+#undef PWC_THIN
+  return (int)cudaErrorInvalidValue;
+}
+
+// Flow head on the thin-layer kernel: 3x3 conv Cin -> 2 (weights zero-padded to 16 output rows), + bias + residual,
+// fp32 NCHW result.  dc_conv7 and `flow2 + dc_conv7(x)` of PWCNet.py:132,268.
+extern "C" int pwc_conv3x3_flow_head_fwd(const void* in, long in_pitch, int in_coff, int cin,
+                                         const void* w_packed16, const float* bias2, const float* residual, long res_pitch,
+                                         float* out_nchw, int N, int H, int W, void* stream) {
+  using namespace pwc;
+  if (N <= 0 || H <= 0 || W <= 0 || !(cin == 16 || cin == 32 || cin == 64) || (in_pitch & 7) || (in_coff & 7) || !residual ||
+      (res_pitch & 1) || ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(w_packed16)) & 15) ||
+      (reinterpret_cast<uintptr_t>(residual) & 7))
+    return (int)cudaErrorInvalidValue;
+  ThinConvParams p;
+  p.in = reinterpret_cast<const __nv_bfloat16*>(in); p.in_pitch = in_pitch; p.in_coff = in_coff;
+  p.in2 = nullptr; p.in2_pitch = 0; p.in2_coff = 0; p.n_split_in = N;
+  p.w = reinterpret_cast<const __nv_bfloat16*>(w_packed16); p.bias = bias2; p.cin = cin; p.cout = 2;
+  p.out = nullptr; p.out_pitch = 0; p.out_coff = 0; p.out2 = nullptr; p.out2_pitch = 0; p.out2_coff = 0; p.n_split = N;
+  p.N = N; p.H = H; p.W = W; p.stride = 1; p.slope = 1.f; p.Ho = H; p.Wo = W;
+  p.tiles_y = cdiv(H, 8); p.ih = 10; p.pp = 2 * cin + 16; p.wp = 2 * cin + 16;
+  p.flow_out = out_nchw; p.residual = residual; p.res_pitch = res_pitch;
+  return thin_dispatch(p, 2, cin / 16, (cudaStream_t)stream);
+}
+
 extern "C" int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
                                     const void* in2, long in2_pitch, int in2_coff, int n_split_in, int cin,
                                     const void* w_packed, const float* bias, int cout,
@@ -256,12 +309,6 @@ extern "C" int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
   p.tiles_y = cdiv(p.Ho, 8);
   p.ih = 7 * stride + 3;
   p.pp = 2 * cin + 16; p.wp = 2 * cin + 16;
-  cudaStream_t s = (cudaStream_t)stream;
-  const int nt8 = cout / 8, ks = cin / 16;
-#define PWC_THIN(NTv, KSv) if (nt8 == NTv && ks == KSv) return launch_thin<NTv, KSv>(p, s)
-  PWC_THIN(2, 1); PWC_THIN(4, 1); PWC_THIN(8, 1);
-  PWC_THIN(2, 2); PWC_THIN(4, 2); PWC_THIN(8, 2);
-  PWC_THIN(2, 4); PWC_THIN(4, 4); PWC_THIN(8, 4);
-#undef PWC_THIN
-  return (int)cudaErrorInvalidValue;
+  p.flow_out = nullptr; p.residual = nullptr; p.res_pitch = 0;
+  return thin_dispatch(p, cout / 8, cin / 16, (cudaStream_t)stream);
 }

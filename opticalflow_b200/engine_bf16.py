@@ -368,11 +368,31 @@ class PlanBF16:
             else:
                 self._tc(name + ".0", cin, cout, src, 0, span, self.dc[i], 0, B, h, w, dil=dil, cmap=cmap)
             src, cin, span, cmap = self.dc[i], cout, cout, None
-        self._tc("dc_conv7", 32, 2, src, 0, 32, self.flow_out4, 0, B, h, w, slope=1.0, out_f32=True, residual=self.flow[2],
-                 ts=True)
-        uo = (_lib.ptr(self.flow_out4), 4, 0, _lib.ptr(self.out), B, h, w, 1.0)
-        self.op_info.append(("unpack_flow", 0.0))
-        self.ops.append(lambda st: _lib.check(lib.pwc_unpack_flow_f32(*uo, st), "unpack_flow"))
+        if os.environ.get("PWC_FLOW_HEAD", "1") != "0":
+            # dc_conv7 + residual + NCHW unpack in ONE launch of the thin-layer kernel (csrc/conv_thin.cu, flow-head mode):
+            # 32 + 4 us of tap-stacked tcgen05 conv and unpack kernel -> 12 us
+            L = _TcLayer()
+            L.kkskip, L.groups, L.handle, L.cmap = False, None, None, None
+            L.key, L.cin, L.cout, L.span, L.coutp, L.kc, L.wrows = "dc_conv7", 32, 2, 32, 16, 32, 16
+
+            def pad16(sd):
+                wt = torch.zeros(16, 32, 3, 3, device=dev, dtype=torch.float32)
+                wt[:2] = sd["dc_conv7.weight"]
+                return wt, sd["dc_conv7.bias"]
+            L.wfn = pad16
+            L.w = torch.zeros(9 * 32 * 16, device=dev, dtype=BF)
+            L.b = torch.zeros(2, device=dev, dtype=torch.float32)
+            self.layers["dc_conv7"] = L
+            ha = (_lib.ptr(src), src.shape[-1], 0, 32, _lib.ptr(L.w), _lib.ptr(L.b), _lib.ptr(self.flow[2]), self.flow[2].shape[-1],
+                  _lib.ptr(self.out), B, h, w)
+            self.op_info.append(("dc_conv7", 2.0 * B * h * w * 2 * 32 * 9))
+            self.ops.append(lambda st: _lib.check(lib.pwc_conv3x3_flow_head_fwd(*ha, st), "dc_conv7"))
+        else:
+            self._tc("dc_conv7", 32, 2, src, 0, 32, self.flow_out4, 0, B, h, w, slope=1.0, out_f32=True, residual=self.flow[2],
+                     ts=True)
+            uo = (_lib.ptr(self.flow_out4), 4, 0, _lib.ptr(self.out), B, h, w, 1.0)
+            self.op_info.append(("unpack_flow", 0.0))
+            self.ops.append(lambda st: _lib.check(lib.pwc_unpack_flow_f32(*uo, st), "unpack_flow"))
         self.launches = len(self.ops)
 
     # ------------------------------------------------------------------ weights
