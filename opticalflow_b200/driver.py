@@ -31,6 +31,17 @@ def batches(lo, hi, batch):
     return [(s, min(batch, hi - s)) for s in range(lo, hi, batch)]
 
 
+def video_shard(n_frames, rank, world):
+    """Frames [first, last] (inclusive) of the contiguous chunk of a video stream owned by `rank`: the n_frames - 1
+    consecutive pairs are split as shard_range does and each chunk takes ONE extra frame at its end (the frame it shares
+    with the next rank), so every pair (t, t+1) is computed by exactly one rank and no frame is exchanged
+    (pwc_extract_flow_video.py:process_video walks the pairs in order).  Returns None for an empty chunk."""
+    if n_frames < 0:
+        raise ValueError("n_frames < 0")
+    lo, hi = shard_range(max(n_frames - 1, 0), rank, world)      # pairs [lo, hi): pair t = frames (t, t+1)
+    return (lo, hi) if hi > lo else None
+
+
 def dist_env():
     """(rank, local_rank, world) from the torchrun environment (1-process defaults)."""
     return (int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")),
@@ -244,3 +255,18 @@ class VideoFlowPipeline:
             for j, sj in pending:
                 deliver(j, sj)
         return n_pairs
+
+
+def run_video_sharded(model, n_frames, load_frames, sink, B, H, W, device, rank=None, world=None, **kw):
+    """Each rank runs its chunk of one video through a VideoFlowPipeline.  load_frames(first, last) returns the pinned uint8
+    tensor [last - first + 1, H, W, 3] of frames first..last; sink(t0, count, flow_host) receives the flows of the pairs
+    (t0+k, t0+k+1) in stream numbering.  Returns the number of pairs this rank processed."""
+    r, _, w = dist_env()
+    rank = r if rank is None else rank
+    world = w if world is None else world
+    chunk = video_shard(n_frames, rank, world)
+    if chunk is None:
+        return 0
+    first, last = chunk
+    pipe = VideoFlowPipeline(model, B, H, W, device, **kw)
+    return pipe.run(load_frames(first, last), sink=lambda t0, c, f: sink(first + t0, c, f))

@@ -36,6 +36,26 @@ def test_batches_cover_ragged_tail_and_empty():
     assert driver.batches(5, 22, 8) == [(5, 8), (13, 8), (21, 1)]
 
 
+def test_video_shard_covers_every_pair_once():
+    for n_frames in (0, 1, 2, 3, 9, 100, 1001):
+        for world in (1, 2, 3, 8):
+            chunks = [driver.video_shard(n_frames, r, world) for r in range(world)]
+            pairs = []
+            for ch in chunks:
+                if ch is not None:
+                    first, last = ch
+                    assert 0 <= first < last <= n_frames - 1
+                    pairs.extend(range(first, last))                   # pair t = frames (t, t+1), both inside the chunk
+            assert pairs == list(range(max(n_frames - 1, 0)))
+            live = [c for c in chunks if c is not None]
+            assert all(live[i][1] == live[i + 1][0] for i in range(len(live) - 1))   # neighbours share exactly one frame
+    with pytest.raises(ValueError):
+        driver.video_shard(-1, 0, 1)
+    from opticalflow_b200.models.PWCNet import PWCDCNet
+    with pytest.raises(RuntimeError):
+        driver.VideoFlowPipeline(PWCDCNet(), 1, 64, 64, torch.device("cpu"))
+
+
 def test_pipeline_and_model_refuse_cpu():
     from opticalflow_b200.models.PWCNet import PWCDCNet
     m = PWCDCNet()
@@ -68,6 +88,8 @@ def _worker(rank, world, port, n_pairs, batch, q):
         done = []
         for s, c in driver.batches(lo, hi, batch):          # stand-in for load -> forward -> sink
             done.extend(range(s, s + c))
+        chunk = driver.video_shard(n_pairs + 1, rank, world)         # the same pairs seen as a stream of n_pairs + 1 frames
+        assert (chunk is None and lo == hi) or chunk == (lo, hi)
         t_max = driver.max_over_ranks([float(rank + 1), 10.0 - rank])
         n_sum = driver.sum_over_ranks([float(len(done))])
         gathered = [None] * world
