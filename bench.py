@@ -260,7 +260,7 @@ def run_ours(args):
                 "top_launch": {"layer": top[0], "us": round(top[1] * 1e6, 1), "TFLOPs": round(top[2] / top[1] / 1e12, 1),
                                "frac": top[2] / top[1] / 1e12 / peak},
                 "note": f"algorithmic conv FLOPs of the {len(tc)} tensor-core launches of one step / their summed CUDA-event "
-                        f"durations (each timed alone); peak = bf16 burst ({peaks['source']}); whole-step figure "
+                        f"durations (each launch captured 8x into a CUDA graph and timed alone); peak = bf16 burst ({peaks['source']}); whole-step figure "
                         f"{step_tflops:.1f} TFLOP/s incl. all other kernels"}
         kern_table = {n: round(t * 1e6, 1) for n, t, _ in ops_t}
     corr_res, corr_bytes, corr_t = corr_microbench(dev, B)
@@ -283,8 +283,8 @@ def run_ours(args):
                      "frac": cb / ct / 1e9 / peaks["hbm_gbs"], "traffic": ncu_traffic("warp_corr2"),
                      "traffic_note": "DRAM bytes of the level-2 launch alone (ncu --set full, profiles/r1_ncu_traffic.json)", "levels": lv,
                      "kernel": "warp_corr_tc_kernel (levels 2,3: tcgen05) / warp_corr_mma_kernel (levels 4-6: mma.sync)",
-                     "note": "the 5 cost-volume launches of one forward (bf16 features in the concat buffers), CUDA events, "
-                             "each timed in sequence; algorithmic bytes B*H*W*(2*C*2 + 81*2 + 8)"}
+                     "note": "the 5 cost-volume launches of one forward (bf16 features in the concat buffers); each launch captured 8x into "
+                             "a CUDA graph and timed with CUDA events (no host launch cost); algorithmic bytes B*H*W*(2*C*2 + 81*2 + 8)"}
     if roof is None:
         roof = {"bound": "tensor", "achieved": step_tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": step_tflops / peaks["bf16_tflops_sustained"], "traffic": None,

@@ -15,18 +15,10 @@ plan = m._plan(B, H, W, dev)
 plan.pack_weights(m)
 plan.x_static.copy_(torch.rand(B, 6, H, W, device=dev))
 plan._launch_all(); torch.cuda.synchronize()
-st = _lib.stream_handle()
-tot = [0.0] * len(plan.ops)
-for r in range(reps):
-    for i, op in enumerate(plan.ops):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(); op(st); e1.record(); e1.synchronize()
-        tot[i] += e0.elapsed_time(e1) * 1e-3 / reps
-rows = []
-for (name, fl), t in zip(plan.op_info, tot):
-    rows.append((name, t, fl))
+rows = plan.time_ops(reps=reps)          # each launch captured 8x into its own CUDA graph: GPU time without host launch cost
+tot = [t for _, t, _ in rows]
 T = sum(tot)
-print(f"B={B} {W}x{H}: sum of launches {T*1e3:.3f} ms -> {B/T:.1f} pairs/s (serialised, with event gaps)")
+print(f"B={B} {W}x{H}: sum of launches {T*1e3:.3f} ms -> {B/T:.1f} pairs/s (each timed alone, back to back with itself)")
 for name, t, fl in rows:
     print(f"{name:18s} {t*1e6:9.1f} us  {100*t/T:5.1f}%  {fl/t/1e12 if t > 0 else 0:8.1f} TFLOP/s")
 # whole-graph time
