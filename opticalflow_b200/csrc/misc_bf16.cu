@@ -88,6 +88,139 @@ __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __rest
   }
 }
 
+// conv1a on the tensor cores without giving up fp32 inputs: the layer is FMA-issue bound on the CUDA cores (432 FMA per
+// output pixel: 78 us at batch 8, about 50% of the fp32 pipe), so the 27-tap dot products run as mma.sync.m16n8k16 (K = 27
+// padded to 32) with BOTH operands split into bf16 hi + lo parts (x = hi + lo exactly to 16 mantissa bits) and the three
+// products hi*hi + lo*hi + hi*lo accumulated in fp32: error ~2^-16 relative, far below the bf16 rounding of the output.
+// CTA = 8 output rows x 64 pixels; the fp32 input patch (3 x 17 x 132) is staged with aligned 16-byte cp.async (zero fill
+// = padding); each thread gathers its A-fragment elements from it with precomputed tap offsets (im2col in registers).
+constexpr int kC1M_PW = 132, kC1M_IH = 17;
+__device__ __forceinline__ void c1m_split(float v, float w, uint32_t& hi, uint32_t& lo) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(v, w);
+  const float2 hf = __bfloat1622float2(h);
+  const __nv_bfloat162 l = __floats2bfloat162_rn(v - hf.x, w - hf.y);
+  hi = *reinterpret_cast<const uint32_t*>(&h); lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+__device__ __forceinline__ void c1m_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                         const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                                                         int B, int H, int W, float slope, int frames, int tiles_x, int tiles_y) {
+  __shared__ __align__(16) float patch[3 * kC1M_IH * kC1M_PW];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, c = lane & 3;
+  // ---- weights (independent of the previous kernel): B fragments of both n-tiles and k-steps, split hi / lo
+  uint32_t bh[2][2][2], bl[2][2][2];                           // [k step][n-tile][k half]
+  int koff[2][4];                                               // patch offsets of this thread's 8 k indices (-1: padding)
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = 16 * s + 2 * c + (q & 1) + 8 * (q >> 1);
+      const int ci = k / 9, ky = (k - 9 * ci) / 3, kx = k - 9 * ci - 3 * ky;
+      koff[s][q] = k < 27 ? (ci * kC1M_IH + ky) * kC1M_PW + kx : -1;
+    }
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int k = 16 * s + 2 * c + 8 * h, co = 8 * j + g;
+        const float w0 = k < 27 ? w[co * 27 + k] : 0.f, w1 = k + 1 < 27 ? w[co * 27 + k + 1] : 0.f;
+        c1m_split(w0, w1, bh[s][j][h], bl[s][j][h]);
+      }
+  float bia[2][2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) { bia[j][0] = bias[8 * j + 2 * c]; bia[j][1] = bias[8 * j + 2 * c + 1]; }
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int Ho = H >> 1, Wo = W >> 1;
+  const long hw = (long)H * W;
+  int tile = blockIdx.x;
+  const int tx = tile % tiles_x; tile /= tiles_x;
+  const int ty = tile % tiles_y; const int img = tile / tiles_y;
+  const float* src = frames ? x + (long)img * 3 * hw : x + ((long)(img % B) * 6 + (img / B) * 3) * hw;
+  const int ox0 = tx * 64, oy0 = ty * 8;
+  const int xs = 2 * ox0 - 4, ys = 2 * oy0 - 1;                 // patch origin; xs is a multiple of 4 like W
+  const uint32_t p_addr = (uint32_t)__cvta_generic_to_shared(patch);
+  for (int e = tid; e < 3 * kC1M_IH * (kC1M_PW / 4); e += 256) {
+    const int q = e % (kC1M_PW / 4), rr = e / (kC1M_PW / 4);
+    const int r = rr % kC1M_IH, ci = rr / kC1M_IH;
+    const int iy = ys + r, ix = xs + 4 * q;
+    const bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
+    const float* gp = ok ? src + ci * hw + (long)iy * W + ix : src;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(p_addr + (uint32_t)(rr * kC1M_PW + 4 * q) * 4u), "l"(gp),
+                 "r"(ok ? 16 : 0) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+
+  const int oy = oy0 + warp;
+  if (oy >= Ho) return;
+  const float* prow = patch + (2 * warp) * kC1M_PW + 3;         // input row 2*oy - 1 + ky, column 2*x - 1 + kx (+4 - xs offset)
+#pragma unroll 1
+  for (int mt = 0; mt < 4; ++mt) {
+    if (ox0 + 16 * mt >= Wo) break;
+    float acc[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) acc[j][e] = 0.f;
+    const float* p0 = prow + 2 * (16 * mt + g);                 // pixel row g of the m-tile; row g + 8 is 16 floats further
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      float v[2][4];                                            // [pixel row half][k index q]
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        v[0][q] = koff[s][q] >= 0 ? p0[koff[s][q]] : 0.f;
+        v[1][q] = koff[s][q] >= 0 ? p0[koff[s][q] + 16] : 0.f;
+      }
+      uint32_t ah[4], al[4];                                    // a0: (g, k lo pair) a1: (g+8, k lo pair) a2: (g, k hi pair) a3: (g+8, hi)
+      c1m_split(v[0][0], v[0][1], ah[0], al[0]);
+      c1m_split(v[1][0], v[1][1], ah[1], al[1]);
+      c1m_split(v[0][2], v[0][3], ah[2], al[2]);
+      c1m_split(v[1][2], v[1][3], ah[3], al[3]);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        c1m_mma(acc[j], al, bh[s][j][0], bh[s][j][1]);          // small terms first
+        c1m_mma(acc[j], ah, bl[s][j][0], bl[s][j][1]);
+        c1m_mma(acc[j], ah, bh[s][j][0], bh[s][j][1]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int ox = ox0 + 16 * mt + g + 8 * h;
+        if (ox < Wo) {
+          const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
+          *reinterpret_cast<__nv_bfloat162*>(out + (((long)img * Ho + oy) * Wo + ox) * 16 + 8 * j + 2 * c) =
+              __floats2bfloat162_rn(lrelu(v0, slope), lrelu(v1, slope));
+        }
+      }
+  }
+}
+
+static int launch_conv1a(const float* x, const float* w, const float* bias, void* out, int B, int H, int W, float slope,
+                         int frames, cudaStream_t s) {
+  static const int use_mma = []() { const char* e = getenv("PWC_CONV1A_MMA"); return e ? atoi(e) : 1; }();
+  if (use_mma && (W & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    const int tiles_x = cdiv(W >> 1, 64), tiles_y = cdiv(H >> 1, 8);
+    const long nt = (long)(frames ? B : 2 * B) * tiles_x * tiles_y;
+    if (nt <= 0x7fffffffL)
+      return (int)launch_pdl(conv1a_mma_kernel, dim3((unsigned)nt), dim3(256), 0, s, x, w, bias,
+                             reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y);
+  }
+  return (int)launch_pdl(conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, s, x, w, bias, reinterpret_cast<__nv_bfloat16*>(out),
+                         B, H, W, slope, frames);
+}
+
 // One warp per output pixel; lanes stride over input channels (4 at a time), 2x2 live taps, shuffle-reduce 2 sums.
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256) deconv4x4s2_c2_any_kernel(const TI* __restrict__ in, long in_pitch, int in_coff, int Cin,
@@ -188,16 +321,14 @@ __global__ void __launch_bounds__(256) deconv4x4s2_c2_small_kernel(const TI* __r
 extern "C" int pwc_conv1a_bf16_fwd(const float* x, const float* w, const float* bias, void* out,
                                    int B, int H, int W, float slope, void* stream) {
   if (B <= 0 || (H & 1) || (W & 1)) return (int)cudaErrorInvalidValue;
-  return (int)pwc::launch_pdl(pwc::conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, (cudaStream_t)stream, x, w, bias,
-                              reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, 0);
+  return pwc::launch_conv1a(x, w, bias, out, B, H, W, slope, 0, (cudaStream_t)stream);
 }
 
 // conv1a on a stack of N frames [N,3,H,W] fp32 -> [N,H/2,W/2,16] bf16 (video plan: every frame goes through the pyramid once)
 extern "C" int pwc_conv1a_frames_bf16_fwd(const float* frames, const float* w, const float* bias, void* out,
                                           int N, int H, int W, float slope, void* stream) {
   if (N <= 0 || (H & 1) || (W & 1)) return (int)cudaErrorInvalidValue;
-  return (int)pwc::launch_pdl(pwc::conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, (cudaStream_t)stream, frames, w, bias,
-                              reinterpret_cast<__nv_bfloat16*>(out), N, H, W, slope, 1);
+  return pwc::launch_conv1a(frames, w, bias, out, N, H, W, slope, 1, (cudaStream_t)stream);
 }
 
 extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
