@@ -101,27 +101,66 @@ __device__ __forceinline__ void c1m_split(float v, float w, uint32_t& hi, uint32
   const __nv_bfloat162 l = __floats2bfloat162_rn(v - hf.x, w - hf.y);
   hi = *reinterpret_cast<const uint32_t*>(&h); lo = *reinterpret_cast<const uint32_t*>(&l);
 }
+// activations: hi = the top 16 bits (truncation, one PRMT for the pair), lo = the exact remainder rounded to bf16
+__device__ __forceinline__ void c1m_split_trunc(float v, float w, uint32_t& hi, uint32_t& lo) {
+  const uint32_t vb = __float_as_uint(v), wb = __float_as_uint(w);
+  hi = __byte_perm(vb, wb, 0x7632);
+  const __nv_bfloat162 l = __floats2bfloat162_rn(v - __uint_as_float(vb & 0xffff0000u), w - __uint_as_float(wb & 0xffff0000u));
+  lo = *reinterpret_cast<const uint32_t*>(&l);
+}
 __device__ __forceinline__ void c1m_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
+template <int OFF>
+__device__ __forceinline__ float c1m_lds(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(addr), "n"(OFF * 4));
+  return v;
+}
+// one 16-pixel m-tile (MT = its index in the warp's 64-pixel row): every smem offset is an immediate
+template <int MT>
+__device__ __forceinline__ void c1m_tile(const uint32_t (&pa)[2][4], const uint32_t (&bh)[2][2][2], const uint32_t (&bl)[2][2][2],
+                                         float (&acc)[2][4]) {
+#pragma unroll
+  for (int s = 0; s < 2; ++s) {
+    float v[2][4];                                              // [pixel row half][k index q]; row g + 8 is 16 floats further
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { v[0][q] = c1m_lds<32 * MT>(pa[s][q]); v[1][q] = c1m_lds<32 * MT + 16>(pa[s][q]); }
+    uint32_t ah[4], al[4];                                      // a0: (g, k lo pair) a1: (g+8, lo) a2: (g, k hi pair) a3: (g+8, hi)
+    c1m_split_trunc(v[0][0], v[0][1], ah[0], al[0]);
+    c1m_split_trunc(v[1][0], v[1][1], ah[1], al[1]);
+    c1m_split_trunc(v[0][2], v[0][3], ah[2], al[2]);
+    c1m_split_trunc(v[1][2], v[1][3], ah[3], al[3]);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      c1m_mma(acc[j], al, bh[s][j][0], bh[s][j][1]);            // small terms first
+      c1m_mma(acc[j], ah, bl[s][j][0], bl[s][j][1]);
+      c1m_mma(acc[j], ah, bh[s][j][0], bh[s][j][1]);
+    }
+  }
+}
 __global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                          const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
-                                                         int B, int H, int W, float slope, int frames, int tiles_x, int tiles_y) {
+                                                         int B, int H, int W, float slope, int frames, int tiles_x, int tiles_y,
+                                                         int n_tiles) {
   __shared__ __align__(16) float patch[3 * kC1M_IH * kC1M_PW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, c = lane & 3;
+  const uint32_t p_addr = (uint32_t)__cvta_generic_to_shared(patch);
   // ---- weights (independent of the previous kernel): B fragments of both n-tiles and k-steps, split hi / lo
   uint32_t bh[2][2][2], bl[2][2][2];                           // [k step][n-tile][k half]
-  int koff[2][4];                                               // patch offsets of this thread's 8 k indices (-1: padding)
+  uint32_t pa[2][4];                                            // smem address of this thread's 8 k indices, pixel g of m-tile 0
 #pragma unroll
   for (int s = 0; s < 2; ++s)
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const int k = 16 * s + 2 * c + (q & 1) + 8 * (q >> 1);
+      int k = 16 * s + 2 * c + (q & 1) + 8 * (q >> 1);
+      k = k < 27 ? k : 26;                                      // K padding: its weights are 0, any tap of the window will do
       const int ci = k / 9, ky = (k - 9 * ci) / 3, kx = k - 9 * ci - 3 * ky;
-      koff[s][q] = k < 27 ? (ci * kC1M_IH + ky) * kC1M_PW + kx : -1;
+      // input row 2*oy - 1 + ky -> patch row 2*warp + ky; input column 2*x - 1 + kx -> patch column 2*x + 3 + kx
+      pa[s][q] = p_addr + 4u * (uint32_t)((ci * kC1M_IH + ky + 2 * warp) * kC1M_PW + kx + 3 + 2 * g);
     }
 #pragma unroll
   for (int s = 0; s < 2; ++s)
@@ -141,69 +180,76 @@ __global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict
 
   const int Ho = H >> 1, Wo = W >> 1;
   const long hw = (long)H * W;
-  int tile = blockIdx.x;
-  const int tx = tile % tiles_x; tile /= tiles_x;
-  const int ty = tile % tiles_y; const int img = tile / tiles_y;
-  const float* src = frames ? x + (long)img * 3 * hw : x + ((long)(img % B) * 6 + (img / B) * 3) * hw;
-  const int ox0 = tx * 64, oy0 = ty * 8;
-  const int xs = 2 * ox0 - 4, ys = 2 * oy0 - 1;                 // patch origin; xs is a multiple of 4 like W
-  const uint32_t p_addr = (uint32_t)__cvta_generic_to_shared(patch);
-  for (int e = tid; e < 3 * kC1M_IH * (kC1M_PW / 4); e += 256) {
-    const int q = e % (kC1M_PW / 4), rr = e / (kC1M_PW / 4);
-    const int r = rr % kC1M_IH, ci = rr / kC1M_IH;
-    const int iy = ys + r, ix = xs + 4 * q;
-    const bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
-    const float* gp = ok ? src + ci * hw + (long)iy * W + ix : src;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(p_addr + (uint32_t)(rr * kC1M_PW + 4 * q) * 4u), "l"(gp),
-                 "r"(ok ? 16 : 0) : "memory");
-  }
-  asm volatile("cp.async.commit_group;" ::: "memory");
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncthreads();
-
-  const int oy = oy0 + warp;
-  if (oy >= Ho) return;
-  const float* prow = patch + (2 * warp) * kC1M_PW + 3;         // input row 2*oy - 1 + ky, column 2*x - 1 + kx (+4 - xs offset)
-#pragma unroll 1
-  for (int mt = 0; mt < 4; ++mt) {
-    if (ox0 + 16 * mt >= Wo) break;
-    float acc[2][4];
+  const float inv_tx = 1.0f / (float)tiles_x, inv_ty = 1.0f / (float)tiles_y;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    // tile -> (tx, ty, img) without integer divisions (exact below 2^20 tiles, checked by the launcher)
+    const int t2 = (int)(((float)tile + 0.5f) * inv_tx); const int tx = tile - t2 * tiles_x;
+    const int img = (int)(((float)t2 + 0.5f) * inv_ty); const int ty = t2 - img * tiles_y;
+    const float* src = frames ? x + (long)img * 3 * hw : x + ((long)(img % B) * 6 + (img / B) * 3) * hw;
+    const int ox0 = tx * 64, oy0 = ty * 8;
+    const int xs = 2 * ox0 - 4, ys = 2 * oy0 - 1;               // patch origin; xs is a multiple of 4 like W
+    // ---- stage the patch (3 planes x 17 rows x 33 quads of 16 bytes): warp = row (8 + 8, the 17th rows go to warps 0-2),
+    // lane = quad; the 33rd quads of the 51 rows are one more pass of threads 0-50.  32-bit element offsets inside the image.
+    {
+      const int lx = xs + 4 * lane;
+      const bool xok = lx >= 0 && lx < W;
+      const int ihw = (int)hw;
 #pragma unroll
-    for (int j = 0; j < 2; ++j)
+      for (int ci = 0; ci < 3; ++ci)
 #pragma unroll
-      for (int e = 0; e < 4; ++e) acc[j][e] = 0.f;
-    const float* p0 = prow + 2 * (16 * mt + g);                 // pixel row g of the m-tile; row g + 8 is 16 floats further
-#pragma unroll
-    for (int s = 0; s < 2; ++s) {
-      float v[2][4];                                            // [pixel row half][k index q]
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        v[0][q] = koff[s][q] >= 0 ? p0[koff[s][q]] : 0.f;
-        v[1][q] = koff[s][q] >= 0 ? p0[koff[s][q] + 16] : 0.f;
+        for (int rh = 0; rh < 2; ++rh) {
+          const int r = warp + 8 * rh, iy = ys + r;
+          const bool ok = xok && iy >= 0 && iy < H;
+          const int off = ok ? ci * ihw + iy * W + lx : 0;
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::
+                       "r"(p_addr + (uint32_t)((ci * kC1M_IH + r) * kC1M_PW * 4) + 16u * lane), "l"(src + off), "r"(ok ? 16 : 0) : "memory");
+        }
+      if (warp < 3) {
+        const int iy = ys + 16;
+        const bool ok = xok && iy < H;
+        const int off = ok ? warp * ihw + iy * W + lx : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::
+                     "r"(p_addr + (uint32_t)((warp * kC1M_IH + 16) * kC1M_PW * 4) + 16u * lane), "l"(src + off), "r"(ok ? 16 : 0) : "memory");
       }
-      uint32_t ah[4], al[4];                                    // a0: (g, k lo pair) a1: (g+8, k lo pair) a2: (g, k hi pair) a3: (g+8, hi)
-      c1m_split(v[0][0], v[0][1], ah[0], al[0]);
-      c1m_split(v[1][0], v[1][1], ah[1], al[1]);
-      c1m_split(v[0][2], v[0][3], ah[2], al[2]);
-      c1m_split(v[1][2], v[1][3], ah[3], al[3]);
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        c1m_mma(acc[j], al, bh[s][j][0], bh[s][j][1]);          // small terms first
-        c1m_mma(acc[j], ah, bl[s][j][0], bl[s][j][1]);
-        c1m_mma(acc[j], ah, bh[s][j][0], bh[s][j][1]);
+      if (tid < 3 * kC1M_IH) {
+        const int ci = tid / kC1M_IH, r = tid - ci * kC1M_IH, iy = ys + r;
+        const bool ok = xs + 128 < W && iy >= 0 && iy < H;
+        const int off = ok ? ci * ihw + iy * W + xs + 128 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::
+                     "r"(p_addr + (uint32_t)(tid * kC1M_PW * 4) + 512u), "l"(src + off), "r"(ok ? 16 : 0) : "memory");
       }
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    const int oy = oy0 + warp;
+    if (oy < Ho) {
+      __nv_bfloat16* orow = out + (((long)img * Ho + oy) * Wo + ox0 + g) * 16 + 2 * c;
 #pragma unroll
-    for (int j = 0; j < 2; ++j)
+      for (int mt = 0; mt < 4; ++mt) {
+        if (ox0 + 16 * mt >= Wo) break;
+        float acc[2][4];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int ox = ox0 + 16 * mt + g + 8 * h;
-        if (ox < Wo) {
-          const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
-          *reinterpret_cast<__nv_bfloat162*>(out + (((long)img * Ho + oy) * Wo + ox) * 16 + 8 * j + 2 * c) =
-              __floats2bfloat162_rn(lrelu(v0, slope), lrelu(v1, slope));
-        }
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[j][e] = 0.f;
+        if (mt == 0) c1m_tile<0>(pa, bh, bl, acc);
+        else if (mt == 1) c1m_tile<1>(pa, bh, bl, acc);
+        else if (mt == 2) c1m_tile<2>(pa, bh, bl, acc);
+        else c1m_tile<3>(pa, bh, bl, acc);
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            if (ox0 + 16 * mt + g + 8 * h < Wo) {
+              const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
+              *reinterpret_cast<__nv_bfloat162*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) =
+                  __floats2bfloat162_rn(lrelu(v0, slope), lrelu(v1, slope));
+            }
       }
+    }
+    __syncthreads();                                            // the patch is re-staged by the next tile
   }
 }
 
@@ -213,9 +259,11 @@ static int launch_conv1a(const float* x, const float* w, const float* bias, void
   if (use_mma && (W & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
     const int tiles_x = cdiv(W >> 1, 64), tiles_y = cdiv(H >> 1, 8);
     const long nt = (long)(frames ? B : 2 * B) * tiles_x * tiles_y;
-    if (nt <= 0x7fffffffL)
-      return (int)launch_pdl(conv1a_mma_kernel, dim3((unsigned)nt), dim3(256), 0, s, x, w, bias,
-                             reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y);
+    if (nt < (1L << 20) && 3L * H * W < 0x7fffffffL) {
+      static const int ctas = []() { const char* e = getenv("PWC_CONV1A_CTAS"); return e ? atoi(e) : 148 * 4; }();
+      return (int)launch_pdl(conv1a_mma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, x, w, bias,
+                             reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt);
+    }
   }
   return (int)launch_pdl(conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, s, x, w, bias, reinterpret_cast<__nv_bfloat16*>(out),
                          B, H, W, slope, frames);
