@@ -44,6 +44,22 @@ const char* pwc_b200_version(void);
 int pwc_corr_fwd(const void* f1, const void* f2, void* out,
                  int B, int C, int H, int W, int md, void* stream);
 
+/* (1b) Correlation backward: replaces correlation_cuda.backward()
+ *     models/correlation_package/correlation_cuda.cc:89-170 (binding),
+ *     models/correlation_package/correlation_cuda_kernel.cu:150-334 (correlation_backward_input1 / _input2), 430-564 (host),
+ *     same configuration as (1).  All tensors contiguous NCHW fp32; grad_out [B,(2md+1)^2,H,W];
+ *       grad_f1[n,c,y,x] = (1/C) * sum_{dy,dx} grad_out[n,tc,y,x]       * f2[n,c,y+dy,x+dx]
+ *       grad_f2[n,c,y,x] = (1/C) * sum_{dy,dx} grad_out[n,tc,y-dy,x-dx] * f1[n,c,y-dy,x-dx]
+ *     grad_f1 or grad_f2 may be NULL (not needed).  Deterministic (no atomics), no scratch tensors. */
+int pwc_corr_bwd(const float* f1, const float* f2, const float* grad_out, float* grad_f1, float* grad_f2,
+                 int B, int C, int H, int W, int md, void* stream);
+
+/* (1c) Standalone warp: replaces PWCDCNet.warp (models/PWCNet.py:141-177) for callers of that method:
+ *     out[n,c,y,x] = grid_sample(x, grid + flow*flow_scale, bilinear, zeros)[n,c,y,x] * (grid_sample(ones) >= mask_thresh)
+ *   x, out : [B,C,H,W] contiguous NCHW fp32; flow : [B,2,H,W] (u,v in pixels). */
+int pwc_warp_fwd(const float* x, const float* flow, float* out, int B, int C, int H, int W,
+                 float flow_scale, int align_corners, float mask_thresh, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * (2) Fused warp + validity mask + cost volume + LeakyReLU: replaces, in one kernel,
  *     PWCDCNet.warp (PWCNet.py:141-177), self.corr (correlation_cuda_kernel.cu:46-147 + the three

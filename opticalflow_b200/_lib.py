@@ -19,6 +19,8 @@ SIGNATURES = {
     "pwc_b200_arch": (_i, []),
     "pwc_b200_version": (ctypes.c_char_p, []),
     "pwc_corr_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "pwc_corr_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "pwc_warp_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _f, _vp]),
     "pwc_warp_corr_lrelu_fwd": (_i, [_vp, _l, _vp, _l, _vp, _l, _f, _i, _f, _f, _vp, _l,
                                      _i, _i, _i, _i, _i, _i, _i, _vp]),
     "pwc_conv3x3_f32_fwd": (_i, [_vp, _l, _i, _vp, _l, _i, _i, _vp, _vp, _vp, _l, _i, _vp, _l, _i, _i,

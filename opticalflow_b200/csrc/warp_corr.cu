@@ -561,6 +561,105 @@ extern "C" int pwc_corr_fwd(const void* f1, const void* f2, void* out, int B, in
                                  PWC_LAYOUT_NCHW, PWC_F32, stream);
 }
 
+namespace pwc {
+
+// Standalone PWCDCNet.warp (PWCNet.py:141-177) for callers of the reference's method; the forward itself never
+// materialises warped features (they are gathered inside the cost-volume kernels).  One thread = one output pixel: the
+// sample position / corner weights / mask once (warp_entry), then a channel loop of 4 gathers; stores coalesced along x.
+__global__ void __launch_bounds__(256) warp_nchw_kernel(WarpCorrParams p, const float* __restrict__ x, float* __restrict__ out) {
+  const long hw = (long)p.H * p.W, total = (long)p.B * hw;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int n = (int)(i / hw); const long r = i - (long)n * hw;
+    const int yy = (int)(r / p.W), xx = (int)(r - (long)yy * p.W);
+    const float u = p.flow[((long)n * 2) * hw + r], v = p.flow[((long)n * 2 + 1) * hw + r];
+    float4 w; uint2 xy;
+    warp_entry(p, u, v, xx, yy, w, xy);
+    const int x0 = xy.x & 0xffff, x1 = xy.x >> 16, y0 = xy.y & 0xffff, y1 = xy.y >> 16;
+    const long o00 = (long)y0 * p.W + x0, o01 = (long)y0 * p.W + x1, o10 = (long)y1 * p.W + x0, o11 = (long)y1 * p.W + x1;
+    const float* src = x + (long)n * p.C * hw;
+    float* dst = out + (long)n * p.C * hw + r;
+    for (int c = 0; c < p.C; ++c, src += hw, dst += hw) {
+      // ATen grid_sampler_2d: out = nw_val*nw + ne_val*ne + sw_val*sw + se_val*se, accumulated in that order; corners
+      // with weight 0 (outside / masked) are not read by ATen, so a NaN there must not leak: skip them the same way
+      float a = 0.f;
+      if (w.x != 0.f) a = fmaf(src[o00], w.x, a);
+      if (w.y != 0.f) a = fmaf(src[o01], w.y, a);
+      if (w.z != 0.f) a = fmaf(src[o10], w.z, a);
+      if (w.w != 0.f) a = fmaf(src[o11], w.w, a);
+      *dst = a;
+    }
+  }
+}
+
+// Correlation backward (correlation_cuda_kernel.cu:150-334, 430-564) for the PWC-Net configuration, NCHW fp32:
+//   gin1[n,c,y,x] = (1/C) sum_{dy,dx} gout[n,tc,y,x]       * f2[n,c,y+dy,x+dx]
+//   gin2[n,c,y,x] = (1/C) sum_{dy,dx} gout[n,tc,y-dy,x-dx] * f1[n,c,y-dy,x-dx]          tc = (dy+4)*9 + dx+4
+// (terms whose displaced pixel is outside the image are 0).  Both are "81 coefficients per pixel, independent of c, times
+// a 9x9 neighbourhood of the other feature map": SIGN = +1 / -1 selects which.  One thread = one pixel; the 81
+// coefficients live in registers; per channel 81 loads that are coalesced along x and served by L1.  No padded NHWC
+// copies (rInput1/rInput2 of correlation_cuda.cc:95-101), no atomics: deterministic.
+template <int SIGN>
+__global__ void __launch_bounds__(128) corr_bwd_kernel(const float* __restrict__ feat, const float* __restrict__ gout,
+                                                       float* __restrict__ gin, int B, int C, int H, int W) {
+  const long hw = (long)H * W;
+  const int xx = blockIdx.x * 32 + (threadIdx.x & 31), yy = blockIdx.y * 4 + (threadIdx.x >> 5), n = blockIdx.z;
+  if (xx >= W || yy >= H) return;
+  float g[kND * kND];
+  const float* go = gout + (long)n * (kND * kND) * hw;
+#pragma unroll
+  for (int dy = -kMD; dy <= kMD; ++dy)
+#pragma unroll
+    for (int dx = -kMD; dx <= kMD; ++dx) {
+      const int t = (dy + kMD) * kND + dx + kMD;
+      const int sy = yy + SIGN * dy, sx = xx + SIGN * dx;          // the pixel of the other map this term multiplies
+      const bool in = sy >= 0 && sy < H && sx >= 0 && sx < W;
+      // gin1: coefficient at the own pixel; gin2: at the displaced pixel (= where the forward read f1)
+      g[t] = in ? go[(long)t * hw + (SIGN > 0 ? (long)yy * W + xx : (long)sy * W + sx)] : 0.f;
+    }
+  const float fC = (float)C, rc = __frcp_rn(fC);
+  const float* f = feat + (long)n * C * hw;
+  float* dst = gin + (long)n * C * hw + (long)yy * W + xx;
+  for (int c = 0; c < C; ++c, f += hw, dst += hw) {
+    float a = 0.f;
+#pragma unroll
+    for (int dy = -kMD; dy <= kMD; ++dy) {
+      const int sy = yy + SIGN * dy;
+      if (sy < 0 || sy >= H) continue;
+      const float* row = f + (long)sy * W;
+#pragma unroll
+      for (int dx = -kMD; dx <= kMD; ++dx) {
+        const int sx = xx + SIGN * dx;
+        if (sx >= 0 && sx < W) a = fmaf(g[(dy + kMD) * kND + dx + kMD], __ldg(row + sx), a);
+      }
+    }
+    *dst = div_by(a, fC, rc);
+  }
+}
+
+}  // namespace pwc
+
+extern "C" int pwc_warp_fwd(const float* x, const float* flow, float* out, int B, int C, int H, int W,
+                            float flow_scale, int align_corners, float mask_thresh, void* stream) {
+  using namespace pwc;
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || H > 65535 || W > 65535 || !x || !flow || !out) return (int)cudaErrorInvalidValue;
+  WarpCorrParams p{x, 0, x, 0, flow, 0, flow_scale, align_corners, mask_thresh, 1.0f, out, 0, B, C, H, W, 0, 0, 0};
+  const long total = (long)B * H * W;
+  const long blocks = (total + 255) / 256;
+  warp_nchw_kernel<<<(unsigned)(blocks < 148L * 16 ? blocks : 148L * 16), 256, 0, (cudaStream_t)stream>>>(p, x, out);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int pwc_corr_bwd(const float* f1, const float* f2, const float* grad_out, float* grad_f1, float* grad_f2,
+                            int B, int C, int H, int W, int md, void* stream) {
+  using namespace pwc;
+  if (md != kMD || B <= 0 || C <= 0 || H <= 0 || W <= 0 || B > 65535 || (H + 3) / 4 > 65535 || !f1 || !f2 || !grad_out)
+    return (int)cudaErrorInvalidValue;
+  const dim3 grid((W + 31) / 32, (H + 3) / 4, B);
+  if (grad_f1) corr_bwd_kernel<1><<<grid, 128, 0, (cudaStream_t)stream>>>(f2, grad_out, grad_f1, B, C, H, W);
+  if (grad_f2) corr_bwd_kernel<-1><<<grid, 128, 0, (cudaStream_t)stream>>>(f1, grad_out, grad_f2, B, C, H, W);
+  return (int)cudaGetLastError();
+}
+
 // debug: timeline marks of the tensor-core cost-volume kernel (CTA 0), see tools/trace_corr.py
 extern "C" int pwc_debug_corr_trace(unsigned long long* host_dst, int count) {
   if (!host_dst || count < 0 || count > 3 * 64 * 4) return (int)cudaErrorInvalidValue;

@@ -113,8 +113,9 @@ class PWCDCNet(nn.Module):
 
     def warp(self, x, flo):
         """PWCNet.py:141-177 as a standalone op on NCHW tensors (the forward uses the fused kernel instead):
-        returns grid_sample(x, grid+flo) * mask computed by the same device code with an identity 'correlation'."""
-        raise NotImplementedError("warp() is fused into the cost-volume kernel; use opticalflow_b200.ops.warp_corr_lrelu")
+        returns grid_sample(x, grid+flo) * mask, one kernel (pwc_warp_fwd) sharing the fused kernels' sampling code."""
+        from ..ops import warp as _warp
+        return _warp(x, flo, align_corners=self.align_corners)
 
 
 def pwc_dc_net(path=None, **kw):

@@ -2,8 +2,8 @@
 
 Same constructor arguments and call signature as correlation.py:92-117; the forward calls the sm_100a kernel
 through the C ABI (``pwc_corr_fwd``, include/pwc_b200.h) instead of ``correlation_cuda.forward``
-(correlation.py:70).  Inference only: there is no backward (the reference drivers run under no_grad:
-inference.py:193, pwc_extract_flow_video.py:191).  There is no CPU or pure-torch fallback.
+(correlation.py:70), the backward calls ``pwc_corr_bwd`` instead of ``correlation_cuda.backward`` (correlation.py:86-90).
+There is no CPU or pure-torch fallback.
 """
 import torch
 import torch.nn as nn
@@ -35,16 +35,43 @@ def correlation_forward(input1, input2, pad_size=4, kernel_size=1, max_displacem
     return out
 
 
+def correlation_backward(input1, input2, grad_output, max_displacement=4, need1=True, need2=True):
+    """(grad_input1, grad_input2) of correlation_forward (correlation_cuda_kernel.cu:150-334); None where not needed."""
+    if not (input1.is_cuda and input2.is_cuda and grad_output.is_cuda):
+        raise RuntimeError("Correlation: CUDA tensors required (no CPU fallback)")
+    if max_displacement != 4:
+        raise NotImplementedError("only the PWC-Net configuration pad=md=4, k=1, strides 1 is built (PWCNet.py:71)")
+    B, C, H, W = input1.shape
+    if tuple(grad_output.shape) != (B, (2 * max_displacement + 1) ** 2, H, W) or grad_output.dtype != torch.float32:
+        raise RuntimeError("Correlation backward: grad_output must be float32 [B,81,H,W]")
+    lib = _lib.load()
+    a, b, g = input1.contiguous(), input2.contiguous(), grad_output.contiguous()
+    g1 = torch.empty_like(a) if need1 else None
+    g2 = torch.empty_like(b) if need2 else None
+    with torch.cuda.device_of(a):
+        err = lib.pwc_corr_bwd(_lib.ptr(a), _lib.ptr(b), _lib.ptr(g), _lib.ptr(g1), _lib.ptr(g2), B, C, H, W,
+                               max_displacement, _lib.stream_handle())
+    if err != 0:
+        raise RuntimeError("CUDA call failed")   # correlation_cuda.cc:166-168
+    return g1, g2
+
+
 class CorrelationFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, input1, input2, pad_size=3, kernel_size=3, max_displacement=20, stride1=1, stride2=2,
                 corr_multiply=1):
-        return correlation_forward(input1, input2, pad_size, kernel_size, max_displacement, stride1, stride2,
-                                   corr_multiply)
+        out = correlation_forward(input1, input2, pad_size, kernel_size, max_displacement, stride1, stride2,
+                                  corr_multiply)
+        ctx.save_for_backward(input1, input2)
+        ctx.max_displacement = max_displacement
+        return out
 
     @staticmethod
     def backward(ctx, grad_output):
-        raise NotImplementedError("correlation backward is out of scope (inference path)")
+        input1, input2 = ctx.saved_tensors
+        g1, g2 = correlation_backward(input1, input2, grad_output.float(), ctx.max_displacement,
+                                      ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+        return g1, g2, None, None, None, None, None, None
 
 
 class Correlation(nn.Module):

@@ -39,6 +39,25 @@ def warp_corr_lrelu(f1, f2, flow=None, flow_scale=1.0, align_corners=False, mask
     return out
 
 
+def warp(x, flo, flow_scale=1.0, align_corners=False, mask_thresh=0.9999):
+    """PWCDCNet.warp (PWCNet.py:141-177): x [B,C,H,W], flo [B,2,H,W] (pixels) -> grid_sample(x, grid + flo) * mask."""
+    if not (x.is_cuda and flo.is_cuda):
+        raise RuntimeError("warp: CUDA tensors required (no CPU fallback)")
+    if x.dim() != 4 or flo.dim() != 4 or flo.shape[1] != 2 or flo.shape[0] != x.shape[0] or flo.shape[2:] != x.shape[2:]:
+        raise RuntimeError("warp: x [B,C,H,W] and flo [B,2,H,W] expected")
+    if x.dtype != torch.float32 or flo.dtype != torch.float32:
+        raise RuntimeError("expected scalar type Float")          # as grid.float() + grid_sample in the reference (SURVEY F6)
+    x, flo = x.contiguous(), flo.contiguous()
+    B, C, H, W = x.shape
+    out = torch.empty_like(x)
+    lib = _lib.load()
+    with torch.cuda.device_of(x):
+        e = lib.pwc_warp_fwd(_lib.ptr(x), _lib.ptr(flo), _lib.ptr(out), B, C, H, W, float(flow_scale), int(bool(align_corners)),
+                             float(mask_thresh), _lib.stream_handle())
+    _lib.check(e, "pwc_warp_fwd")
+    return out
+
+
 def conv3x3_f32(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=None, out=None, out_coff=0,
                 chan_map=None, residual=None):
     """fp32 CUDA-core conv (pwc_conv3x3_f32_fwd) on an NHWC tensor x [N,H,W,pitch]; reads channels

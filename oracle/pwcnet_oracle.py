@@ -149,6 +149,30 @@ def correlation_mean(f1, f2, md=MD):
     return torch.cat(outs, dim=1) / float(C)
 
 
+def correlation_backward_numpy(f1, f2, gout, md=MD):
+    """(grad_f1, grad_f2) of correlation_mean, restated from correlation_cuda_kernel.cu:150-334 with numpy slices
+    (fp64 accumulation):
+      grad_f1[n,c,y,x] = (1/C) sum_{dy,dx} gout[n,tc,y,x]       * f2[n,c,y+dy,x+dx]      (:150-237, correlation_backward_input1)
+      grad_f2[n,c,y,x] = (1/C) sum_{dy,dx} gout[n,tc,y-dy,x-dx] * f1[n,c,y-dy,x-dx]      (:241-334, correlation_backward_input2)
+    tc = (dy+md)*(2md+1) + (dx+md); terms whose displaced pixel is outside the image vanish (zero padding)."""
+    import numpy as np
+    f1, f2, gout = (np.asarray(a, dtype=np.float64) for a in (f1, f2, gout))
+    B, C, H, W = f1.shape
+    g1, g2 = np.zeros_like(f1), np.zeros_like(f2)
+    nd = 2 * md + 1
+    for dy in range(-md, md + 1):
+        for dx in range(-md, md + 1):
+            t = (dy + md) * nd + dx + md
+            ya, yb = max(0, -dy), min(H, H - dy)            # pixels (y,x) whose partner (y+dy, x+dx) is inside
+            xa, xb = max(0, -dx), min(W, W - dx)
+            if ya >= yb or xa >= xb:
+                continue
+            g = gout[:, t:t + 1, ya:yb, xa:xb]
+            g1[:, :, ya:yb, xa:xb] += g * f2[:, :, ya + dy:yb + dy, xa + dx:xb + dx]
+            g2[:, :, ya + dy:yb + dy, xa + dx:xb + dx] += g * f1[:, :, ya:yb, xa:xb]
+    return (g1 / C).astype(np.float32), (g2 / C).astype(np.float32)
+
+
 def warp(x, flo, align_corners=False, mask_thresh=0.9999):
     """PWCDCNet.warp (PWCNet.py:141-177) without the hard-wired ``.cuda()``.
 
