@@ -153,6 +153,7 @@ class PlanBF16:
         self.ops = []
         self.op_info = []          # (name, algorithmic flops) per launch, for profiling tools
         self.graph = None
+        self.graph_tail = None     # ops[1:] as a graph, for run_from()
         self.launches = 0
 
     def __del__(self):
@@ -293,6 +294,7 @@ class PlanBF16:
         self.op_info.append(("conv1a.0", 2.0 * NP * (self.H // 2) * (self.W // 2) * 16 * 27))
         c1a = lib.pwc_conv1a_frames_bf16_fwd if vid else lib.pwc_conv1a_bf16_fwd
         self.ops.append(lambda st: _lib.check(c1a(*a1, st), "conv1a"))
+        self._conv1a_on = lambda x, st: _lib.check(c1a(_lib.ptr(x), *a1[1:], st), "conv1a")      # ops[0] on another input
         for l in range(1, 7):
             names = (f"conv{l}a", f"conv{l}aa", f"conv{l}b") if l < 6 else ("conv6aa", "conv6a", "conv6b")
             h, w = self.hw[l]
@@ -472,6 +474,34 @@ class PlanBF16:
                 self._launch_all()
             self.graph = g
         self.graph.replay()
+        return self.out
+
+    def run_from(self, x, release=None):
+        """Same as run(), but the first layer reads the caller's device tensor `x` ([B,6,H,W] fp32, contiguous; [B+1,3,H,W]
+        for a video plan) in place: conv1a -- the only reader of the input -- is launched eagerly on `x` and the other
+        launches replay as one CUDA graph.  Saves the 2 x 11 MB/pair device-to-device copy into the static input; `x` may
+        be overwritten as soon as conv1a has run: `release` (a torch.cuda.Event) is recorded right behind it."""
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.shape != self.x_static.shape or x.data_ptr() % 16:
+            raise RuntimeError("run_from: a contiguous, 16-byte aligned fp32 tensor of the plan's input shape expected")
+        if not self.use_graph:
+            self.x_static.copy_(x, non_blocking=True)
+            if release is not None:
+                release.record(torch.cuda.current_stream())
+            self._launch_all()
+            return self.out
+        if self.graph_tail is None:
+            self._launch_all()
+            torch.cuda.current_stream().synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                st = _lib.stream_handle()
+                for op in self.ops[1:]:
+                    op(st)
+            self.graph_tail = g
+        self._conv1a_on(x, _lib.stream_handle())
+        if release is not None:
+            release.record(torch.cuda.current_stream())
+        self.graph_tail.replay()
         return self.out
 
     def time_ops(self, reps=3, inner=8):

@@ -96,3 +96,24 @@ def test_video_pipeline_matches_reference_steps(full_res, share):
         assert got[t].shape == ref.shape[1:]
         tol = 1e-5 * max(1.0, ref.abs().max().item())
         assert (got[t] - ref[0]).abs().max().item() <= tol, f"pair {t}"
+
+
+def test_run_from_reads_the_callers_tensor_in_place():
+    """plan.run_from(x): conv1a on the caller's buffer + the rest as a graph == plan.run(x); the release event fires."""
+    from opticalflow_b200.models.PWCNet import PWCDCNet
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(2)
+    m = PWCDCNet(conv_mode="bf16").eval().to(dev)
+    B, H, W = 2, 64, 128
+    plan = m._plan(B, H, W, dev)
+    plan.pack_weights(m)
+    for seed in (3, 4):
+        x = O.synthetic_input(B, H, W, seed).to(dev)
+        want = plan.run(x).clone()
+        plan.x_static.zero_()                               # prove the static input is not what run_from reads
+        ev = torch.cuda.Event()
+        got = plan.run_from(x, release=ev).clone()
+        ev.synchronize()
+        assert torch.equal(got, want)
+    with pytest.raises(RuntimeError):
+        plan.run_from(x[:, :, :, ::2])
