@@ -253,6 +253,135 @@ static int launch_thin(ThinConvParams& p, cudaStream_t s) {
 
 }  // namespace pwc
 
+namespace pwc {
+
+// ---- 16 -> 16 channels, stride 1 (conv1aa, conv1b: half-resolution layers, 32-byte pixels; HBM bound: 64 B of traffic per
+// output pixel against 9.2 kFLOP).  The generic kernel above spends ~200 warp instructions per 16-pixel m-tile on this shape
+// (weights re-read from shared memory for every m-tile, transpose epilogue); here ALL weight fragments of the layer live in
+// 36 registers, a tap is one ldmatrix.x4 whose address is a per-lane base + compile-time offset, and the epilogue stores
+// bf16 pairs straight from the accumulators (the two n-tiles complete every 32-byte pixel).  Persistent CTAs; tile = 8 rows
+// x 64 pixels, warp = row; the 10 x 66-pixel patch is staged with cp.async (zero fill = padding), its two 16-byte halves
+// swapped on every other group of 4 pixels so that the 8 row addresses of an ldmatrix phase hit 8 different bank groups.
+constexpr int kC16PW = 66, kC16IH = 10, kC16Patch = kC16IH * kC16PW * 32;
+
+template <int OFF>
+__device__ __forceinline__ void c16_ldsm4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4+%5];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr), "n"(OFF));
+}
+template <int MT, int KY>
+__device__ __forceinline__ void c16_taps(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][4]) {
+#pragma unroll
+  for (int kx = 0; kx < 3; ++kx) {
+    uint32_t a[4];
+    c16_ldsm4<(KY * kC16PW + 16 * MT) * 32>(a, abase[kx]);
+    thin_mma(acc[0], a, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    thin_mma(acc[1], a, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+  }
+}
+template <int MT>
+__device__ __forceinline__ void c16_tile(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][4]) {
+  c16_taps<MT, 0>(abase, bw, acc);
+  c16_taps<MT, 1>(abase, bw, acc);
+  c16_taps<MT, 2>(abase, bw, acc);
+}
+
+__global__ void __launch_bounds__(256) conv_c16_kernel(const ThinConvParams p, int n_tiles) {
+  __shared__ __align__(128) unsigned char patch[kC16Patch];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, c = lane & 3;
+  const uint32_t p_addr = (uint32_t)__cvta_generic_to_shared(patch);
+  // weights [9][16 cout][16 cin]: B fragment of (tap, n-tile j) = rows 8j+g, k pairs {2c,2c+1} and {2c+8,2c+9}
+  uint32_t bw[9][2][2];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const uint32_t* wr = reinterpret_cast<const uint32_t*>(p.w + (t * 16 + 8 * j + g) * 16);
+      bw[t][j][0] = __ldg(wr + c); bw[t][j][1] = __ldg(wr + 4 + c);
+    }
+  float bia[2][2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) { bia[j][0] = p.bias[8 * j + 2 * c]; bia[j][1] = p.bias[8 * j + 2 * c + 1]; }
+  // ldmatrix row of this lane: matrix m = lane / 8 -> pixels 8*(m & 1) + (lane & 7), channel half m >> 1
+  uint32_t abase[3];
+  {
+    const int px = (lane & 7) + 8 * ((lane >> 3) & 1), half = lane >> 4;
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const int q = px + kx;                                     // patch column of m-tile 0 (16 * MT more: same swap phase)
+      abase[kx] = p_addr + (uint32_t)((warp * kC16PW + q) * 32 + 16 * (half ^ ((q >> 2) & 1)));
+    }
+  }
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int H = p.H, W = p.W;
+  const float inv_tx = 1.0f / (float)p.tiles_x, inv_ty = 1.0f / (float)p.tiles_y;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int t2 = (int)(((float)tile + 0.5f) * inv_tx); const int tx = tile - t2 * p.tiles_x;
+    const int img = (int)(((float)t2 + 0.5f) * inv_ty); const int ty = t2 - img * p.tiles_y;
+    const int ox0 = tx * 64, oy0 = ty * 8;
+    const bool sec = p.in2 != nullptr && img >= p.n_split_in;
+    const __nv_bfloat16* src = sec ? p.in2 + ((long)(img - p.n_split_in) * H * W) * p.in2_pitch + p.in2_coff
+                                   : p.in + ((long)img * H * W) * p.in_pitch + p.in_coff;
+    const int pitch = (int)(sec ? p.in2_pitch : p.in_pitch);
+    // ---- stage: 10 rows x 66 pixels x 2 halves of 16 bytes
+    for (int e = tid; e < kC16IH * kC16PW * 2; e += 256) {
+      const int r = e / (kC16PW * 2), ch = e - r * (kC16PW * 2);
+      const int q = ch >> 1, h = ch & 1;
+      const int iy = oy0 - 1 + r, ix = ox0 - 1 + q;
+      const bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
+      const int off = ok ? (iy * W + ix) * pitch + 8 * h : 0;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::
+                   "r"(p_addr + (uint32_t)((r * kC16PW + q) * 32 + 16 * (h ^ ((q >> 2) & 1)))), "l"(src + off), "r"(ok ? 16 : 0) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+
+    const int oy = oy0 + warp;
+    if (oy < H) {
+      const bool second = p.out2 != nullptr && img >= p.n_split;
+      __nv_bfloat16* orow = second ? p.out2 + (((long)(img - p.n_split) * H + oy) * W + ox0 + g) * p.out2_pitch + p.out2_coff + 2 * c
+                                   : p.out + (((long)img * H + oy) * W + ox0 + g) * p.out_pitch + p.out_coff + 2 * c;
+      const long opitch = second ? p.out2_pitch : p.out_pitch;
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) {
+        if (ox0 + 16 * mt >= W) break;
+        float acc[2][4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[j][e] = 0.f;
+        if (mt == 0) c16_tile<0>(abase, bw, acc);
+        else if (mt == 1) c16_tile<1>(abase, bw, acc);
+        else if (mt == 2) c16_tile<2>(abase, bw, acc);
+        else c16_tile<3>(abase, bw, acc);
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            if (ox0 + 16 * mt + g + 8 * h < W) {
+              const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
+              *reinterpret_cast<__nv_bfloat162*>(orow + (16 * mt + 8 * h) * opitch + 8 * j) =
+                  __floats2bfloat162_rn(lrelu(v0, p.slope), lrelu(v1, p.slope));
+            }
+      }
+    }
+    __syncthreads();                                            // the patch is re-staged by the next tile
+  }
+}
+
+static int launch_c16(ThinConvParams& p, cudaStream_t s) {
+  p.tiles_x = cdiv(p.W, 64); p.tiles_y = cdiv(p.H, 8);
+  const long nt = (long)p.N * p.tiles_x * p.tiles_y;
+  static const int ctas = []() { const char* e = getenv("PWC_THIN_C16_CTAS"); return e ? atoi(e) : 148 * 3; }();
+  return (int)launch_pdl(conv_c16_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, p, (int)nt);
+}
+
+}  // namespace pwc
+
 static int thin_dispatch(pwc::ThinConvParams& p, int nt8, int ks, cudaStream_t s) {
   using namespace pwc;
 #define PWC_THIN(NTv, KSv) if (nt8 == NTv && ks == KSv) return launch_thin<NTv, KSv>(p, s)
@@ -310,5 +439,10 @@ extern "C" int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
   p.ih = 7 * stride + 3;
   p.pp = 2 * cin + 16; p.wp = 2 * cin + 16;
   p.flow_out = nullptr; p.residual = nullptr; p.res_pitch = 0;
+  static const int use_c16 = []() { const char* e = getenv("PWC_THIN_C16"); return e ? atoi(e) : 1; }();
+  const long max_pitch = in_pitch > in2_pitch ? in_pitch : in2_pitch;
+  if (use_c16 && cin == 16 && cout == 16 && stride == 1 && (long)N * cdiv(H, 8) * cdiv(W, 64) < (1L << 20) &&
+      (long)H * W * max_pitch < 0x7fffffffL)
+    return launch_c16(p, (cudaStream_t)stream);
   return thin_dispatch(p, cout / 8, cin / 16, (cudaStream_t)stream);
 }

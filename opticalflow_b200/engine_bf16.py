@@ -107,7 +107,7 @@ SMALL_LAYERS = set(x for x in os.environ.get("PWC_MMA_SMALL_LAYERS", _SMALL_DEFA
 # Thin pyramid layers routed to the persistent warp-MMA kernel (csrc/conv_thin.cu).  Measured on B200 (batch 8): conv2a
 # (16 -> 32, stride 2) 62.7 -> 41.6 us, conv2b 44 -> 41 us; the other stride-1 layers are on par with or slower than the tcgen05
 # space-to-depth path (conv1aa 60.8 vs 58.7 us, conv3aa 37 vs 23 us).
-THIN_LAYERS = set(x for x in os.environ.get("PWC_THIN_LAYERS", "conv2a.0,conv2b.0").split(",") if x and x != "none")
+THIN_LAYERS = set(x for x in os.environ.get("PWC_THIN_LAYERS", "conv1aa.0,conv1b.0,conv2a.0,conv2b.0").split(",") if x and x != "none")
 
 
 class _TcLayer:
@@ -314,12 +314,14 @@ class PlanBF16:
             fl = 2.0 * NP * h * w * C * C * 9
             va = self.pa[l].view(NP, h, w // g, g * PYR_CP[l]) if g > 1 else self.pa[l]
             vb = self.pb[l].view(NP, h, w // g, g * PYR_CP[l]) if g > 1 else self.pb[l]
-            if g > 1:
+            if g > 1 and names[1] + ".0" not in THIN_LAYERS:
                 self._tc(names[1] + ".0", g * C, g * C, va, 0, g * C, vb, 0, NP, h, w // g,
                          wfn=_s2d_weights(names[1] + ".0", g), flops=fl, kkskip=True)
             else:
                 self._tc(names[1] + ".0", C, C, self.pa[l], 0, PYR_CP[l], self.pb[l], 0, NP, h, w)
-            if l == 1:
+            if l == 1 and names[2] + ".0" in THIN_LAYERS:
+                self._tc(names[2] + ".0", C, C, self.pb[l], 0, PYR_CP[l], self.pa[l], 0, NP, h, w)
+            elif l == 1:
                 self._tc(names[2] + ".0", g * C, g * C, vb, 0, g * C, va, 0, NP, h, w // g,
                          wfn=_s2d_weights(names[2] + ".0", g), flops=fl, kkskip=True)
             elif l < 6:
