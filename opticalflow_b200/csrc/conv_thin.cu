@@ -269,24 +269,28 @@ __device__ __forceinline__ void c16_ldsm4(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4+%5];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr), "n"(OFF));
 }
+// two m-tiles (MT, MT + 1) per call: four independent accumulator chains hide the HMMA / ldmatrix latency
 template <int MT, int KY>
-__device__ __forceinline__ void c16_taps(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][4]) {
+__device__ __forceinline__ void c16_taps(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
 #pragma unroll
   for (int kx = 0; kx < 3; ++kx) {
-    uint32_t a[4];
-    c16_ldsm4<(KY * kC16PW + 16 * MT) * 32>(a, abase[kx]);
-    thin_mma(acc[0], a, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
-    thin_mma(acc[1], a, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+    uint32_t a0[4], a1[4];
+    c16_ldsm4<(KY * kC16PW + 16 * MT) * 32>(a0, abase[kx]);
+    c16_ldsm4<(KY * kC16PW + 16 * MT + 16) * 32>(a1, abase[kx]);
+    thin_mma(acc[0][0], a0, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    thin_mma(acc[0][1], a0, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+    thin_mma(acc[1][0], a1, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    thin_mma(acc[1][1], a1, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
   }
 }
 template <int MT>
-__device__ __forceinline__ void c16_tile(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][4]) {
+__device__ __forceinline__ void c16_tile(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
   c16_taps<MT, 0>(abase, bw, acc);
   c16_taps<MT, 1>(abase, bw, acc);
   c16_taps<MT, 2>(abase, bw, acc);
 }
 
-__global__ void __launch_bounds__(256) conv_c16_kernel(const ThinConvParams p, int n_tiles) {
+__global__ void __launch_bounds__(256, 3) conv_c16_kernel(const ThinConvParams p, int n_tiles) {
   __shared__ __align__(128) unsigned char patch[kC16Patch];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, c = lane & 3;
@@ -326,15 +330,22 @@ __global__ void __launch_bounds__(256) conv_c16_kernel(const ThinConvParams p, i
     const __nv_bfloat16* src = sec ? p.in2 + ((long)(img - p.n_split_in) * H * W) * p.in2_pitch + p.in2_coff
                                    : p.in + ((long)img * H * W) * p.in_pitch + p.in_coff;
     const int pitch = (int)(sec ? p.in2_pitch : p.in_pitch);
-    // ---- stage: 10 rows x 66 pixels x 2 halves of 16 bytes
-    for (int e = tid; e < kC16IH * kC16PW * 2; e += 256) {
-      const int r = e / (kC16PW * 2), ch = e - r * (kC16PW * 2);
-      const int q = ch >> 1, h = ch & 1;
+    // ---- stage: 10 rows x 66 pixels x 2 halves of 16 bytes = 40 warp items of 32 chunks (row, 16-pixel quarter) + the last
+    // two pixels of the 10 rows (40 chunks: items 40, 41); item = warp + 8 i
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      const int it = warp + 8 * i;
+      if (it >= 42) break;
+      int r, q;
+      if (it < 40) { r = it >> 2; q = (lane >> 1) + 16 * (it & 3); }
+      else { const int idx = (it - 40) * 32 + lane; r = idx >> 2; q = 64 + ((idx >> 1) & 1); }
+      const int h = lane & 1;
       const int iy = oy0 - 1 + r, ix = ox0 - 1 + q;
-      const bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
+      const bool ok = r < kC16IH && iy >= 0 && iy < H && ix >= 0 && ix < W;
       const int off = ok ? (iy * W + ix) * pitch + 8 * h : 0;
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::
-                   "r"(p_addr + (uint32_t)((r * kC16PW + q) * 32 + 16 * (h ^ ((q >> 2) & 1)))), "l"(src + off), "r"(ok ? 16 : 0) : "memory");
+      if (r < kC16IH)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::
+                     "r"(p_addr + (uint32_t)((r * kC16PW + q) * 32 + 16 * (h ^ ((q >> 2) & 1)))), "l"(src + off), "r"(ok ? 16 : 0) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -347,26 +358,28 @@ __global__ void __launch_bounds__(256) conv_c16_kernel(const ThinConvParams p, i
                                    : p.out + (((long)img * H + oy) * W + ox0 + g) * p.out_pitch + p.out_coff + 2 * c;
       const long opitch = second ? p.out2_pitch : p.out_pitch;
 #pragma unroll
-      for (int mt = 0; mt < 4; ++mt) {
-        if (ox0 + 16 * mt >= W) break;
-        float acc[2][4];
+      for (int mp = 0; mp < 2; ++mp) {                          // pairs of 16-pixel m-tiles
+        if (ox0 + 32 * mp >= W) break;
+        float acc[2][2][4];
 #pragma unroll
-        for (int j = 0; j < 2; ++j)
+        for (int m = 0; m < 2; ++m)
 #pragma unroll
-          for (int e = 0; e < 4; ++e) acc[j][e] = 0.f;
-        if (mt == 0) c16_tile<0>(abase, bw, acc);
-        else if (mt == 1) c16_tile<1>(abase, bw, acc);
-        else if (mt == 2) c16_tile<2>(abase, bw, acc);
-        else c16_tile<3>(abase, bw, acc);
+          for (int j = 0; j < 2; ++j)
 #pragma unroll
-        for (int j = 0; j < 2; ++j)
+            for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
+        if (mp == 0) c16_tile<0>(abase, bw, acc);
+        else c16_tile<2>(abase, bw, acc);
 #pragma unroll
-          for (int h = 0; h < 2; ++h)
-            if (ox0 + 16 * mt + g + 8 * h < W) {
-              const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
-              *reinterpret_cast<__nv_bfloat162*>(orow + (16 * mt + 8 * h) * opitch + 8 * j) =
-                  __floats2bfloat162_rn(lrelu(v0, p.slope), lrelu(v1, p.slope));
-            }
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              if (ox0 + 32 * mp + 16 * m + g + 8 * h < W) {
+                const float v0 = acc[m][j][2 * h] + bia[j][0], v1 = acc[m][j][2 * h + 1] + bia[j][1];
+                *reinterpret_cast<__nv_bfloat162*>(orow + (32 * mp + 16 * m + 8 * h) * opitch + 8 * j) =
+                    __floats2bfloat162_rn(lrelu(v0, p.slope), lrelu(v1, p.slope));
+              }
       }
     }
     __syncthreads();                                            // the patch is re-staged by the next tile
