@@ -192,6 +192,7 @@ def test_conv3x3_mma_small_matches_torch(case):
     (16, 16, 1, 2, 24, 40), (16, 32, 2, 2, 30, 70), (32, 32, 1, 1, 9, 33), (16, 64, 2, 3, 17, 31), (64, 64, 1, 2, 16, 64),
     (16, 16, 1, 4, 224, 512), (16, 32, 2, 2, 224, 512), (64, 32, 1, 1, 8, 32), (16, 16, 2, 1, 5, 7), (32, 64, 1, 2, 56, 128),
     (16, 16, 1, 3, 13, 100), (16, 16, 1, 1, 1, 1), (16, 16, 1, 2, 9, 129),      # the 16 -> 16 kernel: ragged rows / columns
+    (32, 32, 1, 2, 24, 70), (32, 32, 1, 4, 112, 256), (32, 32, 1, 1, 1, 1),     # the 32 -> 32 kernel
 ])
 def test_conv3x3_thin_matches_torch(case):
     """pwc_conv3x3_thin_fwd against torch conv2d on the same bf16-rounded operands; channel slices of wider tensors."""
