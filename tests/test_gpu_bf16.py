@@ -66,9 +66,9 @@ def test_conv3x3_tc_matches_torch(case):
     assert (out - ref).abs().max().item() <= tol
 
 
-@pytest.mark.parametrize("shape", [(2, 64, 96), (1, 72, 200), (2, 130, 516), (1, 448, 1024)])
+@pytest.mark.parametrize("shape", [(2, 64, 96), (1, 72, 200), (2, 130, 516), (1, 448, 1024), (1, 10, 66), (1, 2, 4)])
 def test_conv1a_bf16_matches_torch(shape):
-    """tiles of 8 x 128 output pixels: ragged in both directions, one tile, many tiles"""
+    """tiles of 8 x 64 output pixels: ragged in both directions, one tile, many tiles; W % 4 != 0 takes the CUDA-core kernel"""
     from opticalflow_b200 import ops
     g = torch.Generator().manual_seed(5)
     x = torch.rand(shape[0], 6, shape[1], shape[2], generator=g)
@@ -80,6 +80,29 @@ def test_conv1a_bf16_matches_torch(shape):
                      F.leaky_relu(F.conv2d(x[:, 3:], w, b, stride=2, padding=1), 0.1)], 0)
     assert out.shape == ref.shape
     assert (out - ref).abs().max().item() <= 8e-3 * ref.abs().max().item()
+
+
+def test_conv1a_split_keeps_fp32_grade_inputs():
+    """The tensor-core conv1a splits x and w into bf16 hi + lo parts (3 products, lo*lo dropped: ~2^-16 relative error
+    against 2^-9 for a plain bf16 cast): its bf16 output must be the correctly rounded fp64 result in >= 99% of the elements
+    (measured 99.4%: the rest sit within 2^-16 of a rounding boundary) and never more than one bf16 ulp away."""
+    from opticalflow_b200 import ops
+    g = torch.Generator().manual_seed(6)
+    x = torch.rand(2, 6, 96, 256, generator=g)
+    w = torch.randn(16, 3, 3, 3, generator=g) / 5.0
+    b = torch.randn(16, generator=g) * 0.1
+    d = torch.device("cuda:0")
+    out = ops.conv1a_bf16(x.to(d), w.to(d), b.to(d)).permute(0, 3, 1, 2).cpu()
+    ref64 = torch.cat([F.leaky_relu(F.conv2d(x[:, :3].double(), w.double(), b.double(), stride=2, padding=1), 0.1),
+                       F.leaky_relu(F.conv2d(x[:, 3:].double(), w.double(), b.double(), stride=2, padding=1), 0.1)], 0)
+    want = ref64.float().bfloat16()
+    exact = (out == want).float().mean().item()
+    ulp = torch.maximum(want.float().abs(), torch.tensor(2.0 ** -126)) * 2.0 ** -7      # >= 1 bf16 ulp of the value
+    assert exact >= 0.99, exact
+    assert ((out.float() - want.float()).abs() <= ulp).all()
+    cast = torch.cat([F.leaky_relu(F.conv2d(x[:, :3].bfloat16().float(), w.bfloat16().float(), b, stride=2, padding=1), 0.1),
+                      F.leaky_relu(F.conv2d(x[:, 3:].bfloat16().float(), w.bfloat16().float(), b, stride=2, padding=1), 0.1)], 0)
+    assert (cast.bfloat16() == want).float().mean().item() < exact - 0.1            # what the split buys
 
 
 @pytest.mark.parametrize("idt,odt", [(torch.bfloat16, torch.bfloat16), (torch.float32, torch.bfloat16), (torch.bfloat16, torch.float32)])
