@@ -219,6 +219,23 @@ def run_ours(args):
     t_e2e = e0.elapsed_time(e1) * 1e-3
     assert len(got) == args.steps
     barrier()
+    # the same pairs handed over as uint8 BGR frames (what the reference drivers hold before frame_to_tensor): /255 + pad +
+    # cat run on the GPU, 6 bytes per pixel pair go over PCIe instead of 24 -- reported beside the fp32-input figure
+    t_u8 = None
+    if args.mode == "bf16":
+        gen = torch.Generator().manual_seed(7 + rank)
+        u8_hosts = [torch.randint(0, 256, (B, 2, H, W, 3), dtype=torch.uint8, generator=gen).pin_memory() for _ in range(2)]
+        pipe8 = driver.FlowPipeline(model, B, H, W, dev, input="u8")
+        got8 = []
+        pipe8.run((u8_hosts[i % 2] for i in range(3)))
+        barrier()
+        e0.record()
+        pipe8.run((u8_hosts[i % 2] for i in range(args.steps)), sink=lambda i, f: got8.append(float(f[0, 0, 0, 0])))
+        e1.record(); e1.synchronize()
+        t_u8 = e0.elapsed_time(e1) * 1e-3
+        assert len(got8) == args.steps
+        del pipe8
+        barrier()
     # unpipelined variant (one blocking model(x) call per step), reported beside it
     out_host = torch.empty(B, 2, H // 4, W // 4).pin_memory()
     for _ in range(2):
@@ -232,7 +249,8 @@ def run_ours(args):
     barrier()
     clocks = sampler.stop() if sampler else None
     if world > 1:
-        t_dev, t_e2e, t_sync = driver.max_over_ranks([t_dev, t_e2e, t_sync], device=dev)
+        t_dev, t_e2e, t_sync, t_u8x = driver.max_over_ranks([t_dev, t_e2e, t_sync, t_u8 if t_u8 is not None else 0.0], device=dev)
+        t_u8 = t_u8x if t_u8 is not None else None
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -300,7 +318,10 @@ def run_ours(args):
         "e2e": {"value": pairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": x_host.numel() * 4 * world,
                 "d2h_bytes_per_step": out_host.numel() * 4 * world,
                 "api": "opticalflow_b200.driver.FlowPipeline.run (copy/compute overlapped)",
-                "blocking_model_call_value": pairs / t_sync},
+                "blocking_model_call_value": pairs / t_sync,
+                "uint8_frames_input": None if t_u8 is None else {
+                    "value": pairs / t_u8, "unit": "pairs/s", "h2d_bytes_per_step": 6 * B * H * W * world,
+                    "api": "FlowPipeline(input='u8'): uint8 BGR frame pairs in, pre-processing kernel + forward on the GPU"}},
         "gpu_launches": launches_per_step * args.steps * world,
         "roofline": roof, "roofline_corr": roof_corr, "roofline_corr_fp32": roof_corr_f32,
         "step_tflops": step_tflops,

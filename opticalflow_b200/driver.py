@@ -70,6 +70,31 @@ def sum_over_ranks(values, device=None):
 # ------------------------------------------------------------------------------------------------------------------
 # Copy/compute pipeline on one GPU
 # ------------------------------------------------------------------------------------------------------------------
+def bind_host_to_gpu(device_index):
+    """Pin this process (and so its first-touch pinned allocations) to the CPU cores NVML reports as nearest to GPU
+    `device_index` (a torch device index: CUDA_VISIBLE_DEVICES is honoured through the device UUID).  With 8 ranks each
+    uploading 11 MB per pair, host buffers on the wrong socket halve the aggregate H2D rate.  Returns the core list, or
+    None when NVML / the affinity call is unavailable or the intersection with the allowed cores is empty (no change)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        props = torch.cuda.get_device_properties(device_index)
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(props.uuid)).encode())
+        except Exception:  # noqa: BLE001
+            h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        near = {64 * i + b for i, w in enumerate(mask) for b in range(64) if (int(w) >> b) & 1}
+        allowed = os.sched_getaffinity(0) & near
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return sorted(allowed)
+    except Exception:  # noqa: BLE001
+        return None
+
+
 class FlowPipeline:
     """Streams host batches [B,6,H,W] fp32 (pinned) through `model` with H2D, compute and D2H on three streams.
 
@@ -81,15 +106,31 @@ class FlowPipeline:
     so the 22 MB/pair input upload of batch i+1 overlaps the forward of batch i.
     """
 
-    def __init__(self, model, B, H, W, device, depth=2):
+    def __init__(self, model, B, H, W, device, depth=2, input="f32", swap_rb=True):
+        """input='f32': host batches are the model's own input, [B,6,H,W] fp32 (H, W multiples of 64).
+        input='u8' : host batches are the frames as the reference drivers hold them before frame_to_tensor /
+        pad_to_multiple_of_64 (pwc_extract_flow_video.py:27-42, inference_kitti.py:53-63): uint8 [B,2,H,W,3] (frame 1,
+        frame 2; BGR if swap_rb); /255, channel swap, replicate pad and cat run as ONE kernel on the GPU
+        (prepost.frames_to_input), so a pair costs 6*H*W bytes of upload instead of 24*Hp*Wp.  Flows come back at a
+        quarter of the PADDED size, like the reference model's output before unpad."""
         if device.type != "cuda":
             raise RuntimeError("FlowPipeline: CUDA device required -- this build has no CPU fallback")
-        self.model, self.B, self.H, self.W, self.device, self.depth = model, B, H, W, device, depth
+        if input not in ("f32", "u8"):
+            raise ValueError("FlowPipeline: input must be 'f32' or 'u8'")
+        self.model, self.B, self.device, self.depth = model, B, device, depth
+        self.input, self.swap_rb, self.in_h, self.in_w = input, bool(swap_rb), H, W
+        if input == "u8":
+            from . import prepost
+            ph, pw = prepost.pad_amounts(H, W)
+            H, W = H + ph, W + pw
+        self.H, self.W = H, W
         with torch.cuda.device(device):
             self.plan = model._plan(B, H, W, device)
             self.plan.pack_weights(model)
             self.s_in, self.s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
             self.x_dev = [torch.empty(B, 6, H, W, device=device) for _ in range(depth)]
+            self.u8_dev = [torch.empty(B, 2, self.in_h, self.in_w, 3, device=device, dtype=torch.uint8) for _ in range(depth)] \
+                if input == "u8" else None
             self.o_dev = [torch.empty(B, 2, H // 4, W // 4, device=device) for _ in range(depth)]
             self.o_host = [torch.empty(B, 2, H // 4, W // 4).pin_memory() for _ in range(depth)]
             ev = lambda: [torch.cuda.Event() for _ in range(depth)]  # noqa: E731
@@ -110,7 +151,8 @@ class FlowPipeline:
         with torch.cuda.device(self.device):
             for i, xh in enumerate(host_batches):
                 s = i % self.depth
-                if xh.shape != self.x_dev[s].shape or xh.dtype != torch.float32:
+                slot = self.u8_dev[s] if self.input == "u8" else self.x_dev[s]
+                if xh.shape != slot.shape or xh.dtype != slot.dtype:
                     raise RuntimeError(f"FlowPipeline: batch {i} has shape {tuple(xh.shape)} / {xh.dtype}")
                 if len(pending) == self.depth:           # slot s is about to be reused: hand its flow to the sink
                     j, sj = pending.pop(0)
@@ -119,10 +161,15 @@ class FlowPipeline:
                         sink(j, self.o_host[sj])
                 with torch.cuda.stream(self.s_in):
                     self.s_in.wait_event(self.in_free[s])
-                    self.x_dev[s].copy_(xh, non_blocking=True)
+                    slot.copy_(xh, non_blocking=True)
                     self.in_ready[s].record(self.s_in)
                 cs.wait_event(self.in_ready[s])
-                if hasattr(self.plan, "run_from"):       # bf16 plan: conv1a reads the slot in place, the rest is one graph
+                if self.input == "u8":                   # /255 + swap + pad + cat into the fp32 slot; the u8 slot is free again
+                    from . import prepost
+                    prepost.frames_to_input(self.u8_dev[s][:, 0], self.u8_dev[s][:, 1], swap_rb=self.swap_rb, out=self.x_dev[s])
+                    self.in_free[s].record(cs)
+                    flow2 = self.plan.run_from(self.x_dev[s]) if hasattr(self.plan, "run_from") else self.plan.run(self.x_dev[s])
+                elif hasattr(self.plan, "run_from"):       # bf16 plan: conv1a reads the slot in place, the rest is one graph
                     flow2 = self.plan.run_from(self.x_dev[s], release=self.in_free[s])
                 elif hasattr(self.plan, "x_static"):     # graph plan: release the slot right after the d2d copy
                     self.plan.x_static.copy_(self.x_dev[s], non_blocking=True)

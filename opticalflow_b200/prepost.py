@@ -35,8 +35,11 @@ def frames_to_input(frames1, frames2, swap_rb=True, multiple=64, out=None):
         frames1, frames2 = frames1[None], frames2[None]
     if frames1.dtype != torch.uint8 or frames1.shape != frames2.shape or frames1.shape[-1] != 3:
         raise RuntimeError("frames_to_input: two uint8 [B,H,W,3] tensors of the same shape expected")
-    frames1, frames2 = frames1.contiguous(), frames2.contiguous()
     B, H, W, _ = frames1.shape
+    dense = lambda t: t.stride()[1:] == (W * 3, 3, 1) and t.stride(0) >= H * W * 3      # noqa: E731  (batch stride is free)
+    if not (dense(frames1) and dense(frames2) and frames1.stride(0) == frames2.stride(0)):
+        frames1, frames2 = frames1.contiguous(), frames2.contiguous()
+    img_stride = frames1.stride(0) if B > 1 else H * W * 3
     ph, pw = pad_amounts(H, W, multiple)
     Hp, Wp = H + ph, W + pw
     if Wp % 4:
@@ -44,7 +47,7 @@ def frames_to_input(frames1, frames2, swap_rb=True, multiple=64, out=None):
     if out is None:
         out = torch.empty(B, 6, Hp, Wp, device=frames1.device, dtype=torch.float32)
     lib = _lib.load()
-    e = lib.pwc_preprocess_u8_fwd(_lib.ptr(frames1), _lib.ptr(frames2), H * W * 3, W * 3, B, H, W, Hp, Wp,
+    e = lib.pwc_preprocess_u8_fwd(_lib.ptr(frames1), _lib.ptr(frames2), img_stride, W * 3, B, H, W, Hp, Wp,
                                   int(bool(swap_rb)), _lib.ptr(out), _lib.stream_handle())
     _lib.check(e, "pwc_preprocess_u8_fwd")
     return out, ph, pw

@@ -117,3 +117,29 @@ def test_run_from_reads_the_callers_tensor_in_place():
         assert torch.equal(got, want)
     with pytest.raises(RuntimeError):
         plan.run_from(x[:, :, :, ::2])
+
+
+@pytest.mark.parametrize("hw", [(128, 192), (100, 150)])
+def test_pipeline_uint8_input_matches_reference_preprocessing(hw):
+    """FlowPipeline(input='u8'): uint8 BGR frame pairs in, the flow of model(cat(frame_to_tensor + pad)) out -- the
+    pre-processing of pwc_extract_flow_video.py:27-42,197-205 restated by oracle/prepost_oracle.py."""
+    from opticalflow_b200 import driver
+    from opticalflow_b200.models.PWCNet import PWCDCNet
+    from oracle import prepost_oracle as PO
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(3)
+    m = PWCDCNet(conv_mode="bf16").eval().to(dev)
+    B, (H, W) = 2, hw
+    g = torch.Generator().manual_seed(8)
+    batches = [torch.randint(0, 256, (B, 2, H, W, 3), dtype=torch.uint8, generator=g).pin_memory() for _ in range(4)]
+    want = []
+    for xb in batches:
+        xs = [PO.frames_to_input(xb[k, 0].numpy(), xb[k, 1].numpy())[0] for k in range(B)]
+        want.append(m(torch.cat(xs, 0).to(dev)).cpu())
+    got = {}
+    pipe = driver.FlowPipeline(m, B, H, W, dev, input="u8")
+    assert pipe.run(iter(batches), sink=lambda i, f: got.__setitem__(i, f.clone())) == 4
+    for i in range(4):
+        assert got[i].shape == want[i].shape and torch.equal(got[i], want[i]), f"batch {i} differs"
+    with pytest.raises(RuntimeError):
+        pipe.run(iter([batches[0].float()]))
