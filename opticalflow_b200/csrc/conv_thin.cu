@@ -16,6 +16,7 @@
 //     straight into the concat slice (or the second tensor for the im2 half of the batch).
 #include "common.cuh"
 #include "ptx_sm100.cuh"
+#include "tmap.cuh"
 #include "../../include/pwc_b200.h"
 
 namespace pwc {
@@ -386,6 +387,149 @@ __global__ void __launch_bounds__(256, 3) conv_c16_kernel(const ThinConvParams p
   }
 }
 
+// ---- the same layer with the patch brought in by TMA (one box per tile, SWIZZLE_32B = the XOR pattern above, OOB zero fill
+// = padding) into two buffers: the next tile loads while this one computes, and the 1320 cp.async + address arithmetic per
+// tile disappear from the LSU / issue slots.  Patch rows are 72 pixels apart (2304 B: keeps the swizzle phase of a pixel
+// independent of its row, so tap offsets stay immediates).
+constexpr int kC16TPW = 72, kC16TPatch = kC16IH * kC16TPW * 32;
+
+template <int MT, int KY>
+__device__ __forceinline__ void c16t_taps(const uint32_t (&ab)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
+#pragma unroll
+  for (int kx = 0; kx < 3; ++kx) {
+    uint32_t a0[4], a1[4];
+    c16_ldsm4<(KY * kC16TPW + 16 * MT) * 32>(a0, ab[kx]);
+    c16_ldsm4<(KY * kC16TPW + 16 * MT + 16) * 32>(a1, ab[kx]);
+    thin_mma(acc[0][0], a0, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    thin_mma(acc[0][1], a0, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+    thin_mma(acc[1][0], a1, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    thin_mma(acc[1][1], a1, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+  }
+}
+template <int MT>
+__device__ __forceinline__ void c16t_tile(const uint32_t (&ab)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
+  c16t_taps<MT, 0>(ab, bw, acc);
+  c16t_taps<MT, 1>(ab, bw, acc);
+  c16t_taps<MT, 2>(ab, bw, acc);
+}
+
+__global__ void __launch_bounds__(256, 3)
+conv_c16_tma_kernel(const __grid_constant__ CUtensorMap tm1, const __grid_constant__ CUtensorMap tm2, const ThinConvParams p,
+                    int n_tiles) {
+  __shared__ __align__(1024) unsigned char patch[2 * kC16TPatch];
+  __shared__ __align__(8) unsigned long long bars[2];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, c = lane & 3;
+  const uint32_t p_addr = (uint32_t)__cvta_generic_to_shared(patch);
+  const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(bars);
+  if (tid == 0) {
+    ptx::prefetch_tmap(&tm1);
+    ptx::mbar_init(bar0, 1); ptx::mbar_init(bar0 + 8, 1);
+    ptx::fence_barrier_init();
+  }
+  uint32_t bw[9][2][2];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const uint32_t* wr = reinterpret_cast<const uint32_t*>(p.w + (t * 16 + 8 * j + g) * 16);
+      bw[t][j][0] = __ldg(wr + c); bw[t][j][1] = __ldg(wr + 4 + c);
+    }
+  float bia[2][2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) { bia[j][0] = p.bias[8 * j + 2 * c]; bia[j][1] = p.bias[8 * j + 2 * c + 1]; }
+  uint32_t abase[3];
+  {
+    const int px = (lane & 7) + 8 * ((lane >> 3) & 1), half = lane >> 4;
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const int q = px + kx;
+      abase[kx] = p_addr + (uint32_t)((warp * kC16TPW + q) * 32 + 16 * (half ^ ((q >> 2) & 1)));
+    }
+  }
+  __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int H = p.H, W = p.W;
+  const float inv_tx = 1.0f / (float)p.tiles_x, inv_ty = 1.0f / (float)p.tiles_y;
+  auto decode = [&](int tile, int& ox0, int& oy0, int& img) {
+    const int t2 = (int)(((float)tile + 0.5f) * inv_tx); const int tx = tile - t2 * p.tiles_x;
+    img = (int)(((float)t2 + 0.5f) * inv_ty); const int ty = t2 - img * p.tiles_y;
+    ox0 = tx * 64; oy0 = ty * 8;
+  };
+  auto issue = [&](int tile, int buf) {                        // one thread
+    int ox0, oy0, img;
+    decode(tile, ox0, oy0, img);
+    const bool sec = p.in2 != nullptr && img >= p.n_split_in;
+    ptx::mbar_expect_tx(bar0 + 8u * buf, (uint32_t)kC16TPatch);
+    ptx::tma_load_4d(p_addr + (uint32_t)buf * kC16TPatch, sec ? &tm2 : &tm1, bar0 + 8u * buf, 0, ox0 - 1, oy0 - 1,
+                     sec ? img - p.n_split_in : img);
+  };
+  int tile = blockIdx.x;
+  if (tid == 0 && tile < n_tiles) issue(tile, 0);
+  uint32_t ph0 = 0, ph1 = 0;
+  for (int it = 0; tile < n_tiles; tile += gridDim.x, ++it) {
+    const int b = it & 1;
+    if (tid == 0 && tile + (int)gridDim.x < n_tiles) issue(tile + gridDim.x, b ^ 1);   // that buffer was released by the last sync
+    if (b == 0) { ptx::mbar_wait(bar0, ph0); ph0 ^= 1; } else { ptx::mbar_wait(bar0 + 8, ph1); ph1 ^= 1; }
+    int ox0, oy0, img;
+    decode(tile, ox0, oy0, img);
+    const uint32_t boff = (uint32_t)b * kC16TPatch;
+    const uint32_t ab[3] = {abase[0] + boff, abase[1] + boff, abase[2] + boff};
+    const int oy = oy0 + warp;
+    if (oy < H) {
+      const bool second = p.out2 != nullptr && img >= p.n_split;
+      __nv_bfloat16* orow = second ? p.out2 + (((long)(img - p.n_split) * H + oy) * W + ox0 + g) * p.out2_pitch + p.out2_coff + 2 * c
+                                   : p.out + (((long)img * H + oy) * W + ox0 + g) * p.out_pitch + p.out_coff + 2 * c;
+      const long opitch = second ? p.out2_pitch : p.out_pitch;
+#pragma unroll
+      for (int mp = 0; mp < 2; ++mp) {
+        if (ox0 + 32 * mp >= W) break;
+        float acc[2][2][4];
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
+        if (mp == 0) c16t_tile<0>(ab, bw, acc);
+        else c16t_tile<2>(ab, bw, acc);
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              if (ox0 + 32 * mp + 16 * m + g + 8 * h < W) {
+                const float v0 = acc[m][j][2 * h] + bia[j][0], v1 = acc[m][j][2 * h + 1] + bia[j][1];
+                *reinterpret_cast<__nv_bfloat162*>(orow + (32 * mp + 16 * m + 8 * h) * opitch + 8 * j) =
+                    __floats2bfloat162_rn(lrelu(v0, p.slope), lrelu(v1, p.slope));
+              }
+      }
+    }
+    __syncthreads();                                            // buffer b may be refilled
+  }
+}
+
+static int launch_c16_tma(ThinConvParams& p, cudaStream_t s) {
+  p.tiles_x = cdiv(p.W, 64); p.tiles_y = cdiv(p.H, 8);
+  const long nt = (long)p.N * p.tiles_x * p.tiles_y;
+  const int n1 = p.in2 ? p.n_split_in : p.N;
+  CUtensorMap tm1, tm2;
+  int e = make_tmap_nhwc(&tm1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p.in + p.in_coff, p.in_pitch, 16, p.W, p.H, n1 > 0 ? n1 : 1, 16,
+                         kC16TPW, kC16IH, 1, 1, CU_TENSOR_MAP_SWIZZLE_32B);
+  if (e) return e;
+  tm2 = tm1;
+  if (p.in2 && p.N > p.n_split_in) {
+    e = make_tmap_nhwc(&tm2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p.in2 + p.in2_coff, p.in2_pitch, 16, p.W, p.H, p.N - p.n_split_in,
+                       16, kC16TPW, kC16IH, 1, 1, CU_TENSOR_MAP_SWIZZLE_32B);
+    if (e) return e;
+  }
+  static const int ctas = []() { const char* e = getenv("PWC_THIN_C16_CTAS"); return e ? atoi(e) : 148 * 3; }();
+  return (int)launch_pdl(conv_c16_tma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, tm1, tm2, p, (int)nt);
+}
+
 static int launch_c16(ThinConvParams& p, cudaStream_t s) {
   p.tiles_x = cdiv(p.W, 64); p.tiles_y = cdiv(p.H, 8);
   const long nt = (long)p.N * p.tiles_x * p.tiles_y;
@@ -456,6 +600,9 @@ extern "C" int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
   const long max_pitch = in_pitch > in2_pitch ? in_pitch : in2_pitch;
   if (use_c16 && cin == 16 && cout == 16 && stride == 1 && (long)N * cdiv(H, 8) * cdiv(W, 64) < (1L << 20) &&
       (long)H * W * max_pitch < 0x7fffffffL)
-    return launch_c16(p, (cudaStream_t)stream);
+  {
+    static const int use_tma = []() { const char* e = getenv("PWC_THIN_C16_TMA"); return e ? atoi(e) : 1; }();
+    return use_tma ? launch_c16_tma(p, (cudaStream_t)stream) : launch_c16(p, (cudaStream_t)stream);
+  }
   return thin_dispatch(p, cout / 8, cin / 16, (cudaStream_t)stream);
 }

@@ -85,7 +85,8 @@ def test_conv1a_bf16_matches_torch(shape):
 def test_conv1a_split_keeps_fp32_grade_inputs():
     """The tensor-core conv1a splits x and w into bf16 hi + lo parts (3 products, lo*lo dropped: ~2^-16 relative error
     against 2^-9 for a plain bf16 cast): its bf16 output must be the correctly rounded fp64 result in >= 99% of the elements
-    (measured 99.4%: the rest sit within 2^-16 of a rounding boundary) and never more than one bf16 ulp away."""
+    (measured 99.4%: the rest sit within 2^-16 of a rounding boundary) and never more than one bf16 ulp (+ 2^-15 of the
+    sum of |x*w|, for results that cancel to nearly zero) away."""
     from opticalflow_b200 import ops
     g = torch.Generator().manual_seed(6)
     x = torch.rand(2, 6, 96, 256, generator=g)
@@ -97,9 +98,12 @@ def test_conv1a_split_keeps_fp32_grade_inputs():
                        F.leaky_relu(F.conv2d(x[:, 3:].double(), w.double(), b.double(), stride=2, padding=1), 0.1)], 0)
     want = ref64.float().bfloat16()
     exact = (out == want).float().mean().item()
-    ulp = torch.maximum(want.float().abs(), torch.tensor(2.0 ** -126)) * 2.0 ** -7      # >= 1 bf16 ulp of the value
     assert exact >= 0.99, exact
-    assert ((out.float() - want.float()).abs() <= ulp).all()
+    # never more than one bf16 ulp of the value plus the split's own error, 2^-16 of the sum of |x*w| (which matters only
+    # where the 27 products cancel to a result near zero)
+    mag = torch.cat([F.conv2d(x[:, :3], w.abs(), None, stride=2, padding=1), F.conv2d(x[:, 3:], w.abs(), None, stride=2, padding=1)], 0)
+    tol = want.float().abs() * 2.0 ** -7 + mag * 2.0 ** -15
+    assert ((out.float() - want.float()).abs() <= tol).all()
     cast = torch.cat([F.leaky_relu(F.conv2d(x[:, :3].bfloat16().float(), w.bfloat16().float(), b, stride=2, padding=1), 0.1),
                       F.leaky_relu(F.conv2d(x[:, 3:].bfloat16().float(), w.bfloat16().float(), b, stride=2, padding=1), 0.1)], 0)
     assert (cast.bfloat16() == want).float().mean().item() < exact - 0.1            # what the split buys
