@@ -5,6 +5,8 @@
 //   * the 2-channel transposed convolution deconv() (PWCNet.py:35-36; call sites 208-209,222-223,236-237,252-253)
 //     with fp32 or bf16 input and output.
 #include "common.cuh"
+#include "ptx_sm100.cuh"
+#include "tmap.cuh"
 #include "../../include/pwc_b200.h"
 
 namespace pwc {
@@ -95,6 +97,7 @@ __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __rest
 // CTA = 8 output rows x 64 pixels; the fp32 input patch (3 x 17 x 132) is staged with aligned 16-byte cp.async (zero fill
 // = padding); each thread gathers its A-fragment elements from it with precomputed tap offsets (im2col in registers).
 constexpr int kC1M_PW = 132, kC1M_IH = 17;
+constexpr uint32_t kC1M_BUF = (3 * kC1M_IH * kC1M_PW * 4 + 127) / 128 * 128;   // TMA variant: patch buffer stride
 __device__ __forceinline__ void c1m_split(float v, float w, uint32_t& hi, uint32_t& lo) {
   const __nv_bfloat162 h = __floats2bfloat162_rn(v, w);
   const float2 hf = __bfloat1622float2(h);
@@ -253,6 +256,113 @@ __global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict
   }
 }
 
+// The same kernel with the patch brought in by TMA: ONE 3-D box (132 floats x 17 rows x 3 planes, OOB zero fill = padding)
+// per tile into one of two buffers, so the next tile loads while this one computes and no thread spends issue slots on staging.
+__global__ void __launch_bounds__(256) conv1a_mma_tma_kernel(const __grid_constant__ CUtensorMap tmx, const float* __restrict__ w,
+                                                         const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                                                         int B, int H, int W, float slope, int frames, int tiles_x, int tiles_y,
+                                                         int n_tiles) {
+  extern __shared__ __align__(128) unsigned char c1m_smem[];   // two patch buffers of kC1M_BUF bytes | two mbarriers
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, c = lane & 3;
+  const uint32_t p_addr = (uint32_t)__cvta_generic_to_shared(c1m_smem);
+  const uint32_t bar0 = p_addr + 2u * kC1M_BUF;
+  if (tid == 0) {
+    ptx::prefetch_tmap(&tmx);
+    ptx::mbar_init(bar0, 1); ptx::mbar_init(bar0 + 8, 1);
+    ptx::fence_barrier_init();
+  }
+  // ---- weights (independent of the previous kernel): B fragments of both n-tiles and k-steps, split hi / lo
+  uint32_t bh[2][2][2], bl[2][2][2];                           // [k step][n-tile][k half]
+  uint32_t pa[2][4];                                            // smem address of this thread's 8 k indices, pixel g of m-tile 0
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      int k = 16 * s + 2 * c + (q & 1) + 8 * (q >> 1);
+      k = k < 27 ? k : 26;                                      // K padding: its weights are 0, any tap of the window will do
+      const int ci = k / 9, ky = (k - 9 * ci) / 3, kx = k - 9 * ci - 3 * ky;
+      // input row 2*oy - 1 + ky -> patch row 2*warp + ky; input column 2*x - 1 + kx -> patch column 2*x + 3 + kx
+      pa[s][q] = p_addr + 4u * (uint32_t)((ci * kC1M_IH + ky + 2 * warp) * kC1M_PW + kx + 3 + 2 * g);
+    }
+#pragma unroll
+  for (int s = 0; s < 2; ++s)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int k = 16 * s + 2 * c + 8 * h, co = 8 * j + g;
+        const float w0 = k < 27 ? w[co * 27 + k] : 0.f, w1 = k + 1 < 27 ? w[co * 27 + k + 1] : 0.f;
+        c1m_split(w0, w1, bh[s][j][h], bl[s][j][h]);
+      }
+  float bia[2][2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) { bia[j][0] = bias[8 * j + 2 * c]; bia[j][1] = bias[8 * j + 2 * c + 1]; }
+  __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int Ho = H >> 1, Wo = W >> 1;
+  const float inv_tx = 1.0f / (float)tiles_x, inv_ty = 1.0f / (float)tiles_y;
+  auto decode = [&](int tile, int& ox0, int& oy0, int& img) {
+    // tile -> (tx, ty, img) without integer divisions (exact below 2^20 tiles, checked by the launcher)
+    const int t2 = (int)(((float)tile + 0.5f) * inv_tx); const int tx = tile - t2 * tiles_x;
+    img = (int)(((float)t2 + 0.5f) * inv_ty); const int ty = t2 - img * tiles_y;
+    ox0 = tx * 64; oy0 = ty * 8;
+  };
+  auto issue = [&](int tile, int buf) {                        // one thread
+    int ox0, oy0, img;
+    decode(tile, ox0, oy0, img);
+    const int plane0 = frames ? img * 3 : (img % B) * 6 + (img / B) * 3;
+    ptx::mbar_expect_tx(bar0 + 8u * buf, (uint32_t)(3 * kC1M_IH * kC1M_PW * 4));
+    ptx::tma_load_3d(p_addr + (uint32_t)buf * kC1M_BUF, &tmx, bar0 + 8u * buf, 2 * ox0 - 4, 2 * oy0 - 1, plane0);
+  };
+  int tile = blockIdx.x;
+  if (tid == 0 && tile < n_tiles) issue(tile, 0);
+  uint32_t ph0 = 0, ph1 = 0, pdelta = kC1M_BUF;
+  for (int it = 0; tile < n_tiles; tile += gridDim.x, ++it) {
+    const int b = it & 1;
+    if (tid == 0 && tile + (int)gridDim.x < n_tiles) issue(tile + gridDim.x, b ^ 1);   // released by the sync that ended the last tile
+    if (b == 0) { ptx::mbar_wait(bar0, ph0); ph0 ^= 1; } else { ptx::mbar_wait(bar0 + 8, ph1); ph1 ^= 1; }
+    int ox0, oy0, img;
+    decode(tile, ox0, oy0, img);
+
+    const int oy = oy0 + warp;
+    if (oy < Ho) {
+      __nv_bfloat16* orow = out + (((long)img * Ho + oy) * Wo + ox0 + g) * 16 + 2 * c;
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt) {
+        if (ox0 + 16 * mt >= Wo) break;
+        float acc[2][4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[j][e] = 0.f;
+        if (mt == 0) c1m_tile<0>(pa, bh, bl, acc);
+        else if (mt == 1) c1m_tile<1>(pa, bh, bl, acc);
+        else if (mt == 2) c1m_tile<2>(pa, bh, bl, acc);
+        else c1m_tile<3>(pa, bh, bl, acc);
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            if (ox0 + 16 * mt + g + 8 * h < Wo) {
+              const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
+              *reinterpret_cast<__nv_bfloat162*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) =
+                  __floats2bfloat162_rn(lrelu(v0, slope), lrelu(v1, slope));
+            }
+      }
+    }
+    __syncthreads();                                            // this buffer may be refilled
+#pragma unroll
+    for (int s = 0; s < 2; ++s)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) pa[s][q] += pdelta;
+    pdelta = 0u - pdelta;
+  }
+}
+
+
 static int launch_conv1a(const float* x, const float* w, const float* bias, void* out, int B, int H, int W, float slope,
                          int frames, cudaStream_t s) {
   static const int use_mma = []() { const char* e = getenv("PWC_CONV1A_MMA"); return e ? atoi(e) : 1; }();
@@ -261,6 +371,23 @@ static int launch_conv1a(const float* x, const float* w, const float* bias, void
     const long nt = (long)(frames ? B : 2 * B) * tiles_x * tiles_y;
     if (nt < (1L << 20) && 3L * H * W < 0x7fffffffL) {
       static const int ctas = []() { const char* e = getenv("PWC_CONV1A_CTAS"); return e ? atoi(e) : 148 * 4; }();
+      static const int use_tma = []() { const char* e = getenv("PWC_CONV1A_TMA"); return e ? atoi(e) : 1; }();
+      EncodeTiledFn enc = use_tma ? get_encode_tiled() : nullptr;
+      if (enc) {
+        const size_t smem = 2 * kC1M_BUF + 16;
+        static const cudaError_t attr = cudaFuncSetAttribute(conv1a_mma_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                             (int)(2 * kC1M_BUF + 16));
+        if (attr != cudaSuccess) return (int)attr;
+        CUtensorMap tm;
+        cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)(frames ? 3 * B : 6 * B)};
+        cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)W * H * 4};
+        cuuint32_t box[3] = {(cuuint32_t)kC1M_PW, (cuuint32_t)kC1M_IH, 3}, es[3] = {1, 1, 1};
+        if (enc(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(x), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+          return (int)cudaErrorInvalidValue;
+        return (int)launch_pdl(conv1a_mma_tma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), smem, s, tm, w, bias,
+                               reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt);
+      }
       return (int)launch_pdl(conv1a_mma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, x, w, bias,
                              reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt);
     }
