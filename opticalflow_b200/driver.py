@@ -206,6 +206,8 @@ def run_sharded(model, n_pairs, load_batch, sink, B, H, W, device, rank=None, wo
     todo = batches(lo, hi, B)
     if not todo:
         return 0
+    if world > 1:
+        bind_host_to_gpu(device.index if device.index is not None else torch.cuda.current_device())
     pipe = FlowPipeline(model, B, H, W, device)
     pipe.run((load_batch(s, c) for s, c in todo),
              sink=lambda i, f: sink(todo[i][0], todo[i][1], f[:todo[i][1]]))

@@ -117,3 +117,15 @@ def test_two_ranks_gloo_cover_all_pairs_once(n_pairs, batch):
     assert sorted(flat) == list(range(n_pairs)) and len(set(flat)) == n_pairs
     assert t_max == [2.0, 10.0]                              # max over ranks, as bench.py times a step
     assert n_sum == [float(n_pairs)]
+
+
+def test_bind_host_to_gpu_is_harmless_without_a_gpu():
+    """No NVML / no CUDA device: the NUMA binding helper reports None and leaves the affinity mask alone."""
+    import os
+    from opticalflow_b200 import driver
+    before = os.sched_getaffinity(0)
+    try:
+        cpus = driver.bind_host_to_gpu(0)
+        assert cpus is None or (isinstance(cpus, list) and set(cpus) <= before)
+    finally:
+        os.sched_setaffinity(0, before)
