@@ -181,6 +181,23 @@ int pwc_tc_conv_set_skip(pwc_tc_conv* handle, const unsigned long long* masks);
 int pwc_tc_conv_set_kk_skip(pwc_tc_conv* handle, const int* masks);
 int pwc_tc_conv_set_out_groups(pwc_tc_conv* handle, int g, long group_pitch);
 void pwc_tc_conv_destroy(pwc_tc_conv* handle);
+/* Split-K launch of a created handle that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  The split-K form of the tcgen05 kernel (`ksplit` CTAs share one pixel tile, each a range of
+ * 64-channel chunks; fp32 partial sums + per-tile arrival counters in scratch memory) normally gets its scratch from
+ * cudaMalloc inside pwc_tc_conv_create (opt-in, PWC_TC_WM_KSPLIT=1).  This entry point runs the same kernel on ANY
+ * eligible handle with the scratch in a file-scope `static __device__` array of 16 MiB (held by every GPU that loads the
+ * library until exit; device address from cudaGetSymbolAddress, once per device).  Inputs, weights and outputs are the
+ * ones the handle was created with; the handle is not modified.
+ *   ksplit : CTAs per pixel tile, 2..8 (clamped to the chunk count); 0 = as many as fill the SMs.
+ *   eligible: stride 1, coutp <= 128 and % 32 == 0, bf16 output (out_f32 == 0), >= 2 channel chunks, no tap stacking.
+ *   errors : cudaErrorInvalidValue (and a message on stderr) for an ineligible handle or when
+ *            tiles * tile_pixels * 128 * 4 + tiles * 4 bytes exceed the 16 MiB array.
+ *   Calls no cudaMalloc / cudaFree / allocating library routine; enqueues one cudaMemsetAsync of the used prefix of the
+ *   array (sums and counters start at zero) and one kernel on `stream`.  Every call on a GPU shares the array: calls
+ *   that overlap on that GPU (different streams, no ordering) race.  The atomic summation order varies, so results may
+ *   differ from pwc_tc_conv_launch in the last bit of the bf16 output. */
+int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* handle, int ksplit, void* stream);
 /* debug aid: timeline of CTA 0 of the halo kernel (enabled by env PWC_TC_HALO_BO bit 16); host memory destination */
 int pwc_debug_halo_trace(unsigned long long* host_dst, int count);
 int pwc_debug_corr_trace(unsigned long long* host_dst, int count);

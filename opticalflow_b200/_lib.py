@@ -31,6 +31,7 @@ SIGNATURES = {
     "pwc_tc_conv_create": (_i, [ctypes.POINTER(_vp), _vp, _l, _i, _vp, _l, _i, _i, _i, _i, _vp, _vp, _i, _i,
                                 _vp, _l, _i, _vp, _l, _i, _i, _vp, _l, _i, _i, _i, _i, _i, _f]),
     "pwc_tc_conv_launch": (_i, [_vp, _vp]),
+    "pwc_tc_conv_launch_static_splitk": (_i, [_vp, _i, _vp]),
     "pwc_tc_conv_set_skip": (_i, [_vp, _vp]),
     "pwc_tc_conv_set_kk_skip": (_i, [_vp, _vp]),
     "pwc_tc_conv_set_out_groups": (_i, [_vp, _i, _l]),

@@ -19,7 +19,9 @@
 #include "conv_tc_wm.cuh"
 #include "../../include/pwc_b200.h"
 
+#include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <new>
 
 namespace pwc {
@@ -687,6 +689,77 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
 }
 
 extern "C" void pwc_tc_conv_destroy(pwc_tc_conv* h) { delete h; }
+
+// ------------------------------------------------------------------------------------------------------------------
+// Split-K launch that allocates nothing (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).  The fp32 partial-sum scratch and
+// the per-tile arrival counters of the split-K path live in ONE file-scope device array of kStaticScratchBytes; every
+// GPU that loads the library holds it until exit.  In host code `g_static_scratch` is only a stand-in for the symbol:
+// the device address comes from cudaGetSymbolAddress, once per device with that device current.
+// ------------------------------------------------------------------------------------------------------------------
+namespace pwc {
+constexpr size_t kStaticScratchBytes = 16u << 20;                   // 16 MiB per GPU
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+constexpr int kMaxDevices = 64;
+static void* g_static_scratch_ptr[kMaxDevices] = {};              // device address of the array, per device
+static std::mutex g_static_scratch_mu;
+}  // namespace pwc
+
+extern "C" int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* h, int ksplit, void* stream) {
+  using namespace pwc;
+  if (!h || h->halo != 2) return (int)cudaErrorInvalidValue;
+  WmParams p = h->wp;                                               // by-value copy: the handle itself is not modified
+  if (!p.wstore || p.ts || p.nchunk < 2 || ksplit < 0) {
+    fprintf(stderr, "pwc_tc_conv_launch_static_splitk: the layer has no split-K form (needs >= 2 channel chunks, "
+                    "16-bit per-warp output stores, no tap stacking)\n");
+    return (int)cudaErrorInvalidValue;
+  }
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return (int)cudaErrorInvalidDevice;
+  void* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+    if (!g_static_scratch_ptr[dev]) {
+      void* sym = nullptr;
+      e = cudaGetSymbolAddress(&sym, g_static_scratch);             // the array's address on the CURRENT device
+      if (e != cudaSuccess) return (int)e;
+      g_static_scratch_ptr[dev] = sym;
+    }
+    base = g_static_scratch_ptr[dev];
+  }
+  int nsm = 0;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+  if (nsm <= 0) nsm = 148;
+  int ks = ksplit ? ksplit : nsm / p.num_items;                     // 0 = as many CTAs per tile as fill the machine
+  if (ks > 8) ks = 8;
+  if (ks > p.nchunk) ks = p.nchunk;
+  if (ks < 2) ks = 2;
+  p.cps = cdiv(p.nchunk, ks);
+  p.ksplit = cdiv(p.nchunk, p.cps);
+  const size_t fl = (size_t)p.num_items * p.npx * 128;              // fp32 partial sums [item][pixel][128 channels]
+  const size_t bytes = fl * sizeof(float) + (size_t)p.num_items * sizeof(int);
+  if (bytes > kStaticScratchBytes) {
+    fprintf(stderr, "pwc_tc_conv_launch_static_splitk: layer needs %zu bytes of split-K scratch, the static array holds %zu\n",
+            bytes, kStaticScratchBytes);
+    return (int)cudaErrorInvalidValue;
+  }
+  p.scratch = reinterpret_cast<float*>(base);
+  p.counters = reinterpret_cast<int*>(p.scratch + fl);
+  const cudaStream_t st = (cudaStream_t)stream;
+  // every call shares the array, which keeps the last call's contents: sums and counters must start at zero
+  e = cudaMemsetAsync(base, 0, bytes, st);
+  if (e != cudaSuccess) return (int)e;
+  const int v = p.num_items * p.ksplit;
+  const int grid = v < nsm ? v : nsm;
+  cudaLaunchConfig_t cfg = {};                                      // plain stream order (no programmatic early launch)
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kHaloThreads); cfg.dynamicSmemBytes = h->smem_bytes; cfg.stream = st;
+  if (p.has_skip) e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<2>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
+  else if (p.has_kk) e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<3>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
+  else e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<0>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
+  return (int)(e != cudaSuccess ? e : cudaGetLastError());
+}
 
 extern "C" int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, const int* chan_map,
                                          int Cout, int Cin, int cin_span, int kc, int coutp, void* stream) {
