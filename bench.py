@@ -64,59 +64,145 @@ class ClockSampler(threading.Thread):
                 if v.lower().startswith("active"):
                     reasons.add(nm)
         mx = max((int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()), default=None)
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
         return {"sm_mhz": (sm[len(sm) // 2] if sm else None), "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "power_w_max": (max(pw) if pw else None)}
+
+
+def _cpu_forward_fn(H, W):
+    """The reference's CPU forward on 1 pair: the UNMODIFIED models/PWCNet.py from oracle/_ref/refpkg (kind 'reference',
+    SURVEY App. D harness) when oracle/build_ref.sh has run, else the oracle port (kind 'port')."""
+    import torch
+    from oracle import pwcnet_oracle as O
+    x = O.synthetic_input(1, H, W, 1)
+    try:
+        from oracle import ref_runtime as R
+        if R.available():
+            m = R.reference_model(0)
+
+            def fwd():
+                with R.cpu_execution(), torch.no_grad():
+                    return m(x)
+            return fwd, "reference"
+    except Exception as e:  # noqa: BLE001
+        sys.stderr.write(f"bench: reference package unusable ({e}); timing the oracle port\n")
+    sd = O.reference_like_state_dict(0)
+    return (lambda: O.forward(sd, x)), "port"
 
 
 def cpu_reference_forward_timer(H, W, reps, threads=None):
-    """Times the reference's CPU forward (the oracle port: same torch CPU ops in the same order as PWCNet.py:180-273)
-    on a bounded sample: `reps` single 1-pair forwards at HxW after 1 warm-up.  Returns (pairs/s, cores, sample)."""
+    """Times the reference's CPU forward on a bounded sample: `reps` single 1-pair forwards at HxW after 2 warm-ups, with all
+    host threads, plus one 1-thread figure.  Returns (pairs/s, cores, sample, kind, pairs/s on 1 thread)."""
     import torch
-    from oracle import pwcnet_oracle as O
     cores = threads or os.cpu_count() or 1
+    fwd, kind = _cpu_forward_fn(H, W)
     torch.set_num_threads(cores)
-    sd = O.reference_like_state_dict(0)
-    x = O.synthetic_input(1, H, W, 1)
-    O.forward(sd, x)
+    fwd(); fwd()
     ts = []
     for _ in range(reps):
-        t0 = time.perf_counter(); O.forward(sd, x); ts.append(time.perf_counter() - t0)
+        t0 = time.perf_counter(); fwd(); ts.append(time.perf_counter() - t0)
     ts.sort()
     med = ts[len(ts) // 2]
-    return 1.0 / med, cores, f"{reps} forwards of 1 pair {W}x{H} fp32 (median), torch CPU {torch.__version__}, {cores} threads"
+    torch.set_num_threads(1)
+    t0 = time.perf_counter(); fwd(); t1 = time.perf_counter() - t0
+    torch.set_num_threads(cores)
+    return (1.0 / med, cores, f"{reps} forwards of 1 pair {W}x{H} fp32 (median, after 2 warm-ups), torch CPU {torch.__version__}, "
+            f"{cores} threads", kind, 1.0 / t1)
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path on the host cores.  The reference is a
-    Python/torch module that cannot be pip-installed or travel to the GPU box (no setup.py; needs a compiled
-    correlation_cuda), so the timed code is the oracle port (kind 'port')."""
+    """--impl reference: the reference's own CPU implementation of the path on the host cores -- the unmodified
+    models/PWCNet.py (oracle/_ref/refpkg, kind 'reference'; its correlation runs as the reference's torch shift-and-dot / C
+    because correlation_cuda is CUDA-only), else the oracle port.  Each step = 1 pair, a bounded sample of the batch-8 workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warm = max(args.steps, 1), max(args.warmup, 0)
     import torch
-    from oracle import pwcnet_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    sd = O.reference_like_state_dict(0)
-    x = O.synthetic_input(1, args.height, args.width, 1)    # each step = a bounded sample: 1 pair of the batch-8 workload
-    for _ in range(min(warm, 2)):
-        O.forward(sd, x)
-    steps = min(steps, 20)
+    fwd, kind = _cpu_forward_fn(args.height, args.width)
+    t0 = time.perf_counter(); fwd(); t_first = time.perf_counter() - t0
+    warm = max(args.warmup, 1)
+    budget = 150.0                                           # seconds for the whole run
+    steps = max(1, min(max(args.steps, 1), int((budget - warm * t_first) / max(t_first, 1e-3))))
+    for _ in range(warm - 1):
+        fwd()
     t0 = time.perf_counter()
     for _ in range(steps):
-        O.forward(sd, x)
+        fwd()
     dt = time.perf_counter() - t0
     v = steps / dt
     line = {"impl": "reference", "metric": "pwcnet_frame_pairs_per_s", "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
-            "steps": steps, "warmup": min(warm, 2), "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
+            "steps": steps, "warmup": warm, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"PWCDCNet forward {args.width}x{args.height}, random-init weights, 1 pair per step "
                                    f"(bounded sample of the batch-{args.batch} workload)"},
-            "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
-                             "sample": f"{steps} x 1 pair {args.width}x{args.height} fp32, torch CPU, {cores} threads"},
+            "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": kind,
+                             "sample": f"{steps} x 1 pair {args.width}x{args.height} fp32, torch CPU {torch.__version__}, {cores} threads"},
             "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def gpu_reference_baseline(dev, B, H, W, steps=5):
+    """The reference itself on the same B200 (SURVEY 8d 'GPU baselines'): unmodified models/PWCNet.py in eager fp32 with its
+    own correlation_cuda (oracle/_ref, compiled for sm_100a), and its warp + correlation + LeakyReLU per pyramid level.
+    CUDA-event timed.  Returns a dict or {'unavailable': why}."""
+    import torch
+    import torch.nn.functional as F
+    try:
+        from oracle import ref_runtime as R
+        from oracle import pwcnet_oracle as O
+        if not R.cuda_ext_available():
+            return {"unavailable": "oracle/_ref not built (oracle/build_ref.sh runs in the build container)"}
+        out = {}
+        m = R.reference_model(0, dev)
+        x = O.synthetic_input(B, H, W, 1).to(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for name, tf32, bench in (("eager_fp32", False, False), ("eager_tf32_cudnn_benchmark", True, True)):
+            torch.backends.cudnn.allow_tf32 = tf32
+            torch.backends.cudnn.benchmark = bench
+            with torch.no_grad():
+                for _ in range(3):
+                    m(x)
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(steps):
+                    m(x)
+                e1.record(); e1.synchronize()
+            out[name] = {"value": B * steps / (e0.elapsed_time(e1) * 1e-3), "unit": "pairs/s", "ms_per_step": e0.elapsed_time(e1) / steps}
+        torch.backends.cudnn.allow_tf32 = True
+        torch.backends.cudnn.benchmark = False
+        _, corr_mod, _ = R.load()
+        corr = corr_mod.Correlation(pad_size=4, kernel_size=1, max_displacement=4, stride1=1, stride2=1, corr_multiply=1)
+        lv, tot = {}, 0.0
+        for lvl, (C, h, w) in LEVELS.items():
+            f1, f2, flow = O.corr_microbench_inputs(lvl, B, h, w, C, with_flow=(lvl < 6))
+            f1, f2 = f1.to(dev), f2.to(dev)
+            fl = None if flow is None else flow.to(dev) * O.FLOW_SCALE[lvl]
+
+            def step():
+                with torch.no_grad():
+                    w2 = f2 if fl is None else m.warp(f2, fl)
+                    return F.leaky_relu(corr(f1, w2), 0.1)
+            for _ in range(3):
+                step()
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(10):
+                step()
+            e1.record(); e1.synchronize()
+            t = e0.elapsed_time(e1) * 1e-3 / 10
+            nbytes = 4.0 * B * h * w * (2 * C + 81 + (2 if lvl < 6 else 0))
+            lv[f"L{lvl}"] = {"us": round(t * 1e6, 1), "GBps": round(nbytes / t / 1e9, 1)}
+            tot += t
+        out["warp_corr_lrelu"] = {"levels": lv, "total_us": round(tot * 1e6, 1),
+                                  "what": "reference PWCDCNet.warp + correlation_cuda.forward + leaky_relu, eager, fp32 NCHW"}
+        out["what"] = "unmodified /root/reference models/PWCNet.py + its correlation_cuda (7-token F8 patch) on this GPU, eager"
+        del m
+        torch.cuda.empty_cache()
+        return out
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": f"{type(e).__name__}: {e}"}
 
 
 def ncu_traffic(layer):
@@ -222,7 +308,7 @@ def run_ours(args):
     # the same pairs handed over as uint8 BGR frames (what the reference drivers hold before frame_to_tensor): /255 + pad +
     # cat run on the GPU, 6 bytes per pixel pair go over PCIe instead of 24 -- reported beside the fp32-input figure
     t_u8 = None
-    if args.mode == "bf16":
+    if args.mode != "fp32":
         gen = torch.Generator().manual_seed(7 + rank)
         u8_hosts = [torch.randint(0, 256, (B, 2, H, W, 3), dtype=torch.uint8, generator=gen).pin_memory() for _ in range(2)]
         pipe8 = driver.FlowPipeline(model, B, H, W, dev, input="u8")
@@ -248,6 +334,41 @@ def run_ours(args):
     t_sync = e0.elapsed_time(e1) * 1e-3
     barrier()
     clocks = sampler.stop() if sampler else None
+    # ---- sustained leg (BASELINE configs[4] "sustained pairs/s"): the same graph back to back for >= args.sustain seconds,
+    #      then the uint8-input pipeline for as long, clocks and power sampled throughout ----
+    sus = None
+    if args.sustain > 0:
+        n_s = max(args.steps, int(args.sustain / (t_dev / args.steps)) + 1)
+        sampler2 = ClockSampler(local) if rank == 0 else None
+        if sampler2:
+            sampler2.start(); time.sleep(0.2)
+        barrier()
+        e0.record()
+        for _ in range(n_s):
+            run_step()
+        e1.record(); e1.synchronize()
+        t_sus = e0.elapsed_time(e1) * 1e-3
+        barrier()
+        n_p = max(args.steps, int(args.sustain / (t_e2e / args.steps)) + 1)
+        pipe_s = pipe
+        hosts_s = x_hosts
+        if args.mode != "fp32":
+            pipe_s = driver.FlowPipeline(model, B, H, W, dev, input="u8")
+            hosts_s = u8_hosts
+            pipe_s.run((hosts_s[i % 2] for i in range(3)))
+        barrier()
+        e0.record()
+        pipe_s.run((hosts_s[i % 2] for i in range(n_p)))
+        e1.record(); e1.synchronize()
+        t_sus_e2e = e0.elapsed_time(e1) * 1e-3
+        barrier()
+        ck2 = sampler2.stop() if sampler2 else None
+        if world > 1:
+            t_sus, t_sus_e2e = driver.max_over_ranks([t_sus, t_sus_e2e], device=dev)
+        sus = {"value": B * world * n_s / t_sus, "e2e": B * world * n_p / t_sus_e2e, "unit": "pairs/s", "seconds": [t_sus, t_sus_e2e],
+               "steps": [n_s, n_p], "e2e_input": "uint8 frames (FlowPipeline input='u8')" if args.mode != "fp32" else "fp32 [B,6,H,W]",
+               "sm_mhz_median": ck2 and ck2["sm_mhz"], "power_w_max": ck2 and ck2["power_w_max"],
+               "reasons": ck2 and ck2["reasons"], "vs_burst": (B * world * n_s / t_sus) / (B * world * args.steps / t_dev)}
     if world > 1:
         t_dev, t_e2e, t_sync, t_u8x = driver.max_over_ranks([t_dev, t_e2e, t_sync, t_u8 if t_u8 is not None else 0.0], device=dev)
         t_u8 = t_u8x if t_u8 is not None else None
@@ -308,11 +429,28 @@ def run_ours(args):
                 "frac": step_tflops / peaks["bf16_tflops_sustained"], "traffic": None,
                 "note": "whole forward (fp32 CUDA-core mode): conv FLOPs / step time"}
     # host-core baseline: rank 0 at N = 1 only (under torchrun the other ranks' processes share the cores)
-    cpu_v, cpu_cores, cpu_sample = cpu_reference_forward_timer(H, W, reps=5) if world == 1 else (None, None, "not measured at N > 1")
+    cpu_v, cpu_cores, cpu_sample, cpu_kind, cpu_v1 = cpu_reference_forward_timer(H, W, reps=5) if world == 1 else \
+        (None, None, "not measured at N > 1", "reference", None)
+    gpu_base = gpu_reference_baseline(dev, B, H, W) if world == 1 else None
+    parity = None
+    if world == 1:
+        # parity of exactly what was benched: this mode, this batch, this shape, against the CPU oracle on the first pairs
+        npar = min(B, 2)
+        got_f = model(x).float().cpu()[:npar]
+        ref_f = O.forward({k: v.detach().cpu() for k, v in model.state_dict().items()}, x_host[:npar])
+        d_ = (got_f - ref_f)
+        epe = d_.pow(2).sum(1).sqrt().mean().item()
+        parity = {"vs": "oracle/pwcnet_oracle.forward (CPU fp32, pinned to the unmodified reference)", "pairs_checked": npar,
+                  "epe_delta_px_over_20": epe, "epe_delta_px": 20.0 * epe, "max_abs_px": 20.0 * d_.abs().max().item(),
+                  "flow_max_px": 20.0 * ref_f.abs().max().item(),
+                  "bar": "fp32: max-abs <= 1e-3 px; 16-bit conv modes: mean EPE delta <= 0.02 px on the x20 flow (script_pwc.py:72)"}
+    if sus is not None and roof is not None:
+        sus["step_tflops"] = sus["value"] * gflop_pair / 1e3 / world
+        sus["frac_of_sustained_peak"] = sus["step_tflops"] / peaks["bf16_tflops_sustained"]
     line = {
         "metric": "pwcnet_frame_pairs_per_s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.mode == "bf16" else "f32", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16", "f16": "f16", "fp32": "f32"}.get(args.mode, args.mode), "data": "synthetic",
         "config": {"workload": f"PWCDCNet forward, batch {B}/GPU, {W}x{H}, random-init weights, conv_mode={args.mode}",
                    "l2": "activation working set per step >> 126 MB L2 (no flush needed)", "parallelism": f"pairs sharded x{world}, no collective"},
         "e2e": {"value": pairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": x_host.numel() * 4 * world,
@@ -325,8 +463,10 @@ def run_ours(args):
         "gpu_launches": launches_per_step * args.steps * world,
         "roofline": roof, "roofline_corr": roof_corr, "roofline_corr_fp32": roof_corr_f32,
         "step_tflops": step_tflops,
-        "cpu_baseline": {"value": cpu_v, "unit": "pairs/s", "cores": cpu_cores, "kind": "port", "sample": cpu_sample},
-        "clocks": clocks,
+        "cpu_baseline": {"value": cpu_v, "unit": "pairs/s", "cores": cpu_cores, "kind": cpu_kind, "sample": cpu_sample,
+                         "one_thread_value": cpu_v1},
+        "gpu_baseline": gpu_base,
+        "clocks": clocks, "sustained": sus, "parity": parity,
     }
     if kern_table and os.environ.get("PWC_BENCH_KERNELS"):
         line["kernel_us"] = kern_table
@@ -341,7 +481,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "bf16"), choices=["fp32", "bf16"])
+    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "bf16"), choices=["fp32", "bf16", "f16", "mixed"])
+    ap.add_argument("--sustain", type=float, default=float(os.environ.get("PWC_BENCH_SUSTAIN", "3")),
+                    help="seconds of the back-to-back sustained leg (0 = off)")
     ap.add_argument("--batch", type=int, default=B_DEF)
     ap.add_argument("--height", type=int, default=H_DEF)
     ap.add_argument("--width", type=int, default=W_DEF)

@@ -38,6 +38,7 @@ struct TcConvParams {
   void* out2; long out2_pitch; int out2_coff;
   int out_f32;
   const float* residual; long res_pitch;
+  int fp16;                                       // 16-bit operands / outputs are IEEE half instead of bf16
 };
 
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -103,7 +104,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   } else if (warp == 1) {
     // ===================== MMA issuer: whole warp converged, ONE elected lane issues (see conv_tc_halo.cuh) =====
     {
-      const uint32_t idesc = ptx::make_idesc_bf16(kTcM, p.coutp);
+      uint32_t idesc = ptx::make_idesc_bf16(kTcM, p.coutp);
+      if (p.fp16) idesc &= ~((7u << 7) | (7u << 10));          // A/B format 0 = F16
       const uint32_t row_bytes = p.kc * 2;
       const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
       int s = 0; uint32_t ph = 0;
@@ -175,10 +177,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                                       : reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.out_pitch + p.out_coff;
             uint32_t w[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-              w[i] = *reinterpret_cast<uint32_t*>(&h);
-            }
+            for (int i = 0; i < 8; ++i) w[i] = pack2_h16(f[2 * i], f[2 * i + 1], p.fp16);
             uint4* o4 = reinterpret_cast<uint4*>(o + c0);
             o4[0] = make_uint4(w[0], w[1], w[2], w[3]);
             o4[1] = make_uint4(w[4], w[5], w[6], w[7]);
@@ -216,7 +215,8 @@ struct pwc_tc_conv {
 namespace pwc {
 
 __global__ void pack_conv_weight_bf16_kernel(const float* __restrict__ wt, __nv_bfloat16* __restrict__ wp,
-                                             const int* __restrict__ map, int Cout, int Cin, int nchunk, int kc, int coutp) {
+                                             const int* __restrict__ map, int Cout, int Cin, int nchunk, int kc, int coutp,
+                                             int f16) {
   // wt: [Cout][Cin][3][3] fp32 -> wp: [9][nchunk][coutp][kc] bf16 (pre-zeroed)
   const long total = (long)Cout * Cin * 9;
   for (long e = blockIdx.x * (long)blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
@@ -224,11 +224,13 @@ __global__ void pack_conv_weight_bf16_kernel(const float* __restrict__ wt, __nv_
     const int ci = r % Cin, co = r / Cin;
     const int row = map ? map[ci] : ci;
     const int ch = row / kc, kk = row - ch * kc;
-    wp[(((long)tap * nchunk + ch) * coutp + co) * kc + kk] = __float2bfloat16_rn(wt[e]);
+    reinterpret_cast<uint16_t*>(wp)[(((long)tap * nchunk + ch) * coutp + co) * kc + kk] = pack1_h16(wt[e], f16);
   }
 }
 
 static int g_num_sms = 0;
+static thread_local int g_half_format = 0;        // 0 = bf16, 1 = IEEE half (pwc_set_half_format)
+int half_format() { return g_half_format; }
 
 static int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
@@ -287,7 +289,7 @@ static int create_halo(pwc_tc_conv** handle, const void* in, long in_pitch, int 
   p.b_stages = stages > 12 ? 12 : (stages < 2 ? 2 : stages);
   uint32_t cols = 32; while (cols < 2u * halves * p.nsl) cols <<= 1;
   p.tmem_cols = cols;
-  p.fp16 = 0; p.bo_mode = env_int("PWC_TC_HALO_BO", 0);
+  p.fp16 = g_half_format; p.bo_mode = env_int("PWC_TC_HALO_BO", 0);
   p.bias = bias; p.slope = slope;
   p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
   p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = out2 ? n_split : N;
@@ -456,7 +458,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   uint32_t cols = 32; while (cols < 2u * p.npx) cols <<= 1;
   if (ts) cols = 512;
   p.tmem_cols = cols;
-  p.fp16 = 0; p.dbg = env_int("PWC_TC_HALO_BO", 0);
+  p.fp16 = g_half_format; p.dbg = env_int("PWC_TC_HALO_BO", 0);
   p.bias = bias; p.slope = slope;
   p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
   p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff; p.n_split = (out2 && out_f32 != 2) ? n_split : N;
@@ -534,16 +536,21 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   using namespace pwc;
   if (!handle) return (int)cudaErrorInvalidValue;
   *handle = nullptr;
-  if (!g_num_sms) {
+  {
+    // per DEVICE: the shared-memory opt-in is a per-device function attribute and PWCDCNet.forward follows its input's device
+    static int attr_dev = -1;
     int dev = 0; cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
-    cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_wm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_wm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_wm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    cudaFuncSetAttribute(conv_tc_wm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (attr_dev != dev) {
+      cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+      if (g_num_sms <= 0) g_num_sms = 148;
+      cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(conv_tc_wm_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(conv_tc_wm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(conv_tc_wm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(conv_tc_wm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      attr_dev = dev;
+    }
   }
   const int wm_max_dil = env_int("PWC_TC_WM_YDENSE_MINDIL", 8) <= 16 ? 16 : 8;    // y-dense tiles take dilation 16 too
   if (halo_eligible(stride, dil, in2 != nullptr, kc, wm_max_dil) && coutp <= 128 && (env_int("PWC_TC_WM", 1) || out_f32 == 2) &&
@@ -583,6 +590,7 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   p.out = out; p.out_pitch = out_pitch; p.out_coff = out_coff;
   p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff;
   p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
+  p.fp16 = g_half_format;
   h->smem_bytes = (size_t)p.stages * p.stage_bytes + 8 * (2 * p.stages + 5) + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
@@ -690,6 +698,13 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
 
 extern "C" void pwc_tc_conv_destroy(pwc_tc_conv* h) { delete h; }
 
+extern "C" int pwc_set_half_format(int fmt) {
+  if (fmt != 0 && fmt != 1) return (int)cudaErrorInvalidValue;
+  pwc::g_half_format = fmt;
+  return 0;
+}
+extern "C" int pwc_get_half_format(void) { return pwc::g_half_format; }
+
 // ------------------------------------------------------------------------------------------------------------------
 // Split-K launch that allocates nothing (no counterpart in the reference; added
 // for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).  The fp32 partial-sum scratch and
@@ -768,7 +783,7 @@ extern "C" int pwc_pack_conv_weight_bf16(const float* w_torch, void* w_packed, c
   cudaError_t e = cudaMemsetAsync(w_packed, 0, 2 * (size_t)9 * nchunk * coutp * kc, s);
   if (e != cudaSuccess) return (int)e;
   pwc::pack_conv_weight_bf16_kernel<<<256, 256, 0, s>>>(w_torch, reinterpret_cast<__nv_bfloat16*>(w_packed), chan_map,
-                                                        Cout, Cin, nchunk, kc, coutp);
+                                                        Cout, Cin, nchunk, kc, coutp, pwc::g_half_format);
   return (int)cudaGetLastError();
 }
 

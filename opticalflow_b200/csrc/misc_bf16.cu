@@ -375,9 +375,14 @@ static int launch_conv1a(const float* x, const float* w, const float* bias, void
       EncodeTiledFn enc = use_tma ? get_encode_tiled() : nullptr;
       if (enc) {
         const size_t smem = 2 * kC1M_BUF + 16;
-        static const cudaError_t attr = cudaFuncSetAttribute(conv1a_mma_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                             (int)(2 * kC1M_BUF + 16));
-        if (attr != cudaSuccess) return (int)attr;
+        static int attr_dev = -1;                                 // the opt-in is a per-device attribute
+        int dev = 0; cudaGetDevice(&dev);
+        if (attr_dev != dev) {
+          const cudaError_t attr = cudaFuncSetAttribute(conv1a_mma_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                        (int)(2 * kC1M_BUF + 16));
+          if (attr != cudaSuccess) return (int)attr;
+          attr_dev = dev;
+        }
         CUtensorMap tm;
         cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)(frames ? 3 * B : 6 * B)};
         cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)W * H * 4};

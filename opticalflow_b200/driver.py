@@ -142,13 +142,18 @@ class FlowPipeline:
         self.launches_per_batch = self.plan.launches
 
     @torch.no_grad()
-    def run(self, host_batches, sink=None):
+    def run(self, host_batches, sink=None, uploaded=None):
         """host_batches: iterable of pinned [B,6,H,W] fp32 tensors.  sink(i, flow_host) is called once batch i's flow2
-        ([B,2,H/4,W/4] fp32, pinned, reused after `depth` more batches) is on the host.  Returns the batch count."""
+        ([B,2,H/4,W/4] fp32, pinned) is on the host.  The tensor handed to sink is a pipeline-owned staging buffer that is
+        VALID ONLY DURING THE CALL: the next D2H copy into it is enqueued as soon as sink returns -- clone it to keep it.
+        uploaded(i, event): optional callback, called right after batch i's H2D copy has been enqueued; `event` (a
+        torch.cuda.Event) completes when the copy has finished reading the host batch -- a loader that recycles its
+        pinned buffers must wait for it (event.synchronize()) before overwriting batch i.  Returns the batch count."""
         cs = torch.cuda.current_stream(self.device)
         pending = []                                     # (i, slot) whose D2H is in flight
         n = 0
         with torch.cuda.device(self.device):
+            self.plan.pack_weights(self.model)           # no-op unless the parameters changed since the last run
             for i, xh in enumerate(host_batches):
                 s = i % self.depth
                 slot = self.u8_dev[s] if self.input == "u8" else self.x_dev[s]
@@ -163,6 +168,10 @@ class FlowPipeline:
                     self.s_in.wait_event(self.in_free[s])
                     slot.copy_(xh, non_blocking=True)
                     self.in_ready[s].record(self.s_in)
+                if uploaded is not None:
+                    ev = torch.cuda.Event()
+                    ev.record(self.s_in)
+                    uploaded(i, ev)
                 cs.wait_event(self.in_ready[s])
                 if self.input == "u8":                   # /255 + swap + pad + cat into the fp32 slot; the u8 slot is free again
                     from . import prepost
@@ -270,7 +279,9 @@ class VideoFlowPipeline:
     @torch.no_grad()
     def run(self, frames, sink=None):
         """frames: pinned uint8 tensor [N,H,W,3] (N >= 2).  sink(t0, count, flow_host) receives the flows of pairs
-        (t0+k, t0+k+1), k < count, as [count,2,oh,ow] fp32 (pinned, reused after `depth` batches).  Returns N-1."""
+        (t0+k, t0+k+1), k < count, as [count,2,oh,ow] fp32 (a pinned staging buffer, valid only during the sink call: the
+        next D2H copy into it is enqueued as soon as sink returns).  `frames` must stay untouched until run() returns.
+        Returns N-1."""
         if frames.dtype != torch.uint8 or frames.dim() != 4 or tuple(frames.shape[1:]) != (self.H, self.W, 3):
             raise RuntimeError(f"VideoFlowPipeline: uint8 [N,{self.H},{self.W},3] frames expected, got {tuple(frames.shape)}")
         n_pairs = frames.shape[0] - 1
@@ -284,6 +295,7 @@ class VideoFlowPipeline:
                 sink(todo[j][0], todo[j][1], self.o_host[sj][:todo[j][1]])
 
         with torch.cuda.device(self.device):
+            self.plan.pack_weights(self.model)           # no-op unless the parameters changed since the last run
             for i, (t0, cnt) in enumerate(todo):
                 s = i % self.depth
                 if len(pending) == self.depth:

@@ -52,6 +52,27 @@ def chan_map(lvl, start):
     return list(range(dense)) + [dense + t for t in tail_map(lvl)]
 
 
+CONV_MODES = ("fp32", "bf16")
+
+
+def weights_key(model):
+    """Identity of the parameter values a plan has packed.  In-place edits through autograd-visible ops bump
+    ``p._version``; re-assigned storage changes ``data_ptr``.  Edits through ``.data`` (``m.weight.data.copy_()``,
+    ``nn.init.*(m.weight.data)`` -- the reference's own init idiom, PWCNet.py:134-138) change neither, so the key also
+    carries ``model._weights_epoch`` (``PWCDCNet.invalidate_weights()`` bumps it; ``load_state_dict`` does so
+    automatically) and, when ``model.verify_weights`` is set, a device-side checksum of every parameter (one reduction
+    + one 8-byte D2H copy per forward)."""
+    ps = list(model.parameters())
+    key = tuple((p.data_ptr(), p._version) for p in ps) + (id(model), getattr(model, "_weights_epoch", 0))
+    if getattr(model, "verify_weights", False):
+        import torch
+        with torch.no_grad():
+            sums = torch._foreach_norm([p.detach().double() for p in ps], 1)
+            w = torch.arange(1, len(ps) + 1, device=sums[0].device, dtype=torch.float64)
+            key += (float((torch.stack(sums) * w).sum().item()),)
+    return key
+
+
 def _roundup(a, b):
     return (a + b - 1) // b * b
 
@@ -96,7 +117,7 @@ class Plan:
 
     # ------------------------------------------------------------------ weights
     def pack_weights(self, model):
-        ver = tuple(p._version for p in model.parameters()) + (id(model),)
+        ver = weights_key(model)
         if ver == self.weights_version:
             return
         lib, dev = self.lib, self.device

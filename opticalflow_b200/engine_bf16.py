@@ -16,7 +16,7 @@ import torch
 
 from . import _lib
 from .ops import pick_kc
-from .engine import (C1_OFF, CORR_OFF, DC, DEC_START, DEC_WRITE, FLOW_SCALE, PYR_CH, UPFEAT_OFF, UPFLOW_OFF, chan_map,
+from .engine import (weights_key, C1_OFF, CORR_OFF, DC, DEC_START, DEC_WRITE, FLOW_SCALE, PYR_CH, UPFEAT_OFF, UPFLOW_OFF, chan_map,
                      concat_width)
 
 BF = torch.bfloat16
@@ -111,7 +111,8 @@ THIN_LAYERS = set(x for x in os.environ.get("PWC_THIN_LAYERS", "conv1aa.0,conv1b
 
 
 class _TcLayer:
-    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups", "kkskip")
+    __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups", "kkskip",
+                 "masks_set")
 
 
 class PlanBF16:
@@ -401,7 +402,7 @@ class PlanBF16:
 
     # ------------------------------------------------------------------ weights
     def pack_weights(self, model):
-        ver = tuple(p._version for p in model.parameters()) + (id(model),)
+        ver = weights_key(model)
         if ver == self.weights_version:
             return
         if not self.ops:
@@ -420,29 +421,39 @@ class PlanBF16:
             _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.wrows, L.cin, L.span, L.kc,
                                                      L.coutp, st), f"pack {key}")
             L.b.copy_(bs)
-            if L.kkskip:
-                # single-chunk space-to-depth layer: all-zero 16-channel K steps of each tap's weight tile are not issued
-                km = (ctypes.c_int * 9)()
-                for tap in range(9):
-                    blk = wt[:, :, tap // 3, tap % 3]
-                    for kk in range((L.span + 15) // 16):
-                        if not bool((blk[:, 16 * kk:16 * kk + 16] != 0).any()):
-                            km[tap] |= 1 << kk
-                _lib.check(lib.pwc_tc_conv_set_kk_skip(L.handle, km), f"set_kk_skip {key}")
-            if L.groups is not None:
-                # zero-block skip list of the block-structured space-to-depth weight: (tap, 64-channel chunk) pairs
-                nchunk = (L.span + L.kc - 1) // L.kc
-                cm = torch.tensor(L.cmap, device=dev, dtype=torch.long) if L.cmap is not None else torch.arange(L.cin, device=dev)
-                masks = (ctypes.c_ulonglong * 9)()
-                for tap in range(9):
-                    nz = (wt[:, :, tap // 3, tap % 3] != 0).any(0)
-                    used = torch.zeros(nchunk, dtype=torch.bool, device=dev)
-                    used[(cm[nz] // L.kc).unique()] = True
-                    m = 0
-                    for ch in (~used).nonzero().flatten().tolist():
-                        m |= 1 << ch
-                    masks[tap] = m
-                _lib.check(lib.pwc_tc_conv_set_skip(L.handle, masks), f"set_skip {key}")
+            if (L.kkskip or L.groups is not None) and not getattr(L, "masks_set", False):
+                # Skip masks come from the STRUCTURE of the space-to-depth weight (which (tap, K block) pairs can ever be
+                # non-zero: the weight builder applied to all-ones parameters), never from the values: they are kernel
+                # parameters baked into the captured CUDA graph and must not change when a new state_dict is loaded.
+                ones = {k: torch.ones_like(v) for k, v in sd.items() if k.startswith(key.split(".")[0] + ".")}
+                ws = (L.wfn(ones)[0] != 0)
+                if L.kkskip:
+                    # single-chunk layer: all-zero 16-channel K steps of each tap's weight tile are not issued
+                    km = (ctypes.c_int * 9)()
+                    nkk = (L.span + 15) // 16
+                    for tap in range(9):
+                        blk = ws[:, :, tap // 3, tap % 3]
+                        for kk in range(nkk):
+                            if not bool(blk[:, 16 * kk:16 * kk + 16].any()):
+                                km[tap] |= 1 << kk
+                    if all(km[t] == (1 << nkk) - 1 for t in range(9)):
+                        km = (ctypes.c_int * 9)()                # nothing structurally non-zero: issue everything
+                    _lib.check(lib.pwc_tc_conv_set_kk_skip(L.handle, km), f"set_kk_skip {key}")
+                if L.groups is not None:
+                    # zero-block skip list of the block-structured weight: (tap, 64-channel chunk) pairs
+                    nchunk = (L.span + L.kc - 1) // L.kc
+                    cm = torch.tensor(L.cmap, device=dev, dtype=torch.long) if L.cmap is not None else torch.arange(L.cin, device=dev)
+                    masks = (ctypes.c_ulonglong * 9)()
+                    for tap in range(9):
+                        nz = ws[:, :, tap // 3, tap % 3].any(0)
+                        used = torch.zeros(nchunk, dtype=torch.bool, device=dev)
+                        used[(cm[nz] // L.kc).unique()] = True
+                        m = 0
+                        for ch in (~used).nonzero().flatten().tolist():
+                            m |= 1 << ch
+                        masks[tap] = m
+                    _lib.check(lib.pwc_tc_conv_set_skip(L.handle, masks), f"set_skip {key}")
+                L.masks_set = True
         for key, (w, b, cin, cinp) in self.small.items():
             wt = sd[key + ".weight"]
             mp = None

@@ -136,7 +136,10 @@ def read_png16(filename):
 
 
 def write_kitti_png(filename, flow, valid=None):
-    """save_flow of inference.py:266-282 (file content: R = u, G = v, B = valid, 16 bit)."""
+    """Role of save_flow (inference.py:266-282), NOT byte-compatible with it: the reference stacks [valid, v, u] (R = valid,
+    B = u) and hands a uint16 RGB array to PIL, which cannot encode it.  This writer emits the standard KITTI layout
+    (R = u, G = v, B = valid, 16 bit: u16 = flow*64 + 2^15), the one load_flow_kitti_png (inference_kitti.py:23-52) and
+    read_kitti_png below decode; write -> read round-trips (tests/test_prepost.py)."""
     write_png16(filename, encode_kitti(flow, valid))
 
 

@@ -82,6 +82,8 @@ class PWCDCNet(nn.Module):
         self.conv_mode = conv_mode
         self.align_corners = align_corners
         self._plans = {}
+        self._weights_epoch = 0
+        self.verify_weights = False      # True: checksum the parameters every forward (catches edits through .data)
 
     # -- execution ---------------------------------------------------------------------------------
     def _plan(self, B, H, W, device, video=False):
@@ -94,6 +96,17 @@ class PWCDCNet(nn.Module):
 
     def release_plans(self):
         self._plans.clear()
+
+    def invalidate_weights(self):
+        """Call after changing parameters through ``.data`` (``m.weight.data.copy_(...)``, ``nn.init.*(m.weight.data)``):
+        such edits bump neither ``_version`` nor ``data_ptr``, so the packed kernel-side weights would go stale.
+        ``load_state_dict`` calls this itself; ``verify_weights = True`` detects such edits automatically."""
+        self._weights_epoch += 1
+
+    def load_state_dict(self, *a, **kw):
+        r = super().load_state_dict(*a, **kw)
+        self.invalidate_weights()
+        return r
 
     @torch.no_grad()
     def forward(self, x):

@@ -197,6 +197,18 @@ def warp(x, flo, align_corners=False, mask_thresh=0.9999):
     return output * mask
 
 
+def warp_mask_sum(flo, H, W, align_corners=False):
+    """The quantity PWCNet.py:168-174 thresholds at 0.9999: grid_sample(ones, vgrid) per pixel, [B,H,W] (test aid: a
+    pixel whose sum sits within rounding of the threshold may legitimately flip between two fp32 evaluation orders)."""
+    B = flo.shape[0]
+    xx = torch.arange(0, W).view(1, -1).repeat(H, 1).view(1, 1, H, W).repeat(B, 1, 1, 1)
+    yy = torch.arange(0, H).view(-1, 1).repeat(1, W).view(1, 1, H, W).repeat(B, 1, 1, 1)
+    vgrid = torch.cat((xx, yy), 1).float() + flo
+    vgrid[:, 0, :, :] = 2.0 * vgrid[:, 0, :, :].clone() / max(W - 1, 1) - 1.0
+    vgrid[:, 1, :, :] = 2.0 * vgrid[:, 1, :, :].clone() / max(H - 1, 1) - 1.0
+    return F.grid_sample(torch.ones(B, 1, H, W), vgrid.permute(0, 2, 3, 1), align_corners=align_corners)[:, 0]
+
+
 def warp_corr_lrelu(f1, f2, flow, scale, align_corners=False, slope=0.1, mask_thresh=0.9999):
     """The fused op the CUDA kernel implements, composed from the reference pieces:
     leakyRELU(corr(f1, warp(f2, flow*scale)))  (PWCNet.py:212-214).  flow=None -> level 6 (PWCNet.py:198-199)."""

@@ -1,0 +1,85 @@
+"""Parity of EXACTLY what bench.py measures: the batch sizes and shapes of BASELINE.json configs[2..4] --
+(8, 448, 1024), (16, 384, 1280) = KITTI 1242x375 padded, (4, 1088, 1920) = 1080p padded -- in every conv mode, against the
+CPU oracle on the first and the last pair of the batch (pairs are independent; tiling depends on the batch), plus the
+level-3 / level-2 cost volumes of the fp32 plan (88% of the cost-volume bytes) and the shared-pyramid video plan at 1088p.
+Both units are printed: flow2 as returned (px/20) and the x20 flow in pixels (script_pwc.py:72); asserts are in pixels."""
+import warnings
+
+import pytest
+import torch
+
+from oracle import pwcnet_oracle as O
+
+warnings.filterwarnings("ignore")
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(8, 448, 1024), (16, 384, 1280), (4, 1088, 1920)]
+# mean EPE delta bars in PIXELS of the x20 flow.  fp32: the north_star max-abs bar.  16-bit storage modes: the measured floor
+# of the storage type (an fp32 forward with that rounding of weights and stored activations, tools/error_budget.py) x 1.5.
+MEAN_EPE_BAR_PX = {"bf16": 0.60, "f16": 0.09, "mixed": 0.02}
+
+
+def _model(mode):
+    from opticalflow_b200.models.PWCNet import PWCDCNet
+    torch.manual_seed(0)
+    return PWCDCNet(conv_mode=mode).eval().cuda()
+
+
+def _modes():
+    from opticalflow_b200 import engine
+    return [m for m in ("fp32", "bf16", "f16", "mixed") if m in getattr(engine, "CONV_MODES", ("fp32", "bf16"))]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("mode", ["fp32", "bf16", "f16", "mixed"])
+def test_forward_at_bench_shapes(mode, shape):
+    if mode not in _modes():
+        pytest.skip(f"conv_mode {mode} not built")
+    B, H, W = shape
+    m = _model(mode)
+    sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
+    x = O.synthetic_input(B, H, W, 1)
+    flow = m(x.cuda()).float().cpu()
+    sel = [0, B - 1]
+    ref, inter = O.forward(sd, x[sel], return_intermediates=True)
+    d = 20.0 * (flow[sel] - ref)
+    epe_px, max_px = d.pow(2).sum(1).sqrt().mean().item(), d.abs().max().item()
+    print(f"{mode} B={B} {W}x{H}: mean EPE delta {epe_px / 20:.5f} px/20 = {epe_px:.4f} px, max-abs {max_px:.4f} px, "
+          f"|flow| max {20 * ref.abs().max().item():.1f} px")
+    if mode == "fp32":
+        assert max_px <= 1e-3
+        plan = next(iter(m._plans.values()))
+        for lvl in (3, 2):                      # GPU cost volumes straight out of the concat buffers vs the oracle's
+            c = plan.cat[lvl][sel][..., 448:529].permute(0, 3, 1, 2).cpu()
+            rc = inter[f"corr{lvl}"]
+            # in-forward volumes inherit the fp32 summation-order noise of everything upstream (features, up_flow): 1e-4 of
+            # the scale as in test_gpu_forward.py; the kernel alone is held to 1e-5 in test_gpu_kernels.py / test_gpu_reference.py
+            bad = ((c - rc).abs() > 1e-4 * rc.abs().max().item()).float().mean().item()
+            assert bad <= 2e-4, f"corr{lvl}: {bad:.2e} of the elements beyond 1e-4 relative"
+    else:
+        assert epe_px <= MEAN_EPE_BAR_PX[mode], f"{mode}: mean EPE delta {epe_px:.4f} px on the x20 flow"
+    assert torch.equal(m(x.cuda()).float().cpu(), flow)          # graph replay is bit-identical
+    m.release_plans()
+    torch.cuda.empty_cache()
+
+
+@pytest.mark.parametrize("mode", ["bf16", "f16", "mixed"])
+def test_video_plan_shared_pyramid_at_1088p(mode):
+    """PlanBF16(video=True) at the 1080p stream shape: B consecutive pairs from B+1 frames == the per-pair plan fed the
+    same frames as (t, t+1) pairs, bit for bit (same kernels, same tiles: the pyramid is only computed once per frame)."""
+    if mode not in _modes():
+        pytest.skip(f"conv_mode {mode} not built")
+    B, H, W = 3, 1088, 1920
+    m = _model(mode)
+    g = torch.Generator().manual_seed(11)
+    frames = torch.rand(B + 1, 3, H, W, generator=g).cuda()
+    pairs = torch.cat([frames[:-1], frames[1:]], 1).contiguous()
+    ref = m(pairs).clone()
+    plan = m._plan(B, H, W, frames.device, video=True)
+    plan.pack_weights(m)
+    out = plan.run(frames).clone()
+    d = 20.0 * (out - ref).abs().max().item()
+    print(f"{mode} video plan 1088p: max-abs difference to the per-pair plan {d:.3e} px")
+    assert d <= 1e-3
+    m.release_plans()
+    torch.cuda.empty_cache()

@@ -29,13 +29,25 @@ def _rel_err(a, ref):
     return (a - ref).abs().max().item() / max(ref.abs().max().item(), 1e-30)
 
 
-def _robust_corr_check(out, ref, tol=1e-5, max_bad_frac=2e-4):
-    """max-abs relative to the tensor scale, allowing a tiny number of pixels whose warp mask flipped."""
-    scale = ref.abs().max().item()
+def _robust_corr_check(out, ref, tol=1e-5, max_bad_frac=2e-4, flow=None, scale=1.0, align_corners=False, mask_eps=2e-6):
+    """max-abs relative to the tensor scale.  The only elements allowed beyond `tol` are those that read a warped pixel
+    whose mask sum (PWCNet.py:168-174) lies within `mask_eps` of the 0.9999 threshold in the oracle -- there the mask may
+    flip between grid_sample's and the fused kernel's fp32 evaluation order; such elements stay below `max_bad_frac`."""
+    scale_t = ref.abs().max().item()
     err = (out - ref).abs()
-    bad = (err > tol * scale)
+    bad = (err > tol * scale_t)
     frac = bad.float().mean().item()
-    assert frac <= max_bad_frac, f"{bad.sum().item()} elements ({frac:.2e}) beyond {tol} relative; max {err.max().item()/scale:.3e}"
+    assert frac <= max_bad_frac, f"{bad.sum().item()} elements ({frac:.2e}) beyond {tol} relative; max {err.max().item()/scale_t:.3e}"
+    if bad.any():
+        assert flow is not None, f"{bad.sum().item()} elements beyond {tol} relative without a warp to explain them"
+        B, _, H, W = ref.shape
+        near = ((O.warp_mask_sum(flow * scale, H, W, align_corners) - 0.9999).abs() <= mask_eps)       # [B,H,W]
+        pad = torch.zeros(B, H + 8, W + 8, dtype=torch.bool)
+        pad[:, 4:H + 4, 4:W + 4] = near
+        for n, d, y, x in bad.nonzero().tolist():
+            dy, dx = d // 9 - 4, d % 9 - 4
+            assert pad[n, y + dy + 4, x + dx + 4], \
+                f"element {(n, d, y, x)} is off by {err[n, d, y, x].item() / scale_t:.2e} and its warped pixel is not at the mask threshold"
     return frac
 
 
@@ -69,7 +81,7 @@ def test_fused_warp_corr_levels(lvl, layout):
         nhwc = lambda t: t.permute(0, 2, 3, 1).contiguous().to(d)  # noqa: E731
         out = ops.warp_corr_lrelu(nhwc(f1), nhwc(f2), None if flow is None else nhwc(flow), scale, layout="nhwc")
         out = out.permute(0, 3, 1, 2).contiguous().cpu()
-    _robust_corr_check(out, ref)
+    _robust_corr_check(out, ref, flow=flow, scale=scale)
 
 
 @pytest.mark.parametrize("case", ["zero", "huge", "subpixel", "align_corners"])
@@ -90,7 +102,7 @@ def test_fused_warp_corr_edge_flows(case):
     ref = O.warp_corr_lrelu(f1, f2, flow, 1.25, align_corners=ac)
     d = _dev()
     out = ops.warp_corr_lrelu(f1.to(d), f2.to(d), flow.to(d), 1.25, align_corners=ac, layout="nchw").cpu()
-    _robust_corr_check(out, ref)
+    _robust_corr_check(out, ref, flow=flow, scale=1.25, align_corners=ac)
     if case == "zero":
         # 1-px border of the warped features is masked -> displacement (0,0) is 0 there
         assert out[:, 40, 0, :].abs().max() == 0 and out[:, 40, :, 0].abs().max() == 0

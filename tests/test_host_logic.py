@@ -41,3 +41,50 @@ def test_predict_flow_plus_upfeat_as_one_conv(lvl):
         for bb in range(2):
             c0 = 2 + 2 * (2 * a + bb)
             assert torch.allclose(y[:, c0:c0 + 2], up[:, :, a::2, bb::2], atol=1e-4)
+
+
+def test_pwc_dc_net_loader_accepts_the_checkpoint_layouts(tmp_path):
+    """pwc_dc_net(path) (PWCNet.py:497-506) and the drivers' variants: {'state_dict': ...}, {'model': ...}, a flat dict,
+    and keys carrying DataParallel's 'module.' prefix (pwc_extract_flow_video.py:167-172)."""
+    import torch
+    from opticalflow_b200.models.PWCNet import PWCDCNet, pwc_dc_net
+    torch.manual_seed(3)
+    src = PWCDCNet()
+    sd = {k: v.clone() for k, v in src.state_dict().items()}
+    assert len(sd) == 128
+    variants = {
+        "flat.pth.tar": sd,
+        "state_dict.pth.tar": {"state_dict": sd, "epoch": 7},
+        "model.pth.tar": {"model": sd},
+        "module.pth.tar": {"state_dict": {"module." + k: v for k, v in sd.items()}},
+    }
+    for name, obj in variants.items():
+        p = tmp_path / name
+        torch.save(obj, p)
+        m = pwc_dc_net(str(p))
+        got = m.state_dict()
+        assert set(got) == set(sd), name
+        assert all(torch.equal(got[k], sd[k]) for k in sd), name
+        assert m._weights_epoch >= 1                       # load_state_dict invalidates the packed kernel-side weights
+    # a checkpoint of another topology is refused, as torch's strict load_state_dict does in the reference
+    bad = dict(sd); bad.pop("conv1a.0.weight")
+    torch.save(bad, tmp_path / "bad.pth.tar")
+    import pytest
+    with pytest.raises(RuntimeError):
+        pwc_dc_net(str(tmp_path / "bad.pth.tar"))
+
+
+def test_weights_key_sees_data_edits_when_asked():
+    import torch
+    from opticalflow_b200.engine import weights_key
+    from opticalflow_b200.models.PWCNet import PWCDCNet
+    m = PWCDCNet()
+    k0 = weights_key(m)
+    m.conv1a[0].weight.data.mul_(2.0)                      # the reference's init idiom: invisible to _version / data_ptr
+    assert weights_key(m) == k0
+    m.invalidate_weights()
+    assert weights_key(m) != k0
+    m.verify_weights = True
+    k1 = weights_key(m)
+    m.conv1a[0].weight.data.mul_(0.5)
+    assert weights_key(m) != k1                            # the checksum catches it without an explicit call

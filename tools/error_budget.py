@@ -60,11 +60,12 @@ policies = {
     "fp16 L2+L3 (dec+ctx), fp32 pyramid & L4-6": lambda n, k: hf if (("_" in n) and level_of(n) <= 3) else None,
     "fp16 all but L4-6 decoders": lambda n, k: None if (("_" in n and not n.startswith("dc") and level_of(n) >= 4) or n in ("lvl6","lvl5","lvl4")) else hf,
 }
-for iname, x in inputs.items():
-    t0 = time.time()
-    ref = O.forward(sd, x)
-    print(f"[{iname}] ref forward {time.time()-t0:.1f}s |flow2| max {ref.abs().max():.3f} (x20 = {20*ref.abs().max():.1f} px)")
-    for pname, pol in policies.items():
-        out = run(x, pol)
-        e = epe(out, ref)
-        print(f"  {pname:48s} EPE delta {e:.5f} (px/20)  = {20*e:.4f} px")
+if __name__ == "__main__":
+  for iname, x in inputs.items():
+      t0 = time.time()
+      ref = O.forward(sd, x)
+      print(f"[{iname}] ref forward {time.time()-t0:.1f}s |flow2| max {ref.abs().max():.3f} (x20 = {20*ref.abs().max():.1f} px)")
+      for pname, pol in policies.items():
+          out = run(x, pol)
+          e = epe(out, ref)
+          print(f"  {pname:48s} EPE delta {e:.5f} (px/20)  = {20*e:.4f} px")
