@@ -481,7 +481,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "bf16"), choices=["fp32", "bf16", "f16", "mixed"])
+    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "f16"), choices=["fp32", "bf16", "f16", "mixed"])
     ap.add_argument("--sustain", type=float, default=float(os.environ.get("PWC_BENCH_SUSTAIN", "3")),
                     help="seconds of the back-to-back sustained leg (0 = off)")
     ap.add_argument("--batch", type=int, default=B_DEF)

@@ -198,6 +198,14 @@ void pwc_tc_conv_destroy(pwc_tc_conv* handle);
  *   that overlap on that GPU (different streams, no ordering) race.  The atomic summation order varies, so results may
  *   differ from pwc_tc_conv_launch in the last bit of the bf16 output. */
 int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* handle, int ksplit, void* stream);
+/* 16-bit storage format of the tensor-core conv mode.  Every entry point that takes or produces 16-bit tensors (the
+ * pwc_tc_conv_* family, pwc_conv3x3_mma_fwd, pwc_conv3x3_thin_fwd, pwc_conv3x3_flow_head_fwd, pwc_conv1a_*_bf16_fwd,
+ * pwc_pack_conv_weight_bf16, and dtype == PWC_BF16 of pwc_warp_corr_lrelu_fwd / pwc_deconv4x4s2_c2_fwd) reads it at
+ * create / launch time: 0 = bfloat16 (default), 1 = IEEE half (conv_mode 'f16': 3 more mantissa bits; same kernels, same speed;
+ * ~7x lower end-to-end flow error).  Thread-local; a created pwc_tc_conv handle keeps the format it was created
+ * with; captured CUDA graphs keep what was current at capture.  No counterpart in the reference (it computes in fp32). */
+int pwc_set_half_format(int fmt);
+int pwc_get_half_format(void);
 /* debug aid: timeline of CTA 0 of the halo kernel (enabled by env PWC_TC_HALO_BO bit 16); host memory destination */
 int pwc_debug_halo_trace(unsigned long long* host_dst, int count);
 int pwc_debug_corr_trace(unsigned long long* host_dst, int count);

@@ -51,7 +51,7 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-template <int MTW, int NTL>
+template <int MTW, int NTL, bool F16>
 __global__ void __launch_bounds__(256, 2) conv_mma_small_kernel(const SmallConvParams p) {
   extern __shared__ __align__(128) uint8_t sm_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(256, 2) conv_mma_small_kernel(const SmallConvP
 #pragma unroll
       for (int i = 0; i < MTW; ++i)
 #pragma unroll
-        for (int j = 0; j < NTL; ++j) mma16816(acc[i][j], a[i], bq[j][2 * kk], bq[j][2 * kk + 1]);
+        for (int j = 0; j < NTL; ++j) mma_h16<F16>(acc[i][j], a[i], bq[j][2 * kk], bq[j][2 * kk + 1]);
     }
   };
   for (int pr = wk; pr < pairs;) {                           // weights three (tap, chunk) pairs ahead of the MMAs
@@ -212,18 +212,18 @@ __global__ void __launch_bounds__(256, 2) conv_mma_small_kernel(const SmallConvP
     }
     s0 += co < p.cout ? p.bias[co] : 0.f;
     s1 += co + 1 < p.cout ? p.bias[co + 1] : 0.f;
-    const __nv_bfloat162 hv = __floats2bfloat162_rn(fmaxf(s0, s0 * p.slope), fmaxf(s1, s1 * p.slope));
-    *reinterpret_cast<__nv_bfloat162*>(dst + ((long)oy * p.Wo + ox) * dpitch + co) = hv;
+    *reinterpret_cast<uint32_t*>(dst + ((long)oy * p.Wo + ox) * dpitch + co) =
+        pack2_h16(fmaxf(s0, s0 * p.slope), fmaxf(s1, s1 * p.slope), F16 ? 1 : 0);
   }
   if (p.S > 1) cluster.sync();                               // nobody leaves while its partial tile is still being read
 }
 
-template <int MTW, int NTL>
+template <int MTW, int NTL, bool F16>
 static int launch_small(const SmallConvParams& p, int grid, int threads, int smem, cudaStream_t s) {
   static int attr_dev = -1;
   int dev = 0; cudaGetDevice(&dev);
   if (attr_dev != dev) {
-    cudaError_t e = cudaFuncSetAttribute(conv_mma_small_kernel<MTW, NTL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_mma_small_kernel<MTW, NTL, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
     attr_dev = dev;
   }
@@ -235,7 +235,7 @@ static int launch_small(const SmallConvParams& p, int grid, int threads, int sme
   at[1].id = cudaLaunchAttributeClusterDimension;
   at[1].val.clusterDim.x = p.S; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 2;
-  return (int)cudaLaunchKernelEx(&cfg, conv_mma_small_kernel<MTW, NTL>, p);
+  return (int)cudaLaunchKernelEx(&cfg, conv_mma_small_kernel<MTW, NTL, F16>, p);
 }
 
 }  // namespace pwc
@@ -292,6 +292,7 @@ extern "C" int pwc_conv3x3_mma_fwd(const void* in, long in_pitch, int in_coff,
   const long grid = (long)N * p.tiles_y * p.tiles_x * p.q * S;
   if (grid > 0x7fffffffL) return (int)cudaErrorInvalidValue;
   cudaStream_t s = (cudaStream_t)stream;
-  if (mtw == 2) return launch_small<2, 2>(p, (int)grid, 256, smem, s);
-  return launch_small<4, 2>(p, (int)grid, 256, smem, s);
+  if (half_format()) return mtw == 2 ? launch_small<2, 2, true>(p, (int)grid, 256, smem, s) : launch_small<4, 2, true>(p, (int)grid, 256, smem, s);
+  if (mtw == 2) return launch_small<2, 2, false>(p, (int)grid, 256, smem, s);
+  return launch_small<4, 2, false>(p, (int)grid, 256, smem, s);
 }

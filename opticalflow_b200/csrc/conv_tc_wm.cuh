@@ -302,7 +302,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           if ((p.out_f32 & 3) == 2 && co2 >= 2) {
             const int k = co2 - 2, j = k & 1, b = (k >> 1) & 1, aa = k >> 2;
             const long up = (((long)n * 2 * p.H + 2 * oy + aa) * (2 * p.W) + 2 * ox + b) * p.out2_pitch + p.out2_coff + j;
-            reinterpret_cast<__nv_bfloat16*>(p.out2)[up] = __float2bfloat16_rn(val);
+            reinterpret_cast<uint16_t*>(p.out2)[up] = pack1_h16(val, p.fp16);
           } else {
             if (p.residual) val += p.residual[pix * p.res_pitch + co2];
             reinterpret_cast<float*>(p.out)[pix * p.out_pitch + p.out_coff + co2] = val;
@@ -473,8 +473,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
                 // fused upfeat (ConvTranspose 4x4 s2 as 4 phase 3x3 convs): channel 2 + 2*(2a+b) + j -> pixel (2y+a, 2x+b)
                 const int k = co - 2, j = k & 1, b = (k >> 1) & 1, a = k >> 2;
                 const long up = (((long)n * 2 * p.H + 2 * oy + a) * (2 * p.W) + 2 * ox + b) * p.out2_pitch + p.out2_coff + j;
-                __nv_bfloat16 hv = __float2bfloat16_rn(val);
-                reinterpret_cast<__nv_bfloat16*>(p.out2)[up] = hv;
+                reinterpret_cast<uint16_t*>(p.out2)[up] = pack1_h16(val, p.fp16);
               } else if (p.out_f32) {
                 if (p.residual) val += p.residual[pix * p.res_pitch + co];
                 reinterpret_cast<float*>(p.out)[pix * p.out_pitch + p.out_coff + co] = val;

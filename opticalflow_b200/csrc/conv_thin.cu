@@ -49,7 +49,7 @@ __device__ __forceinline__ void thin_cp16(uint32_t dst, const void* src, bool ok
 }
 
 // NT = output-channel n-tiles (Cout = 8 NT), KS = 16-channel k steps per tap (Cin = 16 KS)
-template <int NT, int KS>
+template <int NT, int KS, bool F16>
 __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) {
   extern __shared__ __align__(128) uint8_t thin_smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -159,8 +159,8 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
           for (int j = 0; j < NT; j += 2) {
             uint32_t b[4];
             thin_ldsm4(b, bt + (uint32_t)(j * 8 * p.wp) + ks * 32);
-            thin_mma(acc[0][j], a[0], b[0], b[1]); thin_mma(acc[0][j + 1], a[0], b[2], b[3]);
-            thin_mma(acc[1][j], a[1], b[0], b[1]); thin_mma(acc[1][j + 1], a[1], b[2], b[3]);
+            mma_h16<F16>(acc[0][j], a[0], b[0], b[1]); mma_h16<F16>(acc[0][j + 1], a[0], b[2], b[3]);
+            mma_h16<F16>(acc[1][j], a[1], b[0], b[1]); mma_h16<F16>(acc[1][j + 1], a[1], b[2], b[3]);
           }
         }
       }
@@ -196,8 +196,8 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             const float v0 = acc[m][j][2 * h] + bias2[j][0], v1 = acc[m][j][2 * h + 1] + bias2[j][1];
-            const __nv_bfloat162 hv = __floats2bfloat162_rn(fmaxf(v0, v0 * p.slope), fmaxf(v1, v1 * p.slope));
-            *reinterpret_cast<__nv_bfloat162*>(ostg + ((lane >> 2) + 8 * h) * OP + j * 16 + 4 * (lane & 3)) = hv;
+            *reinterpret_cast<uint32_t*>(ostg + ((lane >> 2) + 8 * h) * OP + j * 16 + 4 * (lane & 3)) =
+                pack2_h16(fmaxf(v0, v0 * p.slope), fmaxf(v1, v1 * p.slope), F16 ? 1 : 0);
           }
         __syncwarp();
         const int ox0 = (tx * p.mp + pr) * 32 + m * 16;
@@ -217,12 +217,12 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
   }
 }
 
-template <int NT, int KS>
+template <int NT, int KS, bool F16>
 static int launch_thin(ThinConvParams& p, cudaStream_t s) {
   static int attr_dev = -1, num_sms = 0, max_ctas = 1;
   int dev = 0; cudaGetDevice(&dev);
   if (attr_dev != dev) {
-    cudaError_t e = cudaFuncSetAttribute(conv_thin_kernel<NT, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_thin_kernel<NT, KS, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     if (num_sms <= 0) num_sms = 148;
@@ -245,11 +245,11 @@ static int launch_thin(ThinConvParams& p, cudaStream_t s) {
   const long nt = (long)p.N * p.tiles_x * p.tiles_y;
   if (nt > 0x7fffffffL) return (int)cudaErrorInvalidValue;
   p.ntiles = (int)nt;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_ctas, conv_thin_kernel<NT, KS>, 256, smem) != cudaSuccess || max_ctas < 1)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_ctas, conv_thin_kernel<NT, KS, F16>, 256, smem) != cudaSuccess || max_ctas < 1)
     max_ctas = 1;
   const long slots = (long)num_sms * max_ctas;
   const int grid = (int)(p.ntiles < slots ? p.ntiles : slots);
-  return (int)launch_pdl(conv_thin_kernel<NT, KS>, dim3(grid), dim3(256), smem, s, p);
+  return (int)launch_pdl(conv_thin_kernel<NT, KS, F16>, dim3(grid), dim3(256), smem, s, p);
 }
 
 }  // namespace pwc
@@ -271,26 +271,27 @@ __device__ __forceinline__ void c16_ldsm4(uint32_t (&r)[4], uint32_t addr) {
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr), "n"(OFF));
 }
 // two m-tiles (MT, MT + 1) per call: four independent accumulator chains hide the HMMA / ldmatrix latency
-template <int MT, int KY>
+template <int MT, int KY, bool F16>
 __device__ __forceinline__ void c16_taps(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
 #pragma unroll
   for (int kx = 0; kx < 3; ++kx) {
     uint32_t a0[4], a1[4];
     c16_ldsm4<(KY * kC16PW + 16 * MT) * 32>(a0, abase[kx]);
     c16_ldsm4<(KY * kC16PW + 16 * MT + 16) * 32>(a1, abase[kx]);
-    thin_mma(acc[0][0], a0, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
-    thin_mma(acc[0][1], a0, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
-    thin_mma(acc[1][0], a1, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
-    thin_mma(acc[1][1], a1, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+    mma_h16<F16>(acc[0][0], a0, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    mma_h16<F16>(acc[0][1], a0, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+    mma_h16<F16>(acc[1][0], a1, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    mma_h16<F16>(acc[1][1], a1, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
   }
 }
-template <int MT>
+template <int MT, bool F16>
 __device__ __forceinline__ void c16_tile(const uint32_t (&abase)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
-  c16_taps<MT, 0>(abase, bw, acc);
-  c16_taps<MT, 1>(abase, bw, acc);
-  c16_taps<MT, 2>(abase, bw, acc);
+  c16_taps<MT, 0, F16>(abase, bw, acc);
+  c16_taps<MT, 1, F16>(abase, bw, acc);
+  c16_taps<MT, 2, F16>(abase, bw, acc);
 }
 
+template <bool F16>
 __global__ void __launch_bounds__(256, 3) conv_c16_kernel(const ThinConvParams p, int n_tiles) {
   __shared__ __align__(128) unsigned char patch[kC16Patch];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -368,8 +369,8 @@ __global__ void __launch_bounds__(256, 3) conv_c16_kernel(const ThinConvParams p
           for (int j = 0; j < 2; ++j)
 #pragma unroll
             for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
-        if (mp == 0) c16_tile<0>(abase, bw, acc);
-        else c16_tile<2>(abase, bw, acc);
+        if (mp == 0) c16_tile<0, F16>(abase, bw, acc);
+        else c16_tile<2, F16>(abase, bw, acc);
 #pragma unroll
         for (int m = 0; m < 2; ++m)
 #pragma unroll
@@ -378,8 +379,8 @@ __global__ void __launch_bounds__(256, 3) conv_c16_kernel(const ThinConvParams p
             for (int h = 0; h < 2; ++h)
               if (ox0 + 32 * mp + 16 * m + g + 8 * h < W) {
                 const float v0 = acc[m][j][2 * h] + bia[j][0], v1 = acc[m][j][2 * h + 1] + bia[j][1];
-                *reinterpret_cast<__nv_bfloat162*>(orow + (32 * mp + 16 * m + 8 * h) * opitch + 8 * j) =
-                    __floats2bfloat162_rn(lrelu(v0, p.slope), lrelu(v1, p.slope));
+                *reinterpret_cast<uint32_t*>(orow + (32 * mp + 16 * m + 8 * h) * opitch + 8 * j) =
+                    pack2_h16(lrelu(v0, p.slope), lrelu(v1, p.slope), F16 ? 1 : 0);
               }
       }
     }
@@ -393,26 +394,27 @@ __global__ void __launch_bounds__(256, 3) conv_c16_kernel(const ThinConvParams p
 // independent of its row, so tap offsets stay immediates).
 constexpr int kC16TPW = 72, kC16TPatch = kC16IH * kC16TPW * 32;
 
-template <int MT, int KY>
+template <int MT, int KY, bool F16>
 __device__ __forceinline__ void c16t_taps(const uint32_t (&ab)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
 #pragma unroll
   for (int kx = 0; kx < 3; ++kx) {
     uint32_t a0[4], a1[4];
     c16_ldsm4<(KY * kC16TPW + 16 * MT) * 32>(a0, ab[kx]);
     c16_ldsm4<(KY * kC16TPW + 16 * MT + 16) * 32>(a1, ab[kx]);
-    thin_mma(acc[0][0], a0, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
-    thin_mma(acc[0][1], a0, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
-    thin_mma(acc[1][0], a1, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
-    thin_mma(acc[1][1], a1, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+    mma_h16<F16>(acc[0][0], a0, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    mma_h16<F16>(acc[0][1], a0, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
+    mma_h16<F16>(acc[1][0], a1, bw[KY * 3 + kx][0][0], bw[KY * 3 + kx][0][1]);
+    mma_h16<F16>(acc[1][1], a1, bw[KY * 3 + kx][1][0], bw[KY * 3 + kx][1][1]);
   }
 }
-template <int MT>
+template <int MT, bool F16>
 __device__ __forceinline__ void c16t_tile(const uint32_t (&ab)[3], const uint32_t (&bw)[9][2][2], float (&acc)[2][2][4]) {
-  c16t_taps<MT, 0>(ab, bw, acc);
-  c16t_taps<MT, 1>(ab, bw, acc);
-  c16t_taps<MT, 2>(ab, bw, acc);
+  c16t_taps<MT, 0, F16>(ab, bw, acc);
+  c16t_taps<MT, 1, F16>(ab, bw, acc);
+  c16t_taps<MT, 2, F16>(ab, bw, acc);
 }
 
+template <bool F16>
 __global__ void __launch_bounds__(256, 3)
 conv_c16_tma_kernel(const __grid_constant__ CUtensorMap tm1, const __grid_constant__ CUtensorMap tm2, const ThinConvParams p,
                     int n_tiles) {
@@ -493,8 +495,8 @@ conv_c16_tma_kernel(const __grid_constant__ CUtensorMap tm1, const __grid_consta
           for (int j = 0; j < 2; ++j)
 #pragma unroll
             for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
-        if (mp == 0) c16t_tile<0>(ab, bw, acc);
-        else c16t_tile<2>(ab, bw, acc);
+        if (mp == 0) c16t_tile<0, F16>(ab, bw, acc);
+        else c16t_tile<2, F16>(ab, bw, acc);
 #pragma unroll
         for (int m = 0; m < 2; ++m)
 #pragma unroll
@@ -503,8 +505,8 @@ conv_c16_tma_kernel(const __grid_constant__ CUtensorMap tm1, const __grid_consta
             for (int h = 0; h < 2; ++h)
               if (ox0 + 32 * mp + 16 * m + g + 8 * h < W) {
                 const float v0 = acc[m][j][2 * h] + bia[j][0], v1 = acc[m][j][2 * h + 1] + bia[j][1];
-                *reinterpret_cast<__nv_bfloat162*>(orow + (32 * mp + 16 * m + 8 * h) * opitch + 8 * j) =
-                    __floats2bfloat162_rn(lrelu(v0, p.slope), lrelu(v1, p.slope));
+                *reinterpret_cast<uint32_t*>(orow + (32 * mp + 16 * m + 8 * h) * opitch + 8 * j) =
+                    pack2_h16(lrelu(v0, p.slope), lrelu(v1, p.slope), F16 ? 1 : 0);
               }
       }
     }
@@ -527,21 +529,26 @@ static int launch_c16_tma(ThinConvParams& p, cudaStream_t s) {
     if (e) return e;
   }
   static const int ctas = []() { const char* e = getenv("PWC_THIN_C16_CTAS"); return e ? atoi(e) : 148 * 3; }();
-  return (int)launch_pdl(conv_c16_tma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, tm1, tm2, p, (int)nt);
+  if (half_format())
+    return (int)launch_pdl(conv_c16_tma_kernel<true>, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, tm1, tm2, p, (int)nt);
+  return (int)launch_pdl(conv_c16_tma_kernel<false>, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, tm1, tm2, p, (int)nt);
 }
 
 static int launch_c16(ThinConvParams& p, cudaStream_t s) {
   p.tiles_x = cdiv(p.W, 64); p.tiles_y = cdiv(p.H, 8);
   const long nt = (long)p.N * p.tiles_x * p.tiles_y;
   static const int ctas = []() { const char* e = getenv("PWC_THIN_C16_CTAS"); return e ? atoi(e) : 148 * 3; }();
-  return (int)launch_pdl(conv_c16_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, p, (int)nt);
+  if (half_format())
+    return (int)launch_pdl(conv_c16_kernel<true>, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, p, (int)nt);
+  return (int)launch_pdl(conv_c16_kernel<false>, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, p, (int)nt);
 }
 
 }  // namespace pwc
 
 static int thin_dispatch(pwc::ThinConvParams& p, int nt8, int ks, cudaStream_t s) {
   using namespace pwc;
-#define PWC_THIN(NTv, KSv) if (nt8 == NTv && ks == KSv) return launch_thin<NTv, KSv>(p, s)
+#define PWC_THIN(NTv, KSv) \
+  if (nt8 == NTv && ks == KSv) return half_format() ? launch_thin<NTv, KSv, true>(p, s) : launch_thin<NTv, KSv, false>(p, s)
   PWC_THIN(2, 1); PWC_THIN(4, 1); PWC_THIN(8, 1);
   PWC_THIN(2, 2); PWC_THIN(4, 2); PWC_THIN(8, 2);
   PWC_THIN(2, 4); PWC_THIN(4, 4); PWC_THIN(8, 4);

@@ -16,7 +16,7 @@ namespace pwc {
 // columns of a row are loaded once for the 4 pixels.
 __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                           const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
-                                                          int B, int H, int W, float slope, int frames) {
+                                                          int B, int H, int W, float slope, int frames, int f16) {
   // frames = 0: x is the driver tensor [B,6,H,W] (image b of half h at planes 6b + 3h), 2B output images (im1 half first);
   // frames = 1: x is a frame stack [B,3,H,W], B output images (shared-pyramid video plan)
   __shared__ __align__(16) float ws[27][16];
@@ -79,10 +79,7 @@ __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __rest
       if (ox0 + p >= Wo) break;
       uint32_t pk[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        __nv_bfloat162 h = __floats2bfloat162_rn(lrelu(acc[p][2 * i], slope), lrelu(acc[p][2 * i + 1], slope));
-        pk[i] = *reinterpret_cast<uint32_t*>(&h);
-      }
+      for (int i = 0; i < 8; ++i) pk[i] = pack2_h16(lrelu(acc[p][2 * i], slope), lrelu(acc[p][2 * i + 1], slope), f16);
       uint4* o = reinterpret_cast<uint4*>(orow + p * 16);
       o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
@@ -147,7 +144,7 @@ __device__ __forceinline__ void c1m_tile(const uint32_t (&pa)[2][4], const uint3
 __global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                          const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
                                                          int B, int H, int W, float slope, int frames, int tiles_x, int tiles_y,
-                                                         int n_tiles) {
+                                                         int n_tiles, int f16) {
   __shared__ __align__(16) float patch[3 * kC1M_IH * kC1M_PW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, c = lane & 3;
@@ -247,8 +244,7 @@ __global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict
           for (int h = 0; h < 2; ++h)
             if (ox0 + 16 * mt + g + 8 * h < Wo) {
               const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
-              *reinterpret_cast<__nv_bfloat162*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) =
-                  __floats2bfloat162_rn(lrelu(v0, slope), lrelu(v1, slope));
+              *reinterpret_cast<uint32_t*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) = pack2_h16(lrelu(v0, slope), lrelu(v1, slope), f16);
             }
       }
     }
@@ -261,7 +257,7 @@ __global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict
 __global__ void __launch_bounds__(256) conv1a_mma_tma_kernel(const __grid_constant__ CUtensorMap tmx, const float* __restrict__ w,
                                                          const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
                                                          int B, int H, int W, float slope, int frames, int tiles_x, int tiles_y,
-                                                         int n_tiles) {
+                                                         int n_tiles, int f16) {
   extern __shared__ __align__(128) unsigned char c1m_smem[];   // two patch buffers of kC1M_BUF bytes | two mbarriers
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, c = lane & 3;
@@ -348,8 +344,7 @@ __global__ void __launch_bounds__(256) conv1a_mma_tma_kernel(const __grid_consta
           for (int h = 0; h < 2; ++h)
             if (ox0 + 16 * mt + g + 8 * h < Wo) {
               const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
-              *reinterpret_cast<__nv_bfloat162*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) =
-                  __floats2bfloat162_rn(lrelu(v0, slope), lrelu(v1, slope));
+              *reinterpret_cast<uint32_t*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) = pack2_h16(lrelu(v0, slope), lrelu(v1, slope), f16);
             }
       }
     }
@@ -391,14 +386,14 @@ static int launch_conv1a(const float* x, const float* w, const float* bias, void
                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
           return (int)cudaErrorInvalidValue;
         return (int)launch_pdl(conv1a_mma_tma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), smem, s, tm, w, bias,
-                               reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt);
+                               reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt, half_format());
       }
       return (int)launch_pdl(conv1a_mma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, x, w, bias,
-                             reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt);
+                             reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt, half_format());
     }
   }
   return (int)launch_pdl(conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, s, x, w, bias, reinterpret_cast<__nv_bfloat16*>(out),
-                         B, H, W, slope, frames);
+                         B, H, W, slope, frames, half_format());
 }
 
 // One warp per output pixel; lanes stride over input channels (4 at a time), 2x2 live taps, shuffle-reduce 2 sums.
@@ -528,7 +523,11 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
 #define PWC_DECONV_S(TI, TO)                                                                                              \
   launch_pdl(deconv4x4s2_c2_small_kernel<TI, TO>, dim3(nb), dim3(256), 0, s, reinterpret_cast<const TI*>(in), in_pitch,    \
              in_coff, w, bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, out_b_pitch, N, Hin, Win, CinP)
+    const bool f16 = half_format() != 0;             // PWC_BF16 = "the 16-bit storage format": IEEE half after pwc_set_half_format(1)
     if (in_dtype == PWC_F32 && out_dtype == PWC_F32) PWC_DECONV_S(float, float);
+    else if (f16 && in_dtype == PWC_F32 && out_dtype == PWC_BF16) PWC_DECONV_S(float, __half);
+    else if (f16 && in_dtype == PWC_BF16 && out_dtype == PWC_BF16) PWC_DECONV_S(__half, __half);
+    else if (f16 && in_dtype == PWC_BF16 && out_dtype == PWC_F32) PWC_DECONV_S(__half, float);
     else if (in_dtype == PWC_F32 && out_dtype == PWC_BF16) PWC_DECONV_S(float, __nv_bfloat16);
     else if (in_dtype == PWC_BF16 && out_dtype == PWC_BF16) PWC_DECONV_S(__nv_bfloat16, __nv_bfloat16);
     else if (in_dtype == PWC_BF16 && out_dtype == PWC_F32) PWC_DECONV_S(__nv_bfloat16, float);
@@ -540,7 +539,11 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
   launch_pdl(deconv4x4s2_c2_any_kernel<TI, TO>, dim3(blocks), dim3(256), 0, s, reinterpret_cast<const TI*>(in), in_pitch, in_coff, CinP, w, \
                                                            bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, \
                                                            out_b_pitch, N, Hin, Win, CinP)
+  const bool f16 = half_format() != 0;
   if (in_dtype == PWC_F32 && out_dtype == PWC_F32) PWC_DECONV(float, float);
+  else if (f16 && in_dtype == PWC_F32 && out_dtype == PWC_BF16) PWC_DECONV(float, __half);
+  else if (f16 && in_dtype == PWC_BF16 && out_dtype == PWC_BF16) PWC_DECONV(__half, __half);
+  else if (f16 && in_dtype == PWC_BF16 && out_dtype == PWC_F32) PWC_DECONV(__half, float);
   else if (in_dtype == PWC_F32 && out_dtype == PWC_BF16) PWC_DECONV(float, __nv_bfloat16);
   else if (in_dtype == PWC_BF16 && out_dtype == PWC_BF16) PWC_DECONV(__nv_bfloat16, __nv_bfloat16);
   else if (in_dtype == PWC_BF16 && out_dtype == PWC_F32) PWC_DECONV(__nv_bfloat16, float);

@@ -48,6 +48,7 @@ struct WarpCorrParams {
   void* out; long out_pitch;
   int B, C, H, W;
   int tiles_x, tiles_y, num_tiles;
+  int f16;                                       // 16-bit features / output are IEEE half (pwc_set_half_format) instead of bf16
 };
 
 // swizzled float4 slot of (pixel index p within its array, 16B-chunk k)
@@ -515,7 +516,7 @@ extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void
   if (md != kMD || B <= 0 || C <= 0 || H <= 0 || W <= 0 || B > 65535 || H > 65535 || W > 65535)
     return (int)cudaErrorInvalidValue;
   WarpCorrParams p{f1, f1_pitch, f2, f2_pitch, flow, flow_pitch, flow_scale, align_corners, mask_thresh, slope,
-                   out, out_pitch, B, C, H, W, 0, 0, 0};
+                   out, out_pitch, B, C, H, W, 0, 0, 0, (dtype == PWC_BF16 && half_format()) ? 1 : 0};
   cudaStream_t s = (cudaStream_t)stream;
   if (layout == PWC_LAYOUT_NCHW) {
     if (dtype != PWC_F32) return (int)cudaErrorInvalidValue;
@@ -542,12 +543,12 @@ extern "C" int pwc_warp_corr_lrelu_fwd(const void* f1, long f1_pitch, const void
     // wide-feature (small) levels 4-6: latency-oriented kernel, one warp per row displacement
     static const int use_small = []() { const char* e = getenv("PWC_CORR_SMALL"); return e ? atoi(e) : 1; }();
     // (each CTA re-gathers the 9 warped rows it needs: only worth it while the grid fits the machine once)
-    const bool small_ok = use_small && C > 64 && C % 4 == 0 && C <= 200 && (long)cdiv(W, 32) * H * B <= 160 && f1_pitch % 4 == 0 && f2_pitch % 4 == 0 &&
+    const bool small_ok = use_small && !p.f16 && C > 64 && C % 4 == 0 && C <= 200 && (long)cdiv(W, 32) * H * B <= 160 && f1_pitch % 4 == 0 && f2_pitch % 4 == 0 &&
                           ((reinterpret_cast<uintptr_t>(f1) | reinterpret_cast<uintptr_t>(f2)) & 7) == 0 &&
                           (reinterpret_cast<uintptr_t>(out) & 15) == 0 && out_pitch % 8 == 0 && slope >= 0.f &&
                           slope <= 1.f && get_encode_tiled() != nullptr;
     if (small_ok) return launch_warp_corr_small(p, s);
-    return dispatch_rows<__nv_bfloat16, false>(p, s);
+    return p.f16 ? dispatch_rows<__half, false>(p, s) : dispatch_rows<__nv_bfloat16, false>(p, s);
   }
   if (dtype != PWC_F32) return (int)cudaErrorInvalidValue;
   // TMA needs a 16-byte aligned base and 16-byte multiples as strides; otherwise the producers load the f1 box themselves

@@ -43,14 +43,15 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
 }
 
 // bilinear blend of four bf16 pairs (one 32-bit word per corner): fp32 FMAs in nw, ne, sw, se order, one rounding
+template <bool F16>
 __device__ __forceinline__ uint32_t blend_pair(const float4& w, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   float lo = 0.f, hi = 0.f;
-  lo = fmaf(w.x, __uint_as_float(a << 16), lo); hi = fmaf(w.x, __uint_as_float(a & 0xffff0000u), hi);
-  lo = fmaf(w.y, __uint_as_float(b << 16), lo); hi = fmaf(w.y, __uint_as_float(b & 0xffff0000u), hi);
-  lo = fmaf(w.z, __uint_as_float(c << 16), lo); hi = fmaf(w.z, __uint_as_float(c & 0xffff0000u), hi);
-  lo = fmaf(w.w, __uint_as_float(d << 16), lo); hi = fmaf(w.w, __uint_as_float(d & 0xffff0000u), hi);
-  const __nv_bfloat162 pr = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<const uint32_t*>(&pr);
+  const float2 fa = unpack2_h16(a, F16), fb = unpack2_h16(b, F16), fc = unpack2_h16(c, F16), fd = unpack2_h16(d, F16);
+  lo = fmaf(w.x, fa.x, lo); hi = fmaf(w.x, fa.y, hi);
+  lo = fmaf(w.y, fb.x, lo); hi = fmaf(w.y, fb.y, hi);
+  lo = fmaf(w.z, fc.x, lo); hi = fmaf(w.z, fc.y, hi);
+  lo = fmaf(w.w, fd.x, lo); hi = fmaf(w.w, fd.y, hi);
+  return pack2_h16(lo, hi, F16);
 }
 
 // 16 bytes (8 channels) at p, or its first `nvalid` channels (4) zero-extended
@@ -60,7 +61,7 @@ __device__ __forceinline__ uint4 ld_cg(const __nv_bfloat16* p, int nvalid) {
   return make_uint4(h.x, h.y, 0u, 0u);
 }
 
-template <int NMI>
+template <int NMI, bool F16>
 __global__ void __launch_bounds__(kMmaThreadsMax, 1)
 warp_corr_mma_kernel(const __grid_constant__ CUtensorMap tmOut, const WarpCorrMmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -186,10 +187,10 @@ warp_corr_mma_kernel(const __grid_constant__ CUtensorMap tmOut, const WarpCorrMm
             if (dstu[u] != 0xffffffffu) {
               const float4 w = tabw[pixu[u]];
               uint4 o;
-              o.x = blend_pair(w, cv[u][0].x, cv[u][1].x, cv[u][2].x, cv[u][3].x);
-              o.y = blend_pair(w, cv[u][0].y, cv[u][1].y, cv[u][2].y, cv[u][3].y);
-              o.z = blend_pair(w, cv[u][0].z, cv[u][1].z, cv[u][2].z, cv[u][3].z);
-              o.w = blend_pair(w, cv[u][0].w, cv[u][1].w, cv[u][2].w, cv[u][3].w);
+              o.x = blend_pair<F16>(w, cv[u][0].x, cv[u][1].x, cv[u][2].x, cv[u][3].x);
+              o.y = blend_pair<F16>(w, cv[u][0].y, cv[u][1].y, cv[u][2].y, cv[u][3].y);
+              o.z = blend_pair<F16>(w, cv[u][0].z, cv[u][1].z, cv[u][2].z, cv[u][3].z);
+              o.w = blend_pair<F16>(w, cv[u][0].w, cv[u][1].w, cv[u][2].w, cv[u][3].w);
               *reinterpret_cast<uint4*>(ring + dstu[u]) = o;
             }
           }
@@ -230,7 +231,7 @@ warp_corr_mma_kernel(const __grid_constant__ CUtensorMap tmOut, const WarpCorrMm
 #pragma unroll
           for (int mi = 0; mi < NMI; ++mi)
 #pragma unroll
-            for (int tt = 0; tt < 3; ++tt) mma_bf16_16816(acc[mi][tt], a[mi], b[2 * mi + tt][0], b[2 * mi + tt][1]);
+            for (int tt = 0; tt < 3; ++tt) mma_h16<F16>(acc[mi][tt], a[mi], b[2 * mi + tt][0], b[2 * mi + tt][1]);
         }
         // accumulator (mi, tt, e): row = 16 mi + lane/4 + 8 (e>>1), column = 8 (2 mi + tt) + 2 (lane%4) + (e&1);
         // j = column - row = 8 (tt - (e>>1)) + (e&1) + cr is the x displacement index when 0 <= j <= 8: per thread the
@@ -246,10 +247,10 @@ warp_corr_mma_kernel(const __grid_constant__ CUtensorMap tmOut, const WarpCorrMm
                 const int d8 = tt - (e >> 1);                         // compile time: only 0 and 1 can hold band elements
                 if (d8 < 0 || d8 > 1) continue;
                 const float q = acc[mi][tt][e] * rc;
-                const __nv_bfloat16 hv = __float2bfloat16_rn(fmaxf(q, q * g.slope));
+                const uint16_t hv = pack1_h16(fmaxf(q, q * g.slope), F16);
                 const bool on = d8 == 0 ? (cr >= -(e & 1)) : (cr <= -(e & 1));
                 if (on) asm volatile("st.shared.b16 [%0], %1;" :: "r"(sbase + (uint32_t)(((16 * mi + 8 * (e >> 1)) * 80 + 8 * d8 + (e & 1)) * 2)),
-                                     "h"(*reinterpret_cast<const uint16_t*>(&hv)) : "memory");
+                                     "h"(hv) : "memory");
               }
         } else {                                                      // dy = 8: its j = 8 is channel 80 -> side array
 #pragma unroll
@@ -263,10 +264,10 @@ warp_corr_mma_kernel(const __grid_constant__ CUtensorMap tmOut, const WarpCorrMm
                 const int j = 8 * d8 + (e & 1) + cr;
                 if ((unsigned)j <= 8u) {
                   const float q = acc[mi][tt][e] * rc;
-                  const __nv_bfloat16 hv = __float2bfloat16_rn(fmaxf(q, q * g.slope));
+                  const uint16_t hv = pack1_h16(fmaxf(q, q * g.slope), F16);
                   const int px = r * XS + 16 * mi + 8 * (e >> 1) + (lane >> 2);
-                  if (j < 8) stg[px * 80 + 72 + j] = *reinterpret_cast<const uint16_t*>(&hv);
-                  else c80[px] = *reinterpret_cast<const uint16_t*>(&hv);
+                  if (j < 8) stg[px * 80 + 72 + j] = hv;
+                  else c80[px] = hv;
                 }
               }
         }
@@ -290,9 +291,11 @@ static int launch_warp_corr_mma(const WarpCorrParams& g, cudaStream_t s) {
   static int attr_dev = -1, num_sms = 0;
   int dev = 0; cudaGetDevice(&dev);
   if (attr_dev != dev) {
-    cudaError_t e = cudaFuncSetAttribute(warp_corr_mma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(warp_corr_mma_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(warp_corr_mma_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(warp_corr_mma_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(warp_corr_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    e = cudaFuncSetAttribute(warp_corr_mma_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     if (num_sms <= 0) num_sms = 148;
@@ -338,8 +341,12 @@ static int launch_warp_corr_mma(const WarpCorrParams& g, cudaStream_t s) {
                          80, XS, 1, 1, 1, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (e) return e;
   const int grid = (int)(p.num_items < slots ? p.num_items : slots);
-  if (nmi == 1) return (int)launch_pdl(warp_corr_mma_kernel<1>, dim3(grid), dim3(threads), smem, s, tmo, p);
-  return (int)launch_pdl(warp_corr_mma_kernel<2>, dim3(grid), dim3(threads), smem, s, tmo, p);
+  if (g.f16) {
+    if (nmi == 1) return (int)launch_pdl(warp_corr_mma_kernel<1, true>, dim3(grid), dim3(threads), smem, s, tmo, p);
+    return (int)launch_pdl(warp_corr_mma_kernel<2, true>, dim3(grid), dim3(threads), smem, s, tmo, p);
+  }
+  if (nmi == 1) return (int)launch_pdl(warp_corr_mma_kernel<1, false>, dim3(grid), dim3(threads), smem, s, tmo, p);
+  return (int)launch_pdl(warp_corr_mma_kernel<2, false>, dim3(grid), dim3(threads), smem, s, tmo, p);
 }
 
 }  // namespace pwc

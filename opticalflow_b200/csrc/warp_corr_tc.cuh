@@ -63,6 +63,7 @@ __device__ __forceinline__ void tc_decode(const WarpCorrTcParams& p, int item, i
   T = q + (rg < rem ? 1 : 0);
 }
 
+template <bool F16>
 __global__ void __launch_bounds__(kTcThreads, 1)
 warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant__ CUtensorMap tmOut,
                     const WarpCorrTcParams p) {
@@ -124,7 +125,7 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
     }
   } else if (warp == 1) {
     // ============================== MMA issuer ==============================
-    const uint32_t idesc = ptx::make_idesc_bf16(128, kTcNP);
+    const uint32_t idesc = F16 ? (ptx::make_idesc_bf16(128, kTcNP) & ~((7u << 7) | (7u << 10))) : ptx::make_idesc_bf16(128, kTcNP);
     int as = 0; uint32_t aph = 0;
     int db = 0; uint32_t dph = 0;
     int gcount = 0, waited = -1;           // global group counter / highest group whose b_full has been observed
@@ -254,18 +255,14 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
             if (k < nchunk) {
               uint32_t w[4];
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const __nv_bfloat162 pr = __floats2bfloat162_rn(pend[8 * k + 2 * e], pend[8 * k + 2 * e + 1]);
-                w[e] = *reinterpret_cast<const uint32_t*>(&pr);
-              }
+              for (int e = 0; e < 4; ++e) w[e] = pack2_h16(pend[8 * k + 2 * e], pend[8 * k + 2 * e + 1], F16);
               *reinterpret_cast<uint4*>(srow + (chunk0 + k) * 8) = make_uint4(w[0], w[1], w[2], w[3]);
             }
           }
 #pragma unroll
           for (int i = 0; i < 6; ++i) if (8 * nchunk + i < npend) carry[i] = pend[8 * nchunk + i];
           if (ps == 2) {                                  // channel 80 goes out from the register
-            const __nv_bfloat16 hv = __float2bfloat16_rn(pend[32]);
-            ch80 = *reinterpret_cast<const uint16_t*>(&hv);
+            ch80 = pack1_h16(pend[32], F16);
           }
           if (++db == 2) { db = 0; dph ^= 1; }
         }
@@ -369,12 +366,13 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
               for (int e = 0; e < 4; ++e) {
                 // bf16 pair -> two fp32 (low half = even channel); same FMA order as the fp32 kernel's gather
                 float lo = 0.f, hi = 0.f;
-                lo = fmaf(w.x, __uint_as_float(a[e] << 16), lo); hi = fmaf(w.x, __uint_as_float(a[e] & 0xffff0000u), hi);
-                lo = fmaf(w.y, __uint_as_float(b[e] << 16), lo); hi = fmaf(w.y, __uint_as_float(b[e] & 0xffff0000u), hi);
-                lo = fmaf(w.z, __uint_as_float(c[e] << 16), lo); hi = fmaf(w.z, __uint_as_float(c[e] & 0xffff0000u), hi);
-                lo = fmaf(w.w, __uint_as_float(d[e] << 16), lo); hi = fmaf(w.w, __uint_as_float(d[e] & 0xffff0000u), hi);
-                const __nv_bfloat162 pr = __floats2bfloat162_rn(lo, hi);
-                o[e] = *reinterpret_cast<const uint32_t*>(&pr);
+                const float2 fa = unpack2_h16(a[e], F16), fb = unpack2_h16(b[e], F16), fc2 = unpack2_h16(c[e], F16),
+                             fd = unpack2_h16(d[e], F16);
+                lo = fmaf(w.x, fa.x, lo); hi = fmaf(w.x, fa.y, hi);
+                lo = fmaf(w.y, fb.x, lo); hi = fmaf(w.y, fb.y, hi);
+                lo = fmaf(w.z, fc2.x, lo); hi = fmaf(w.z, fc2.y, hi);
+                lo = fmaf(w.w, fd.x, lo); hi = fmaf(w.w, fd.y, hi);
+                o[e] = pack2_h16(lo, hi, F16);
               }
               const int i = pix / kTcBW, qx = pix - i * kTcBW;
               const uint32_t off = (uint32_t)((slot * 4 + i) * kTcRowBytes + qx * 128 + ((cg ^ (qx & 7)) << 4));
@@ -401,7 +399,8 @@ static int launch_warp_corr_tc(const WarpCorrParams& g, cudaStream_t s) {
   static int attr_dev = -1, num_sms = 0;
   int dev = 0; cudaGetDevice(&dev);
   if (attr_dev != dev) {
-    cudaError_t e = cudaFuncSetAttribute(warp_corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(warp_corr_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(warp_corr_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemBytes);
     if (e != cudaSuccess) return (int)e;
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     if (num_sms <= 0) num_sms = 148;
@@ -431,7 +430,8 @@ static int launch_warp_corr_tc(const WarpCorrParams& g, cudaStream_t s) {
                      80, 32, 1, 1, 1, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (e) return e;
   const int grid = p.num_items < num_sms ? p.num_items : num_sms;
-  return (int)launch_pdl(warp_corr_tc_kernel, dim3(grid), dim3(kTcThreads), kTcSmemBytes, s, tm, tmo, p);
+  if (g.f16) return (int)launch_pdl(warp_corr_tc_kernel<true>, dim3(grid), dim3(kTcThreads), kTcSmemBytes, s, tm, tmo, p);
+  return (int)launch_pdl(warp_corr_tc_kernel<false>, dim3(grid), dim3(kTcThreads), kTcSmemBytes, s, tm, tmo, p);
 }
 
 }  // namespace pwc

@@ -234,7 +234,7 @@ class VideoFlowPipeline:
     of the 24 bytes/pixel of the fp32 [1,6,H,W] tensor the reference uploads.  Three streams as in FlowPipeline."""
 
     def __init__(self, model, B, H, W, device, swap_rb=True, mult=20.0, full_res=False, depth=2, share_pyramid=None):
-        """share_pyramid (default: on for conv_mode='bf16'): frame t is image 2 of pair t-1 and image 1 of pair t, so the plan
+        """share_pyramid (default: on for the 16-bit conv modes): frame t is image 2 of pair t-1 and image 1 of pair t, so the plan
         runs the feature pyramid once per frame (B+1 images per batch instead of 2B) and the cost volumes read frame t+1's
         features in place (engine_bf16.PlanBF16(video=True))."""
         from . import prepost
@@ -249,7 +249,7 @@ class VideoFlowPipeline:
         # the reference cuts the image-pixel pads from the quarter-resolution flow (unpad quirk, see prepost.unpad)
         self.oh, self.ow = (H, W) if full_res else (Hp // 4 - self.ph, Wp // 4 - self.pw)
         with torch.cuda.device(device):
-            self.share = (getattr(model, "conv_mode", "") == "bf16") if share_pyramid is None else bool(share_pyramid)
+            self.share = (getattr(model, "conv_mode", "") != "fp32") if share_pyramid is None else bool(share_pyramid)
             self.plan = model._plan(B, Hp, Wp, device, video=True) if self.share else model._plan(B, Hp, Wp, device)
             self.plan.pack_weights(model)
             self.s_in, self.s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)

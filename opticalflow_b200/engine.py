@@ -52,7 +52,7 @@ def chan_map(lvl, start):
     return list(range(dense)) + [dense + t for t in tail_map(lvl)]
 
 
-CONV_MODES = ("fp32", "bf16")
+CONV_MODES = ("fp32", "bf16", "f16")
 
 
 def weights_key(model):
@@ -272,9 +272,9 @@ class Plan:
 def make_plan(model, B, H, W, device, conv_mode="fp32", align_corners=False, video=False):
     if conv_mode == "fp32":
         if video:
-            raise ValueError("the shared-pyramid video plan exists for conv_mode='bf16' only")
+            raise ValueError("the shared-pyramid video plan exists for the 16-bit conv modes only")
         return Plan(model, B, H, W, device, align_corners)
-    if conv_mode == "bf16":
+    if conv_mode in ("bf16", "f16"):
         from .engine_bf16 import PlanBF16
-        return PlanBF16(model, B, H, W, device, align_corners, video=video)
-    raise ValueError(f"unknown conv_mode {conv_mode!r} (expected 'fp32' or 'bf16')")
+        return PlanBF16(model, B, H, W, device, align_corners, video=video, half=conv_mode)
+    raise ValueError(f"unknown conv_mode {conv_mode!r} (expected one of {CONV_MODES})")

@@ -116,8 +116,10 @@ class _TcLayer:
 
 
 class PlanBF16:
-    def __init__(self, model, B, H, W, device, align_corners=False, use_graph=True, video=False):
-        """video=True: the B pairs are CONSECUTIVE frames (t, t+1) of one stream: the input is B+1 frames [B+1,3,H,W], the
+    def __init__(self, model, B, H, W, device, align_corners=False, use_graph=True, video=False, half="bf16"):
+        """half: the 16-bit storage format of activations and weights, 'bf16' (conv_mode 'bf16') or 'f16' (conv_mode 'f16':
+        IEEE half, 3 more mantissa bits; same kernels -- tcgen05 kind::f16 and mma.sync take either -- same speed).
+        video=True: the B pairs are CONSECUTIVE frames (t, t+1) of one stream: the input is B+1 frames [B+1,3,H,W], the
         feature pyramid runs ONCE per frame (B+1 images instead of 2B) and pair k reads frame k+1's features in place --
         image k+1 of the same concat buffer -- as its image-2 features."""
         if H % 64 or W % 64:
@@ -126,7 +128,11 @@ class PlanBF16:
         self.B, self.H, self.W, self.device = B, H, W, device
         self.align_corners = int(bool(align_corners))
         self.use_graph = use_graph
-        zb = lambda *s: torch.zeros(*s, device=device, dtype=BF)            # noqa: E731
+        if half not in ("bf16", "f16"):
+            raise ValueError("half must be 'bf16' or 'f16'")
+        self.half_fmt = 1 if half == "f16" else 0
+        self.hdt = torch.float16 if half == "f16" else BF
+        zb = lambda *s: torch.zeros(*s, device=device, dtype=self.hdt)      # noqa: E731
         zf = lambda *s: torch.zeros(*s, device=device, dtype=torch.float32)  # noqa: E731
         self.video = bool(video)
         NP = self.NP = (B + 1) if video else 2 * B            # images through the pyramid
@@ -157,6 +163,22 @@ class PlanBF16:
         self.graph_tail = None     # ops[1:] as a graph, for run_from()
         self.launches = 0
 
+    class _Fmt:
+        """Selects this plan's 16-bit storage format for the library calls made inside the block (pwc_set_half_format is
+        thread-local and read at create / launch time) and restores bf16, the library default, afterwards."""
+
+        def __init__(self, plan):
+            self.plan = plan
+
+        def __enter__(self):
+            if self.plan.half_fmt:
+                _lib.check(self.plan.lib.pwc_set_half_format(self.plan.half_fmt), "pwc_set_half_format")
+
+        def __exit__(self, *exc):
+            if self.plan.half_fmt:
+                self.plan.lib.pwc_set_half_format(0)
+            return False
+
     def __del__(self):
         try:
             for L in self.layers.values():
@@ -186,7 +208,7 @@ class PlanBF16:
         L.kc = pick_kc(span, stride, dil, src2 is not None, W=win, coutp=L.coutp, out_f32=bool(out_f32) or dst2 is not None)
         L.wrows = 128 if ts else cout                   # rows of the weight tensor handed to the packer
         dev = self.device
-        L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp, device=dev, dtype=BF)
+        L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp, device=dev, dtype=self.hdt)
         L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
         h = ctypes.c_void_p()
         e = self.lib.pwc_tc_conv_create(
@@ -213,7 +235,7 @@ class PlanBF16:
         L.kkskip, L.groups, L.handle, L.wfn, L.cmap = False, None, None, None, None
         L.key, L.cin, L.cout, L.span, L.coutp, L.kc, L.wrows = key, cin, cout, cin, cout, cin, cout
         dev = self.device
-        L.w = torch.zeros(9 * cin * cout, device=dev, dtype=BF)
+        L.w = torch.zeros(9 * cin * cout, device=dev, dtype=self.hdt)
         L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
         self.layers[key] = L
         lib = self.lib
@@ -234,7 +256,7 @@ class PlanBF16:
         L.wfn, L.key, L.cin, L.cout, L.span, L.cmap = wfn, key, cin, cout, span, cmap
         L.coutp, L.kc, L.wrows = _roundup(cout, 16), 64, cout
         dev = self.device
-        L.w = torch.zeros(9 * _roundup(span, 64) * L.coutp, device=dev, dtype=BF)
+        L.w = torch.zeros(9 * _roundup(span, 64) * L.coutp, device=dev, dtype=self.hdt)
         L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
         self.layers[key] = L
         lib = self.lib
@@ -254,8 +276,8 @@ class PlanBF16:
         b = torch.zeros(2, device=dev, dtype=torch.float32)
         self.small[key] = (w, b, cin, cinp)
         lib, B = self.lib, self.B
-        idt = _lib.BF16 if src.dtype == BF else _lib.F32
-        odt = _lib.BF16 if dst.dtype == BF else _lib.F32
+        idt = _lib.BF16 if src.dtype in (BF, torch.float16) else _lib.F32      # BF16 = "the 16-bit storage format"
+        odt = _lib.BF16 if dst.dtype in (BF, torch.float16) else _lib.F32
         args = (_lib.ptr(src), idt, src.shape[-1], src_coff, span, _lib.ptr(w), _lib.ptr(b), _lib.ptr(dst), odt,
                 dst.shape[-1], dst_coff, _lib.ptr(dst_b), (dst_b.shape[-1] if dst_b is not None else 0), B, hin, win)
         self.op_info.append((key, 2.0 * B * hin * win * 4 * 2 * cin * 4))
@@ -385,7 +407,7 @@ class PlanBF16:
                 wt[:2] = sd["dc_conv7.weight"]
                 return wt, sd["dc_conv7.bias"]
             L.wfn = pad16
-            L.w = torch.zeros(9 * 32 * 16, device=dev, dtype=BF)
+            L.w = torch.zeros(9 * 32 * 16, device=dev, dtype=self.hdt)
             L.b = torch.zeros(2, device=dev, dtype=torch.float32)
             self.layers["dc_conv7"] = L
             ha = (_lib.ptr(src), src.shape[-1], 0, 32, _lib.ptr(L.w), _lib.ptr(L.b), _lib.ptr(self.flow[2]), self.flow[2].shape[-1],
@@ -406,7 +428,12 @@ class PlanBF16:
         if ver == self.weights_version:
             return
         if not self.ops:
-            self._build()
+            with self._Fmt(self):
+                self._build()
+        with self._Fmt(self):
+            self._pack_weights(model, ver)
+
+    def _pack_weights(self, model, ver):
         lib, dev = self.lib, self.device
         st = _lib.stream_handle()
         sd = {k: v.detach().to(device=dev, dtype=torch.float32).contiguous() for k, v in model.state_dict().items()}
@@ -468,8 +495,9 @@ class PlanBF16:
     # ------------------------------------------------------------------ forward
     def _launch_all(self):
         st = _lib.stream_handle()
-        for op in self.ops:
-            op(st)
+        with self._Fmt(self):
+            for op in self.ops:
+                op(st)
 
     def run(self, x=None, all_levels=False):
         """x: [B,6,H,W] fp32 (device, or pinned host: it is copied into the plan's static input).  Returns flow2
@@ -506,12 +534,13 @@ class PlanBF16:
             self._launch_all()
             torch.cuda.current_stream().synchronize()
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g), self._Fmt(self):
                 st = _lib.stream_handle()
                 for op in self.ops[1:]:
                     op(st)
             self.graph_tail = g
-        self._conv1a_on(x, _lib.stream_handle())
+        with self._Fmt(self):
+            self._conv1a_on(x, _lib.stream_handle())
         if release is not None:
             release.record(torch.cuda.current_stream())
         self.graph_tail.replay()
@@ -529,7 +558,7 @@ class PlanBF16:
         side = torch.cuda.Stream(self.device)
         for (name, fl), op in zip(self.op_info, self.ops):
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.stream(side):
+            with torch.cuda.stream(side), self._Fmt(self):
                 op(_lib.stream_handle())
                 side.synchronize()
                 with torch.cuda.graph(g, stream=side):

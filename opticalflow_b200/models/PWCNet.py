@@ -34,8 +34,9 @@ def deconv(in_planes, out_planes, kernel_size=4, stride=2, padding=1):
 class PWCDCNet(nn.Module):
     """PWC-DC net (dilated context network + DenseNet connections), B200 execution.
 
-    Extra keyword arguments (not in the reference): ``conv_mode`` 'fp32' (exact-fp32 CUDA-core convolutions) or
-    'bf16' (tcgen05 tensor-core convolutions, fp32 accumulate); ``align_corners`` False reproduces the reference as
+    Extra keyword arguments (not in the reference): ``conv_mode`` 'fp32' (exact-fp32 CUDA-core convolutions),
+    'bf16' (tcgen05 tensor-core convolutions, bf16 storage, fp32 accumulate) or 'f16' (the same kernels with IEEE-half
+    storage: ~7x closer to the fp32 flow at the same speed); ``align_corners`` False reproduces the reference as
     it runs under torch>=1.3, True the 2018 semantics.
     """
 

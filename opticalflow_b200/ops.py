@@ -4,6 +4,25 @@ import torch
 from . import _lib
 
 
+class half_format:
+    """``with ops.half_format('f16'):`` -- the 16-bit tensors handed to the wrappers below are IEEE half instead of bf16
+    (pwc_set_half_format: thread-local, read by the library at create / launch time)."""
+
+    def __init__(self, fmt):
+        self.fmt = {"bf16": 0, "f16": 1}[fmt]
+
+    def __enter__(self):
+        _lib.check(_lib.load().pwc_set_half_format(self.fmt), "pwc_set_half_format")
+
+    def __exit__(self, *exc):
+        _lib.load().pwc_set_half_format(0)
+        return False
+
+
+def _h16(lib):
+    return torch.float16 if lib.pwc_get_half_format() else torch.bfloat16
+
+
 def warp_corr_lrelu(f1, f2, flow=None, flow_scale=1.0, align_corners=False, mask_thresh=0.9999, slope=0.1,
                     layout="nchw", out=None):
     """Fused warp + mask + 81-channel cost volume + LeakyReLU (pwc_warp_corr_lrelu_fwd).
@@ -28,7 +47,9 @@ def warp_corr_lrelu(f1, f2, flow=None, flow_scale=1.0, align_corners=False, mask
     else:
         B, H, W, C = f1.shape
         assert f1.stride(3) == 1 and f2.stride(3) == 1
-        dt = _lib.BF16 if f1.dtype == torch.bfloat16 else _lib.F32
+        dt = _lib.F32 if f1.dtype == torch.float32 else _lib.BF16
+        if dt == _lib.BF16 and f1.dtype != _h16(lib):
+            raise RuntimeError(f"warp_corr_lrelu: {f1.dtype} features while the library's 16-bit format is {_h16(lib)}")
         flow = None if flow is None else flow.contiguous().float()
         if out is None:
             out = torch.empty(B, H, W, 81, device=f1.device, dtype=f1.dtype)
@@ -131,12 +152,12 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     lib = _lib.load()
     st = _lib.stream_handle()
     N, H, W, pitch = x.shape
-    assert x.dtype == torch.bfloat16
+    assert x.dtype == _h16(lib)
     cout, cin = weight.shape[:2]
     span = cin_span if cin_span is not None else (cin + 15) // 16 * 16
     coutp = 128 if ts else (cout + 15) // 16 * 16
     kc = pick_kc(span, stride, dil, W=W, coutp=coutp, out_f32=bool(out_f32))
-    wp = torch.empty(9 * ((span + kc - 1) // kc) * kc * coutp, device=x.device, dtype=torch.bfloat16)
+    wp = torch.empty(9 * ((span + kc - 1) // kc) * kc * coutp, device=x.device, dtype=x.dtype)
     mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
     w32 = weight.detach().float().contiguous()
     wrows = cout
@@ -150,7 +171,7 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     if out is None:
         out = torch.zeros(N, ho, wo, coutp if not out_f32 else cout, device=x.device,
-                          dtype=torch.float32 if out_f32 else torch.bfloat16)
+                          dtype=torch.float32 if out_f32 else x.dtype)
     b32 = bias.detach().float().contiguous()
     h = ctypes.c_void_p()
     e = lib.pwc_tc_conv_create(ctypes.byref(h), _lib.ptr(x), pitch, in_coff, None, 0, 0, N, span, kc,

@@ -275,7 +275,7 @@ _BF16_SIM = [False]   # forward(..., bf16_storage=True): model the bf16-conv mod
 
 
 def _q(t):
-    return t.bfloat16().float() if _BF16_SIM[0] else t
+    return t.to(_BF16_SIM[0]).float() if _BF16_SIM[0] else t
 
 
 def _conv(sd, name, x, stride=1, pad=1, dil=1, act=True):
@@ -292,12 +292,13 @@ def _deconv(sd, name, x):
 
 
 @torch.no_grad()
-def forward(sd, x, align_corners=False, return_intermediates=False, bf16_storage=False):
+def forward(sd, x, align_corners=False, return_intermediates=False, bf16_storage=False, storage=None):
     """PWCDCNet.forward in eval mode (PWCNet.py:180-273).  x: [B,6,H,W] fp32, H,W multiples of 64.
     Returns flow2 [B,2,H/4,W/4] (units of px/20, PWCNet.py:272-273); optionally a dict of per-level tensors.
     bf16_storage=True rounds weights and stored activations to bf16 where the bf16-conv mode of the CUDA path does
-    (fp32 arithmetic everywhere): a test aid that separates precision effects from bugs; not reference behaviour."""
-    _BF16_SIM[0] = bool(bf16_storage)
+    (fp32 arithmetic everywhere): a test aid that separates precision effects from bugs; not reference behaviour.
+    storage='bf16' | 'f16' selects the 16-bit format of that model (conv_mode 'bf16' / 'f16')."""
+    _BF16_SIM[0] = {"bf16": torch.bfloat16, "f16": torch.float16, None: (torch.bfloat16 if bf16_storage else False)}[storage]
     try:
         return _forward(sd, x, align_corners, return_intermediates)
     finally:

@@ -108,6 +108,26 @@ def test_fused_warp_corr_edge_flows(case):
         assert out[:, 40, 0, :].abs().max() == 0 and out[:, 40, :, 0].abs().max() == 0
 
 
+@pytest.mark.parametrize("case", [(2, 32, 30, 72), (1, 64, 56, 128), (2, 96, 28, 64), (2, 196, 7, 16)])
+def test_fused_warp_corr_half_features(case):
+    """IEEE-half features / output (conv_mode 'f16'): tcgen05 kernel (C <= 64) and warp-MMA kernel (C > 64)"""
+    from opticalflow_b200 import ops
+    B, C, H, W = case
+    f1, f2, flow = O.corr_microbench_inputs(3, B, H, W, C)
+    f1h, f2h = f1.half(), f2.half()
+    ref = O.warp_corr_lrelu(f1h.float(), f2h.float(), flow, 2.5)
+    d = _dev()
+    nhwc = lambda t: t.permute(0, 2, 3, 1).contiguous().to(d)  # noqa: E731
+    Cp = (C + 15) // 16 * 16
+    a, b = torch.zeros(B, H, W, Cp, dtype=torch.float16, device=d), torch.zeros(B, H, W, Cp, dtype=torch.float16, device=d)
+    a[..., :C], b[..., :C] = nhwc(f1h), nhwc(f2h)
+    out = torch.zeros(B, H, W, 88, dtype=torch.float16, device=d)
+    with ops.half_format("f16"):
+        ops.warp_corr_lrelu(a[..., :C], b[..., :C], nhwc(flow), 2.5, layout="nhwc", out=out[..., :81])
+    out = out[..., :81].float().permute(0, 3, 1, 2).cpu()
+    assert (out - ref).abs().max().item() <= 1.5e-3 * ref.abs().max().item()    # half rounding of output and warped operand
+
+
 def test_fused_warp_corr_bf16_features():
     from opticalflow_b200 import ops
     C, H, W = 64, 24, 40
