@@ -198,6 +198,51 @@ void pwc_tc_conv_destroy(pwc_tc_conv* handle);
  *   that overlap on that GPU (different streams, no ordering) race.  The atomic summation order varies, so results may
  *   differ from pwc_tc_conv_launch in the last bit of the bf16 output. */
 int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* handle, int ksplit, void* stream);
+/* ------------------------------------------------------------------------------------------
+ * Split precision (conv_mode 'mixed').  An fp32-grade activation tensor is stored as TWO 16-bit planes of the same pixel
+ * row: hi = RN16(v) at channel c, lo = RN16(v - hi) at channel c + lo_off.  A convolution over such a tensor issues three
+ * tensor-core products per K step into the same fp32 accumulator, x_hi*W_hi + x_hi*W_lo + x_lo*W_hi (W_hi = RN16(W),
+ * W_lo = RN16(W - W_hi); the dropped x_lo*W_lo term is 2^-22 relative), i.e. the convolution of the fp32 reference
+ * (conv(), PWCNet.py:26-30) to ~2^-21 -- the same technique conv1a uses on its fp32 input.  No counterpart in the reference.
+ *   pwc_tc_conv_create_split : pwc_tc_conv_create plus
+ *       in_lo_off  != 0 : the input is split; w_packed then holds THREE 64-channel weight chunks per logical chunk ch, in
+ *                         the order 3ch: W_hi (for x_hi), 3ch+1: W_lo (for x_hi), 3ch+2: W_hi (for x_lo): pack a virtual
+ *                         [Cout, 3*Cin] tensor with cin_span = 3*kc*ceil(span/kc).  cin_span here stays the logical span.
+ *       out_lo_off != 0 : the 16-bit output is stored as both planes (out_coff + c and out_coff + out_lo_off + c).
+ *       up_lo_off / up_dup_off (out_f32 == 2 only): the fused upfeat outputs also go to out2_coff + up_lo_off + j (lo plane)
+ *                         and out2_coff + up_dup_off + j (second copy of hi; see pwc_deconv4x4s2_c2_split_fwd).
+ *     stride-1 dilation-1 layers with coutp <= 128 and the stride-2 layers (kc | cin_span) are supported.
+ *   pwc_conv3x3_thin_split_fwd : the thin pyramid layers (cin, cout in {16,32}, stride 1); in / out pixels are
+ *       [hi(C) | lo(C)]; w_packed rows are [W_hi(cin) | W_lo(cin)] (pack a [Cout, 2*cin] tensor with kc = span = 2*cin).
+ *   pwc_conv1a_split_fwd : conv1a (PWCNet.py:52,184) with out [N, H/2, W/2, 32] = [hi 16 | lo 16].
+ *   pwc_deconv4x4s2_c2_split_fwd : deconvL with hi / lo (/ second hi) copies of its 2 outputs in a 16-bit slice.  A
+ *       single-precision consumer gets split accuracy for these channels by treating lo and the second hi copy as extra
+ *       input channels with weights W_hi and W_lo ("K padding": the concat buffers have 11 spare channels).
+ *   pwc_copy_channels_h16 : 16-bit channel-slice copy (hi plane of the image-1 features -> c1 slot of the concat buffer).
+ * ------------------------------------------------------------------------------------------ */
+int pwc_tc_conv_create_split(pwc_tc_conv** handle,
+                             const void* in, long in_pitch, int in_coff,
+                             const void* in2, long in2_pitch, int in2_coff, int n_split, int cin_span, int kc,
+                             const void* w_packed, const float* bias, int cout, int coutp,
+                             void* out, long out_pitch, int out_coff,
+                             void* out2, long out2_pitch, int out2_coff, int out_f32,
+                             const float* residual, long res_pitch,
+                             int N, int Hin, int Win, int stride, int dil, float slope,
+                             int in_lo_off, int out_lo_off, int up_lo_off, int up_dup_off);
+int pwc_conv3x3_thin_split_fwd(const void* in, long in_pitch, int in_coff, int cin,
+                               const void* w_packed, const float* bias, int cout,
+                               void* out, long out_pitch, int out_coff,
+                               int N, int H, int W, float slope, void* stream);
+int pwc_conv1a_split_fwd(const float* x, const float* w, const float* bias, void* out,
+                         int B, int H, int W, float slope, int frames, void* stream);
+int pwc_deconv4x4s2_c2_split_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
+                                 const float* w, const float* bias,
+                                 void* out, int out_dtype, long out_pitch, int out_coff,
+                                 float* out_b, long out_b_pitch,
+                                 int N, int Hin, int Win, int lo_off, int dup_off, void* stream);
+int pwc_copy_channels_h16(const void* src, long src_pitch, int src_coff, void* dst, long dst_pitch, int dst_coff,
+                          int C, long npix, void* stream);
+
 /* 16-bit storage format of the tensor-core conv mode.  Every entry point that takes or produces 16-bit tensors (the
  * pwc_tc_conv_* family, pwc_conv3x3_mma_fwd, pwc_conv3x3_thin_fwd, pwc_conv3x3_flow_head_fwd, pwc_conv1a_*_bf16_fwd,
  * pwc_pack_conv_weight_bf16, and dtype == PWC_BF16 of pwc_warp_corr_lrelu_fwd / pwc_deconv4x4s2_c2_fwd) reads it at

@@ -39,6 +39,7 @@ struct TcConvParams {
   int out_f32;
   const float* residual; long res_pitch;
   int fp16;                                       // 16-bit operands / outputs are IEEE half instead of bf16
+  int split, lo_off, out_lo_off;                  // split precision: see WmParams::split (conv_tc_wm.cuh)
 };
 
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -92,7 +93,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             if (ptx::elect_one()) {
               const uint32_t sa = base + s * p.stage_bytes;
               ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (uint32_t)p.coutp * p.kc * 2);
-              ptx::tma_load_4d(sa, tmA, full_bar(s), ch * p.kc, x, y, nn);
+              ptx::tma_load_4d(sa, tmA, full_bar(s), p.split ? (ch / 3) * p.kc + ((ch % 3) == 2 ? p.lo_off : 0) : ch * p.kc, x, y, nn);
               ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * p.nchunk + ch) * p.coutp);
             }
             __syncwarp();
@@ -181,6 +182,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             uint4* o4 = reinterpret_cast<uint4*>(o + c0);
             o4[0] = make_uint4(w[0], w[1], w[2], w[3]);
             o4[1] = make_uint4(w[4], w[5], w[6], w[7]);
+            if (p.out_lo_off) {                     // lo plane: the exact remainders of the hi roundings
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float2 hv = unpack2_h16(w[i], p.fp16);
+                w[i] = pack2_h16(f[2 * i] - hv.x, f[2 * i + 1] - hv.y, p.fp16);
+              }
+              uint4* l4 = reinterpret_cast<uint4*>(o + c0 + p.out_lo_off);
+              l4[0] = make_uint4(w[0], w[1], w[2], w[3]);
+              l4[1] = make_uint4(w[4], w[5], w[6], w[7]);
+            }
           }
         }
       }
@@ -230,6 +241,9 @@ __global__ void pack_conv_weight_bf16_kernel(const float* __restrict__ wt, __nv_
 
 static int g_num_sms = 0;
 static thread_local int g_half_format = 0;        // 0 = bf16, 1 = IEEE half (pwc_set_half_format)
+// split-precision options of the create call in progress (pwc_tc_conv_create_split sets them around pwc_tc_conv_create)
+struct SplitOpts { int in_lo_off, out_lo_off, up_lo_off, up_dup_off; };
+static thread_local SplitOpts g_split = {0, 0, 0, 0};
 int half_format() { return g_half_format; }
 
 static int env_int(const char* name, int dflt) {
@@ -252,6 +266,7 @@ static int create_halo(pwc_tc_conv** handle, const void* in, long in_pitch, int 
   if (coutp % 16 || coutp < 16 || coutp > 256 || cout > coutp || (in_pitch & 7) || (in_coff & 7) ||
       (!out_f32 && ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7))))))
     return (int)cudaErrorInvalidValue;
+  if (g_split.in_lo_off || g_split.out_lo_off) return (int)cudaErrorInvalidValue;   // no split-precision form of this kernel
   pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
   if (!h) return (int)cudaErrorMemoryAllocation;
   h->halo = 1;
@@ -342,7 +357,11 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   for (int i = 0; i < 9; ++i) p.kk_mask[i] = 0;
   for (int i = 0; i < 9; ++i) p.skip[i] = 0ull;
   p.N = N; p.H = H; p.W = W; p.dil = dil;
-  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc);
+  p.split = g_split.in_lo_off ? 1 : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
+  p.up_lo_off = g_split.up_lo_off; p.up_dup_off = g_split.up_dup_off;
+  const int vmul = p.split ? 3 : 1;                 // virtual chunks per logical chunk (see WmParams::split)
+  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc) * vmul;
+  if ((p.split || p.out_lo_off) && (dil != 1 || kc != 64 || (p.lo_off & 7) || (p.out_lo_off & 7))) { delete h; return (int)cudaErrorInvalidValue; }
   // large dilations: phases in x only, the y dilation is a row shift inside a (rows + 2*dil)-row halo tile -- 16 x fewer,
   // 16 x larger items than d x d sub-lattices of a 7 x 16 image (dc_conv5: N = 56 pixels per MMA otherwise)
   const int ydense = (dil >= env_int("PWC_TC_WM_YDENSE_MINDIL", 8) && !ts) ? 1 : 0;
@@ -361,7 +380,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   if (env_int("PWC_TC_WM_ROWMODEL", 1)) {
     // cost model from tools/micro/mma_issue.cu: one M=128,K=16 MMA takes max(68, N/2) cycles, i.e. tiles below N = 128
     // pixels are free to grow; time ~ waves x (MMAs per item x cycles per MMA + fixed per-item cost)
-    const long nmma = (long)cdiv(cin_span, kc) * 36;
+    const long nmma = (long)cdiv(cin_span, kc) * 36 * vmul;
     long best = -1;
     for (int r = 2; r <= max_rows; r += 2) {
       const long waves = (ntiles(r) + g_num_sms - 1) / g_num_sms;
@@ -373,7 +392,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     while (ntiles(rows) < g_num_sms && rows > 8) rows = even_up(cdiv(rows, 2)) < 8 ? 8 : even_up(cdiv(rows, 2));
   }
   // thin single-chunk layers are epilogue-bound: a smaller tile leaves room for the replicated resident weight set
-  if (cdiv(cin_span, kc) == 1 && coutp <= 64 && rows > 16 && !out_f32) rows = 16;
+  if (cdiv(cin_span, kc) * vmul == 1 && coutp <= 64 && rows > 16 && !out_f32) rows = 16;
   const int forced = env_int("PWC_TC_WM_ROWS", 0);
   if (forced >= 2 && forced <= max_rows && !(forced & 1)) rows = forced;
   if (ts) {                                       // N = whole halo tile (rows+2) x 10 <= 256 pixels
@@ -395,7 +414,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   }
   // small pixel tiles consume a halo tile faster than one TMA round trip: deeper pipeline there
   p.x_stages = 2;
-  if (!ts && p.npx <= 128 && cdiv(cin_span, kc) >= 3) {
+  if (!ts && p.npx <= 128 && cdiv(cin_span, kc) * vmul >= 3) {
     p.x_stages = env_int("PWC_TC_WM_XSTAGES", 2);   // measured: 4 stages gain nothing (3374 vs 3400 pairs/s), default stays 2
     if (p.x_stages < 2) p.x_stages = 2;
     if (p.x_stages > 4) p.x_stages = 4;
@@ -472,7 +491,9 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     if (!p.wstore) e = (int)cudaErrorInvalidValue;
     if (!e) e = make_tmap_xsplit(&h->tmA0, a0, in_pitch, cin_span, W, H, N, dil, kc, 10, rows + 2 * dil, swz);
   } else {
-    e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, W, H, N,
+    // split input: one map spans both planes (the hi plane's partial last chunk then reads real neighbouring channels
+    // instead of zero fill: their weight rows are zero and all stored values are finite)
+    e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span + p.lo_off, W, H, N,
                        kc, 10 * dil, ydense ? rows + 2 * dil : (rows + 2) * dil, dil, p.dy, swz);
   }
   if (!e) e = make_tmap_2d(&h->tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w_packed, (long)9 * p.nchunk * coutp, kc, kc, coutp, swz);
@@ -486,10 +507,11 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     if ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7)))) e = (int)cudaErrorInvalidValue;
     const int n1 = out2 ? p.n_split : N;
     const int bc = p.wstore ? 32 : coutp, br = p.wstore ? p.o_rs : rows / 2;
+    if (p.out_lo_off && !p.wstore) e = (int)cudaErrorInvalidValue;     // split output exists in the per-warp store path only
     if (!e) e = make_tmap_nhwc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out) + out_coff,
-                               out_pitch, coutp, W, H, n1, bc, 8 * dil, br * p.dy, dil, p.dy, CU_TENSOR_MAP_SWIZZLE_NONE);
+                               out_pitch, coutp + p.out_lo_off, W, H, n1, bc, 8 * dil, br * p.dy, dil, p.dy, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (!e && out2) e = make_tmap_nhwc(&h->tmO2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out2) + out2_coff,
-                                       out2_pitch, coutp, W, H, N - n1, bc, 8 * dil, br * p.dy, dil, p.dy,
+                                       out2_pitch, coutp + p.out_lo_off, W, H, N - n1, bc, 8 * dil, br * p.dy, dil, p.dy,
                                        CU_TENSOR_MAP_SWIZZLE_NONE);
   }
   if (e || h->smem_bytes > 227u * 1024u || cols > 512) { delete h; return e ? e : (int)cudaErrorInvalidValue; }
@@ -500,7 +522,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   // K loops (conv5aa 16 -> 34 us: the rendezvous costs ~5 us), and the atomic summation order makes replays differ in
   // the last bit, which the parity tests do not accept.
   p.ksplit = 1; p.cps = p.nchunk; p.scratch = nullptr; p.counters = nullptr;
-  if (p.wstore && !ts && p.nchunk >= 2 && env_int("PWC_TC_WM_KSPLIT", 0)) {
+  if (p.wstore && !ts && !p.out_lo_off && p.nchunk >= 2 && env_int("PWC_TC_WM_KSPLIT", 0)) {
     int ks = g_num_sms / p.num_items;
     if (ks > 8) ks = 8;
     if (ks > p.nchunk) ks = p.nchunk;
@@ -576,7 +598,9 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   TcConvParams& p = h->p;
   p.N = N; p.Hin = Hin; p.Win = Win; p.stride = stride; p.dil = dil;
   p.Hout = (Hin - 1) / stride + 1; p.Wout = (Win - 1) / stride + 1;
-  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cin_span / kc;
+  p.split = g_split.in_lo_off ? 1 : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
+  if ((p.lo_off & 7) || (p.out_lo_off & 7) || (p.out_lo_off && out_f32)) { delete h; return (int)cudaErrorInvalidValue; }
+  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = (cin_span / kc) * (p.split ? 3 : 1);
   p.n_split = (in2 || out2) ? n_split : N;
   p.tiles_x = cdiv(p.Wout, kTcTW); p.tiles_y = cdiv(p.Hout, kTcTH); p.num_tiles = p.tiles_x * p.tiles_y * N;
   p.a_bytes = (uint32_t)kTcM * kc * 2;
@@ -594,12 +618,12 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   h->smem_bytes = (size_t)p.stages * p.stage_bytes + 8 * (2 * p.stages + 5) + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
-  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span, Win, Hin,
+  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span + p.lo_off, Win, Hin,
                          in2 ? p.n_split : N, kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
   if (!e) {
     if (in2) {
       const __nv_bfloat16* a1 = reinterpret_cast<const __nv_bfloat16*>(in2) + in2_coff;
-      e = make_tmap_nhwc(&h->tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a1, in2_pitch, cin_span, Win, Hin, N - p.n_split,
+      e = make_tmap_nhwc(&h->tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a1, in2_pitch, cin_span + p.lo_off, Win, Hin, N - p.n_split,
                          kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
     } else {
       h->tmA1 = h->tmA0;
@@ -698,6 +722,24 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
 
 extern "C" void pwc_tc_conv_destroy(pwc_tc_conv* h) { delete h; }
 
+extern "C" int pwc_tc_conv_create_split(pwc_tc_conv** handle,
+                                        const void* in, long in_pitch, int in_coff,
+                                        const void* in2, long in2_pitch, int in2_coff, int n_split, int cin_span, int kc,
+                                        const void* w_packed, const float* bias, int cout, int coutp,
+                                        void* out, long out_pitch, int out_coff,
+                                        void* out2, long out2_pitch, int out2_coff, int out_f32,
+                                        const float* residual, long res_pitch,
+                                        int N, int Hin, int Win, int stride, int dil, float slope,
+                                        int in_lo_off, int out_lo_off, int up_lo_off, int up_dup_off) {
+  if (in_lo_off < 0 || out_lo_off < 0 || up_lo_off < 0 || up_dup_off < 0) return (int)cudaErrorInvalidValue;
+  pwc::g_split = {in_lo_off, out_lo_off, up_lo_off, up_dup_off};
+  const int e = pwc_tc_conv_create(handle, in, in_pitch, in_coff, in2, in2_pitch, in2_coff, n_split, cin_span, kc, w_packed, bias,
+                                   cout, coutp, out, out_pitch, out_coff, out2, out2_pitch, out2_coff, out_f32, residual,
+                                   res_pitch, N, Hin, Win, stride, dil, slope);
+  pwc::g_split = {0, 0, 0, 0};
+  return e;
+}
+
 extern "C" int pwc_set_half_format(int fmt) {
   if (fmt != 0 && fmt != 1) return (int)cudaErrorInvalidValue;
   pwc::g_half_format = fmt;
@@ -724,7 +766,7 @@ extern "C" int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* h, int ksplit
   using namespace pwc;
   if (!h || h->halo != 2) return (int)cudaErrorInvalidValue;
   WmParams p = h->wp;                                               // by-value copy: the handle itself is not modified
-  if (!p.wstore || p.ts || p.nchunk < 2 || ksplit < 0) {
+  if (!p.wstore || p.ts || p.nchunk < 2 || ksplit < 0 || p.out_lo_off) {
     fprintf(stderr, "pwc_tc_conv_launch_static_splitk: the layer has no split-K form (needs >= 2 channel chunks, "
                     "16-bit per-warp output stores, no tap stacking)\n");
     return (int)cudaErrorInvalidValue;

@@ -32,6 +32,12 @@ struct WmParams {
   int o_nbuf; uint32_t o_half;                    // staging buffers (1 | 2) of o_half bytes each
   int wstore, o_rs;                               // per-warp stores: every epilogue warp owns 2 buffers of o_rs rows x 8 px x 32 ch
   int fp16, dbg;
+  // split precision (conv_mode 'mixed'): an fp32-grade tensor is stored as two 16-bit planes of the same pixel row, hi = RN16(v)
+  // at channel c and lo = RN16(v - hi) at channel c + lo_off.  split != 0: nchunk counts VIRTUAL chunks, three per logical
+  // 64-channel chunk -- (x_hi, W_hi), (x_hi, W_lo), (x_lo, W_hi) -- whose products meet in the same fp32 accumulator (the
+  // dropped x_lo * W_lo term is 2^-22 relative).  out_lo_off != 0: the epilogue stores both planes of its output.
+  int split, lo_off, out_lo_off;
+  int up_lo_off, up_dup_off;                      // fused upfeat outputs (out_f32 == 2): lo plane / second hi copy, 0 = none
   unsigned long long skip[9];                    // bit ch of skip[tap]: weight block (tap, chunk ch) is all zero -> no load, no MMA
   int has_kk, kk_mask[9], kk_first_tap, kk_first_kk;   // single-chunk layers: bit kk of kk_mask[tap] set <=> the K=16 step kk of
                                                   // tap's weight tile is all zero (space-to-depth block structure) -> no MMA
@@ -137,8 +143,9 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         if (ch == ch_lo) wm_mark(trp, 0, it_idx, 1);
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
-          if (p.xsplit) ptx::tma_load_5d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, rx, tx0 - 1, ya, n);
-          else ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), ch * p.kc, xa, ya, n);
+          const int xc = p.split ? (ch / 3) * p.kc + ((ch % 3) == 2 ? p.lo_off : 0) : ch * p.kc;
+          if (p.xsplit) ptx::tma_load_5d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, rx, tx0 - 1, ya, n);
+          else ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, xa, ya, n);
         }
         __syncwarp();
         if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
@@ -183,7 +190,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         ptx::tc_fence_after();
         if (ch == ch_lo) wm_mark(trm, 1, it_idx, 2);
         const uint32_t sx = x_base + xb * p.x_bytes;
-        const int nkk = min(p.kc, p.cin_span - ch * p.kc + 15) >> 4;     // K=16 steps holding real channels
+        const int nkk = min(p.kc, p.cin_span - (p.split ? ch / 3 : ch) * p.kc + 15) >> 4;     // K=16 steps holding real channels
         const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
         int ftap = 0;                                        // first tap actually issued for this chunk
         if ((kMode == 2)) while (ftap < 8 && ((p.skip[ftap] >> ch) & 1ull)) ++ftap;
@@ -302,7 +309,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           if ((p.out_f32 & 3) == 2 && co2 >= 2) {
             const int k = co2 - 2, j = k & 1, b = (k >> 1) & 1, aa = k >> 2;
             const long up = (((long)n * 2 * p.H + 2 * oy + aa) * (2 * p.W) + 2 * ox + b) * p.out2_pitch + p.out2_coff + j;
-            reinterpret_cast<uint16_t*>(p.out2)[up] = pack1_h16(val, p.fp16);
+            const uint16_t hb = pack1_h16(val, p.fp16);
+            reinterpret_cast<uint16_t*>(p.out2)[up] = hb;
+            if (p.up_lo_off) reinterpret_cast<uint16_t*>(p.out2)[up + p.up_lo_off] = pack1_h16(val - unpack1_h16(hb, p.fp16), p.fp16);
+            if (p.up_dup_off) reinterpret_cast<uint16_t*>(p.out2)[up + p.up_dup_off] = hb;
           } else {
             if (p.residual) val += p.residual[pix * p.res_pitch + co2];
             reinterpret_cast<float*>(p.out)[pix * p.out_pitch + p.out_coff + co2] = val;
@@ -359,9 +369,11 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           if (p.out_groups > 1) { const int cgp = p.coutp / p.out_groups; grp = c0g / cgp; c0g -= grp * cgp; }
           for (int r0 = 0; r0 < R; r0 += p.o_rs) {
             const uint32_t so = my_o + (uint32_t)wbuf * p.o_half;
-            if (lane == 0) ptx::bulk_wait_read1();           // the store issued two steps ago has released this buffer
+            const uint32_t so_lo = my_o + (uint32_t)(wbuf ^ 1) * p.o_half;   // split output: the other buffer takes the lo plane
+            if (lane == 0) { if (p.out_lo_off) ptx::bulk_wait_read0(); else ptx::bulk_wait_read1(); }   // buffer(s) released
             __syncwarp();
             uint16_t* st = reinterpret_cast<uint16_t*>(smem_raw + (so - ptx::smem_addr(smem_raw))) + lane;
+            uint16_t* st_lo = reinterpret_cast<uint16_t*>(smem_raw + (so_lo - ptx::smem_addr(smem_raw))) + lane;
             const int col0 = (part * R + r0) * 8, ncol = p.o_rs * 8;
             // all TMEM loads of the step (<= 64 columns) are issued before the single wait: their latency (several
             // hundred cycles while the next item's MMAs are writing TMEM) is paid once per step, not once per 16 columns
@@ -392,7 +404,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
                   uint16_t bits;
                   if (p.fp16) { __half hv = __float2half_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
                   else { __nv_bfloat16 hv = __float2bfloat16_rn(val); bits = *reinterpret_cast<uint16_t*>(&hv); }
-                  if (q * 16 + i < ncol) st[(q * 16 + i) * 32] = bits;
+                  if (q * 16 + i < ncol) {
+                    st[(q * 16 + i) * 32] = bits;
+                    if (p.out_lo_off) st_lo[(q * 16 + i) * 32] = pack1_h16(val - unpack1_h16(bits, p.fp16), p.fp16);
+                  }
                 }
               }
             }
@@ -403,9 +418,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
               if (p.out_groups > 1) ptx::tma_store_5d(&tmO, so, c0g, grp, ox, oy, nn);
               else if (p.xsplit) ptx::tma_store_5d(&tmO, so, c0g, rx, tx0, oy, nn);
               else ptx::tma_store_4d(second ? &tmO2 : &tmO, so, c0g, ox, oy, nn);
+              if (p.out_lo_off) ptx::tma_store_4d(second ? &tmO2 : &tmO, so_lo, c0g + p.out_lo_off, ox, oy, nn);
               ptx::bulk_commit();
             }
-            wbuf ^= 1;
+            if (!p.out_lo_off) wbuf ^= 1;
           }
         }
         if (p.ksplit > 1) {                                  // t_empty was signalled above

@@ -49,14 +49,18 @@ __device__ __forceinline__ void thin_cp16(uint32_t dst, const void* src, bool ok
 }
 
 // NT = output-channel n-tiles (Cout = 8 NT), KS = 16-channel k steps per tap (Cin = 16 KS)
-template <int NT, int KS, bool F16>
+// SPLIT (conv_mode 'mixed', fp32-grade pyramid): every tensor is two 16-bit planes of the same pixel row, hi = RN16(v) in
+// channels [0, C) and lo = RN16(v - hi) in [C, 2C); weight rows hold [W_hi | W_lo].  Per K step three products meet in the
+// fp32 accumulator: x_hi*W_hi + x_hi*W_lo + x_lo*W_hi (the dropped x_lo*W_lo is 2^-22 relative).  KS counts LOGICAL steps.
+template <int NT, int KS, bool F16, bool SPLIT = false>
 __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) {
   extern __shared__ __align__(128) uint8_t thin_smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t sm0 = ptx::smem_addr(thin_smem);
   const uint32_t w_addr = sm0, patch_addr = sm0 + p.off_patch;
-  constexpr int NCH = 2 * KS;                                   // 16-byte chunks per pixel / per weight row
-  constexpr int OP = NT * 16 + 16;                              // bytes per staged output pixel (padded)
+  constexpr int NCH = (SPLIT ? 4 : 2) * KS;                     // 16-byte chunks per pixel / per weight row
+  constexpr int NP = SPLIT ? 2 * NT : NT;                       // 16-byte chunks per output pixel
+  constexpr int OP = NP * 16 + 16;                              // bytes per staged output pixel (padded)
   uint8_t* ostg = thin_smem + p.off_ostg + warp * 16 * OP;
 
   // ---- weights: [9 * Cout rows][Cin] bf16, once per CTA (independent of the previous kernel: before pdl_wait)
@@ -155,12 +159,24 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
           uint32_t a[2][4];
           thin_ldsm4(a[0], a_tap + ks * 32);
           thin_ldsm4(a[1], a_tap + a_m1 + ks * 32);
+          uint32_t al[2][4];
+          if (SPLIT) {
+            thin_ldsm4(al[0], a_tap + (KS + ks) * 32);
+            thin_ldsm4(al[1], a_tap + a_m1 + (KS + ks) * 32);
+          }
 #pragma unroll
           for (int j = 0; j < NT; j += 2) {
             uint32_t b[4];
             thin_ldsm4(b, bt + (uint32_t)(j * 8 * p.wp) + ks * 32);
             mma_h16<F16>(acc[0][j], a[0], b[0], b[1]); mma_h16<F16>(acc[0][j + 1], a[0], b[2], b[3]);
             mma_h16<F16>(acc[1][j], a[1], b[0], b[1]); mma_h16<F16>(acc[1][j + 1], a[1], b[2], b[3]);
+            if (SPLIT) {
+              mma_h16<F16>(acc[0][j], al[0], b[0], b[1]); mma_h16<F16>(acc[0][j + 1], al[0], b[2], b[3]);
+              mma_h16<F16>(acc[1][j], al[1], b[0], b[1]); mma_h16<F16>(acc[1][j + 1], al[1], b[2], b[3]);
+              thin_ldsm4(b, bt + (uint32_t)(j * 8 * p.wp) + (KS + ks) * 32);
+              mma_h16<F16>(acc[0][j], a[0], b[0], b[1]); mma_h16<F16>(acc[0][j + 1], a[0], b[2], b[3]);
+              mma_h16<F16>(acc[1][j], a[1], b[0], b[1]); mma_h16<F16>(acc[1][j + 1], a[1], b[2], b[3]);
+            }
           }
         }
       }
@@ -196,14 +212,20 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
             const float v0 = acc[m][j][2 * h] + bias2[j][0], v1 = acc[m][j][2 * h + 1] + bias2[j][1];
-            *reinterpret_cast<uint32_t*>(ostg + ((lane >> 2) + 8 * h) * OP + j * 16 + 4 * (lane & 3)) =
-                pack2_h16(fmaxf(v0, v0 * p.slope), fmaxf(v1, v1 * p.slope), F16 ? 1 : 0);
+            const float r0 = fmaxf(v0, v0 * p.slope), r1 = fmaxf(v1, v1 * p.slope);
+            const uint32_t hi = pack2_h16(r0, r1, F16 ? 1 : 0);
+            *reinterpret_cast<uint32_t*>(ostg + ((lane >> 2) + 8 * h) * OP + j * 16 + 4 * (lane & 3)) = hi;
+            if (SPLIT) {
+              const float2 hf = unpack2_h16(hi, F16 ? 1 : 0);
+              *reinterpret_cast<uint32_t*>(ostg + ((lane >> 2) + 8 * h) * OP + (NT + j) * 16 + 4 * (lane & 3)) =
+                  pack2_h16(r0 - hf.x, r1 - hf.y, F16 ? 1 : 0);
+            }
           }
         __syncwarp();
         const int ox0 = (tx * p.mp + pr) * 32 + m * 16;
 #pragma unroll
-        for (int c = lane; c < 16 * NT; c += 32) {
-          const int px = c / NT, part = c - px * NT;
+        for (int c = lane; c < 16 * NP; c += 32) {
+          const int px = c / NP, part = c - px * NP;
           if (ox0 + px < p.Wo) {
             const uint4 v = *reinterpret_cast<const uint4*>(ostg + px * OP + part * 16);
             *reinterpret_cast<uint4*>(dst + ((long)oy * p.Wo + ox0 + px) * dp + part * 8) = v;
@@ -217,12 +239,12 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
   }
 }
 
-template <int NT, int KS, bool F16>
+template <int NT, int KS, bool F16, bool SPLIT = false>
 static int launch_thin(ThinConvParams& p, cudaStream_t s) {
   static int attr_dev = -1, num_sms = 0, max_ctas = 1;
   int dev = 0; cudaGetDevice(&dev);
   if (attr_dev != dev) {
-    cudaError_t e = cudaFuncSetAttribute(conv_thin_kernel<NT, KS, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_thin_kernel<NT, KS, F16, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     if (num_sms <= 0) num_sms = 148;
@@ -237,7 +259,7 @@ static int launch_thin(ThinConvParams& p, cudaStream_t s) {
     p.off_patch = (wbytes + 127) & ~127;
     p.patch_bytes = (p.ih * p.iw * p.pp + 127) & ~127;
     p.off_ostg = p.off_patch + 2 * p.patch_bytes;
-    p.off_tab = p.off_ostg + 8 * 16 * (NT * 16 + 16);
+    p.off_tab = p.off_ostg + 8 * 16 * ((SPLIT ? 2 : 1) * NT * 16 + 16);
     smem = p.off_tab + p.ih * p.iw * 16;
     if (smem <= 113 * 1024 || (p.mp == 1 && smem <= 227 * 1024)) break;   // keep two CTAs per SM if the wide tile allows it
   }
@@ -245,11 +267,11 @@ static int launch_thin(ThinConvParams& p, cudaStream_t s) {
   const long nt = (long)p.N * p.tiles_x * p.tiles_y;
   if (nt > 0x7fffffffL) return (int)cudaErrorInvalidValue;
   p.ntiles = (int)nt;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_ctas, conv_thin_kernel<NT, KS, F16>, 256, smem) != cudaSuccess || max_ctas < 1)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_ctas, conv_thin_kernel<NT, KS, F16, SPLIT>, 256, smem) != cudaSuccess || max_ctas < 1)
     max_ctas = 1;
   const long slots = (long)num_sms * max_ctas;
   const int grid = (int)(p.ntiles < slots ? p.ntiles : slots);
-  return (int)launch_pdl(conv_thin_kernel<NT, KS, F16>, dim3(grid), dim3(256), smem, s, p);
+  return (int)launch_pdl(conv_thin_kernel<NT, KS, F16, SPLIT>, dim3(grid), dim3(256), smem, s, p);
 }
 
 }  // namespace pwc
@@ -612,4 +634,35 @@ extern "C" int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
     return use_tma ? launch_c16_tma(p, (cudaStream_t)stream) : launch_c16(p, (cudaStream_t)stream);
   }
   return thin_dispatch(p, cout / 8, cin / 16, (cudaStream_t)stream);
+}
+
+// Split-precision form of the thin layers (conv_mode 'mixed': fp32-grade pyramid levels 1 and 2, PWCNet.py:52-56,184-187):
+// in / out are [hi | lo] plane pairs -- 2*cin / 2*cout 16-bit channels per pixel at in_coff / out_coff --, w_packed holds rows
+// [9][cout][W_hi(cin) | W_lo(cin)] (pwc_pack_conv_weight_bf16 with Cin = span = kc = 2*cin).  cin, cout in {16, 32}, stride 1.
+extern "C" int pwc_conv3x3_thin_split_fwd(const void* in, long in_pitch, int in_coff, int cin,
+                                          const void* w_packed, const float* bias, int cout,
+                                          void* out, long out_pitch, int out_coff,
+                                          int N, int H, int W, float slope, void* stream) {
+  using namespace pwc;
+  if (N <= 0 || H <= 0 || W <= 0 || !(cin == 16 || cin == 32) || !(cout == 16 || cout == 32) || (in_pitch & 7) || (in_coff & 7) ||
+      (out_pitch & 7) || (out_coff & 7) || slope < 0.f || slope > 1.f || in_pitch < 2 * cin || out_pitch < 2 * cout ||
+      ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(w_packed)) & 15))
+    return (int)cudaErrorInvalidValue;
+  ThinConvParams p;
+  p.in = reinterpret_cast<const __nv_bfloat16*>(in); p.in_pitch = in_pitch; p.in_coff = in_coff;
+  p.in2 = nullptr; p.in2_pitch = 0; p.in2_coff = 0; p.n_split_in = N;
+  p.w = reinterpret_cast<const __nv_bfloat16*>(w_packed); p.bias = bias; p.cin = 2 * cin; p.cout = cout;
+  p.out = reinterpret_cast<__nv_bfloat16*>(out); p.out_pitch = out_pitch; p.out_coff = out_coff;
+  p.out2 = nullptr; p.out2_pitch = 0; p.out2_coff = 0; p.n_split = N;
+  p.N = N; p.H = H; p.W = W; p.stride = 1; p.slope = slope; p.Ho = H; p.Wo = W;
+  p.tiles_y = cdiv(H, 8); p.ih = 10;
+  p.pp = 4 * cin + 16; p.wp = 4 * cin + 16;
+  p.flow_out = nullptr; p.residual = nullptr; p.res_pitch = 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool f16 = half_format() != 0;
+#define PWC_THIN_SPLIT(NTv, KSv) \
+  if (cout == 8 * NTv && cin == 16 * KSv) return f16 ? launch_thin<NTv, KSv, true, true>(p, s) : launch_thin<NTv, KSv, false, true>(p, s)
+  PWC_THIN_SPLIT(2, 1); PWC_THIN_SPLIT(4, 1); PWC_THIN_SPLIT(2, 2); PWC_THIN_SPLIT(4, 2);
+#undef PWC_THIN_SPLIT
+  return (int)cudaErrorInvalidValue;
 }

@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(256, 2) conv1a_bf16_kernel(const float* __rest
       if (ox0 + p >= Wo) break;
       uint32_t pk[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) pk[i] = pack2_h16(lrelu(acc[p][2 * i], slope), lrelu(acc[p][2 * i + 1], slope), f16);
+      for (int i = 0; i < 8; ++i) pk[i] = pack2_h16(lrelu(acc[p][2 * i], slope), lrelu(acc[p][2 * i + 1], slope), f16 & 1);
       uint4* o = reinterpret_cast<uint4*>(orow + p * 16);
       o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(256) conv1a_mma_kernel(const float* __restrict
           for (int h = 0; h < 2; ++h)
             if (ox0 + 16 * mt + g + 8 * h < Wo) {
               const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
-              *reinterpret_cast<uint32_t*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) = pack2_h16(lrelu(v0, slope), lrelu(v1, slope), f16);
+              *reinterpret_cast<uint32_t*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) = pack2_h16(lrelu(v0, slope), lrelu(v1, slope), f16 & 1);
             }
       }
     }
@@ -325,7 +325,8 @@ __global__ void __launch_bounds__(256) conv1a_mma_tma_kernel(const __grid_consta
 
     const int oy = oy0 + warp;
     if (oy < Ho) {
-      __nv_bfloat16* orow = out + (((long)img * Ho + oy) * Wo + ox0 + g) * 16 + 2 * c;
+      const int opp = (f16 & 2) ? 32 : 16;                       // bit 1: split output, pixel = [hi 16 | lo 16]
+      __nv_bfloat16* orow = out + (((long)img * Ho + oy) * Wo + ox0 + g) * opp + 2 * c;
 #pragma unroll
       for (int mt = 0; mt < 4; ++mt) {
         if (ox0 + 16 * mt >= Wo) break;
@@ -344,7 +345,13 @@ __global__ void __launch_bounds__(256) conv1a_mma_tma_kernel(const __grid_consta
           for (int h = 0; h < 2; ++h)
             if (ox0 + 16 * mt + g + 8 * h < Wo) {
               const float v0 = acc[j][2 * h] + bia[j][0], v1 = acc[j][2 * h + 1] + bia[j][1];
-              *reinterpret_cast<uint32_t*>(orow + (16 * mt + 8 * h) * 16 + 8 * j) = pack2_h16(lrelu(v0, slope), lrelu(v1, slope), f16);
+              const float r0 = lrelu(v0, slope), r1 = lrelu(v1, slope);
+              const uint32_t hi = pack2_h16(r0, r1, f16 & 1);
+              *reinterpret_cast<uint32_t*>(orow + (16 * mt + 8 * h) * opp + 8 * j) = hi;
+              if (f16 & 2) {
+                const float2 hf = unpack2_h16(hi, f16 & 1);
+                *reinterpret_cast<uint32_t*>(orow + (16 * mt + 8 * h) * opp + 16 + 8 * j) = pack2_h16(r0 - hf.x, r1 - hf.y, f16 & 1);
+              }
             }
       }
     }
@@ -359,7 +366,8 @@ __global__ void __launch_bounds__(256) conv1a_mma_tma_kernel(const __grid_consta
 
 
 static int launch_conv1a(const float* x, const float* w, const float* bias, void* out, int B, int H, int W, float slope,
-                         int frames, cudaStream_t s) {
+                         int frames, cudaStream_t s, int split = 0) {
+  const int fmt = half_format() | (split ? 2 : 0);
   static const int use_mma = []() { const char* e = getenv("PWC_CONV1A_MMA"); return e ? atoi(e) : 1; }();
   if (use_mma && (W & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
     const int tiles_x = cdiv(W >> 1, 64), tiles_y = cdiv(H >> 1, 8);
@@ -386,12 +394,14 @@ static int launch_conv1a(const float* x, const float* w, const float* bias, void
                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
           return (int)cudaErrorInvalidValue;
         return (int)launch_pdl(conv1a_mma_tma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), smem, s, tm, w, bias,
-                               reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt, half_format());
+                               reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt, fmt);
       }
+      if (split) return (int)cudaErrorNotSupported;
       return (int)launch_pdl(conv1a_mma_kernel, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, x, w, bias,
                              reinterpret_cast<__nv_bfloat16*>(out), B, H, W, slope, frames, tiles_x, tiles_y, (int)nt, half_format());
     }
   }
+  if (split) return (int)cudaErrorNotSupported;              // the split store exists in the TMA kernel only
   return (int)launch_pdl(conv1a_bf16_kernel, dim3(148 * 8), dim3(256), 0, s, x, w, bias, reinterpret_cast<__nv_bfloat16*>(out),
                          B, H, W, slope, frames, half_format());
 }
@@ -456,7 +466,7 @@ __global__ void __launch_bounds__(256) deconv4x4s2_c2_small_kernel(const TI* __r
                                                                    const float* __restrict__ w, const float* __restrict__ bias,
                                                                    TO* __restrict__ out, long out_pitch, int out_coff,
                                                                    float* __restrict__ out_b, long out_b_pitch,
-                                                                   int N, int Hin, int Win, int CinP) {
+                                                                   int N, int Hin, int Win, int CinP, int lo_off, int dup_off) {
   pdl_wait();
   pdl_launch_dependents();
   const int Hout = 2 * Hin, Wout = 2 * Win;
@@ -487,11 +497,20 @@ __global__ void __launch_bounds__(256) deconv4x4s2_c2_small_kernel(const TI* __r
     }
     TO* o = out + e * out_pitch + out_coff;
     st1(o, s0); st1(o + 1, s1);
+    if (lo_off) { st1(o + lo_off, s0 - ld1(o)); st1(o + lo_off + 1, s1 - ld1(o + 1)); }     // exact remainders of the roundings
+    if (dup_off) { st1(o + dup_off, s0); st1(o + dup_off + 1, s1); }
     if (out_b) { float* ob = out_b + e * out_b_pitch; ob[0] = s0; ob[1] = s1; }
   }
 }
 
 }  // namespace pwc
+
+// conv1a with a split-precision output (conv_mode 'mixed'): out [2B | N, H/2, W/2, 32] = [hi 16 | lo 16] per pixel
+extern "C" int pwc_conv1a_split_fwd(const float* x, const float* w, const float* bias, void* out,
+                                    int B, int H, int W, float slope, int frames, void* stream) {
+  if (B <= 0 || (H & 1) || (W & 3)) return (int)cudaErrorInvalidValue;
+  return pwc::launch_conv1a(x, w, bias, out, B, H, W, slope, frames ? 1 : 0, (cudaStream_t)stream, 1);
+}
 
 extern "C" int pwc_conv1a_bf16_fwd(const float* x, const float* w, const float* bias, void* out,
                                    int B, int H, int W, float slope, void* stream) {
@@ -506,11 +525,11 @@ extern "C" int pwc_conv1a_frames_bf16_fwd(const float* frames, const float* w, c
   return pwc::launch_conv1a(frames, w, bias, out, N, H, W, slope, 1, (cudaStream_t)stream);
 }
 
-extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
-                                      const float* w, const float* bias,
-                                      void* out, int out_dtype, long out_pitch, int out_coff,
-                                      float* out_b, long out_b_pitch,
-                                      int N, int Hin, int Win, void* stream) {
+static int deconv_launch(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
+                         const float* w, const float* bias,
+                         void* out, int out_dtype, long out_pitch, int out_coff,
+                         float* out_b, long out_b_pitch,
+                         int N, int Hin, int Win, void* stream, int lo_off, int dup_off) {
   using namespace pwc;
   if ((in_pitch & 3) || (in_coff & 3) || Cin <= 0) return (int)cudaErrorInvalidValue;
   const int CinP = (Cin + 3) / 4 * 4;
@@ -522,7 +541,7 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
     const unsigned nb = (unsigned)((px + 255) / 256 < 148 * 16 ? (px + 255) / 256 : 148 * 16);
 #define PWC_DECONV_S(TI, TO)                                                                                              \
   launch_pdl(deconv4x4s2_c2_small_kernel<TI, TO>, dim3(nb), dim3(256), 0, s, reinterpret_cast<const TI*>(in), in_pitch,    \
-             in_coff, w, bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, out_b_pitch, N, Hin, Win, CinP)
+             in_coff, w, bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, out_b_pitch, N, Hin, Win, CinP, lo_off, dup_off)
     const bool f16 = half_format() != 0;             // PWC_BF16 = "the 16-bit storage format": IEEE half after pwc_set_half_format(1)
     if (in_dtype == PWC_F32 && out_dtype == PWC_F32) PWC_DECONV_S(float, float);
     else if (f16 && in_dtype == PWC_F32 && out_dtype == PWC_BF16) PWC_DECONV_S(float, __half);
@@ -535,6 +554,7 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
 #undef PWC_DECONV_S
     return (int)cudaGetLastError();
   }
+  if (lo_off || dup_off) return (int)cudaErrorNotSupported;
 #define PWC_DECONV(TI, TO)                                                                                             \
   launch_pdl(deconv4x4s2_c2_any_kernel<TI, TO>, dim3(blocks), dim3(256), 0, s, reinterpret_cast<const TI*>(in), in_pitch, in_coff, CinP, w, \
                                                            bias, reinterpret_cast<TO*>(out), out_pitch, out_coff, out_b, \
@@ -550,4 +570,55 @@ extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitc
   else return (int)cudaErrorInvalidValue;
 #undef PWC_DECONV
   return (int)cudaGetLastError();
+}
+
+extern "C" int pwc_deconv4x4s2_c2_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
+                                      const float* w, const float* bias,
+                                      void* out, int out_dtype, long out_pitch, int out_coff,
+                                      float* out_b, long out_b_pitch,
+                                      int N, int Hin, int Win, void* stream) {
+  return deconv_launch(in, in_dtype, in_pitch, in_coff, Cin, w, bias, out, out_dtype, out_pitch, out_coff, out_b, out_b_pitch,
+                       N, Hin, Win, stream, 0, 0);
+}
+
+// deconvL (2 -> 2 channels, PWCNet.py:208...) with a split-precision result in a 16-bit concat slice: channels out_coff + {0,1}
+// take hi = RN16(v), out_coff + lo_off + {0,1} the exact remainders RN16(v - hi), and (dup_off != 0) out_coff + dup_off + {0,1}
+// a second copy of hi -- the K-padding form of the split for single-precision consumers.  Cin <= 4 only.
+extern "C" int pwc_deconv4x4s2_c2_split_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,
+                                            const float* w, const float* bias,
+                                            void* out, int out_dtype, long out_pitch, int out_coff,
+                                            float* out_b, long out_b_pitch,
+                                            int N, int Hin, int Win, int lo_off, int dup_off, void* stream) {
+  if (lo_off < 0 || dup_off < 0 || out_dtype != PWC_BF16) return (int)cudaErrorInvalidValue;
+  return deconv_launch(in, in_dtype, in_pitch, in_coff, Cin, w, bias, out, out_dtype, out_pitch, out_coff, out_b, out_b_pitch,
+                       N, Hin, Win, stream, lo_off, dup_off);
+}
+
+namespace pwc {
+// channel slice copy between two NHWC+pitch 16-bit tensors, 16 bytes per thread (C % 8 == 0): HBM-bound plumbing kernel
+__global__ void __launch_bounds__(256) copy_channels_h16_kernel(const uint16_t* __restrict__ src, long sp, const uint16_t* dummy,
+                                                                uint16_t* __restrict__ dst, long dp, int cvec, long npix) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const long total = npix * cvec;
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+    const long px = e / cvec; const int v = (int)(e - px * cvec);
+    *reinterpret_cast<uint4*>(dst + px * dp + 8 * v) = *reinterpret_cast<const uint4*>(src + px * sp + 8 * v);
+  }
+}
+}  // namespace pwc
+
+// dst[px, dst_coff + c] = src[px, src_coff + c], c < C, for npix pixels of two NHWC+pitch 16-bit tensors (conv_mode 'mixed':
+// the hi plane of the image-1 pyramid features -> the c1 slot of the decoder concat buffer, PWCNet.py:215,229,243,259).
+extern "C" int pwc_copy_channels_h16(const void* src, long src_pitch, int src_coff, void* dst, long dst_pitch, int dst_coff,
+                                     int C, long npix, void* stream) {
+  using namespace pwc;
+  if (C <= 0 || (C & 7) || (src_pitch & 7) || (dst_pitch & 7) || (src_coff & 7) || (dst_coff & 7) || npix <= 0 ||
+      ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15))
+    return (int)cudaErrorInvalidValue;
+  const long total = npix * (C / 8);
+  const unsigned nb = (unsigned)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  return (int)launch_pdl(copy_channels_h16_kernel, dim3(nb), dim3(256), 0, (cudaStream_t)stream,
+                         reinterpret_cast<const uint16_t*>(src) + src_coff, src_pitch, (const uint16_t*)nullptr,
+                         reinterpret_cast<uint16_t*>(dst) + dst_coff, dst_pitch, C / 8, npix);
 }

@@ -194,6 +194,94 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     return out
 
 
+def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, split_out=True, reps=1):
+    """Split-precision tcgen05 conv (pwc_tc_conv_create_split) for tests / tools: x32 [N,H,W,cin] fp32 NHWC is stored as
+    hi | lo planes of the current 16-bit format; returns the fp32 reconstruction hi + lo of the output [N,Ho,Wo,cout]."""
+    import ctypes
+    from . import split as S
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    dt = _h16(lib)
+    N, H, W, cin = x32.shape
+    cout = weight.shape[0]
+    P = (cin + 15) // 16 * 16
+    span = P
+    coutp = (cout + 31) // 32 * 32 if split_out else (cout + 15) // 16 * 16
+    kc = pick_kc(span, stride, 1, W=W, coutp=coutp)
+    dev = x32.device
+    xin = torch.zeros(N, H, W, 2 * P if split_in else P, device=dev, dtype=dt)
+    hi, lo = S.planes(x32, dt)
+    xin[..., :cin] = hi
+    if split_in:
+        xin[..., P:P + cin] = lo
+    w32 = weight.detach().float().contiguous()
+    if split_in:
+        wv, cm, vspan = S.virtual_weights(w32.cpu(), dt, kc, span)
+        wv = wv.to(dev)
+    else:
+        wv, cm, vspan = w32, list(range(cin)), (span + kc - 1) // kc * kc
+    wp = torch.zeros(9 * vspan * coutp, device=dev, dtype=dt)
+    mp = torch.tensor(cm, device=dev, dtype=torch.int32)
+    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wv), _lib.ptr(wp), _lib.ptr(mp), cout, wv.shape[1], vspan, kc, coutp, st), "pack")
+    ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    out = torch.zeros(N, ho, wo, 2 * coutp if split_out else coutp, device=dev, dtype=dt)
+    b32 = bias.detach().float().contiguous()
+    h = ctypes.c_void_p()
+    e = lib.pwc_tc_conv_create_split(ctypes.byref(h), _lib.ptr(xin), xin.shape[-1], 0, None, 0, 0, N, span, kc, _lib.ptr(wp),
+                                     _lib.ptr(b32), cout, coutp, _lib.ptr(out), out.shape[-1], 0, None, 0, 0, 0, None, 0,
+                                     N, H, W, stride, 1, slope, P if split_in else 0, coutp if split_out else 0, 0, 0)
+    _lib.check(e, "pwc_tc_conv_create_split")
+    try:
+        _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
+        if reps > 1:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps - 1):
+                _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
+            e1.record(); e1.synchronize()
+            conv3x3_tc_split.last_ms = e0.elapsed_time(e1) / (reps - 1)
+        torch.cuda.current_stream().synchronize()
+    finally:
+        lib.pwc_tc_conv_destroy(h)
+    res = out[..., :cout].float()
+    if split_out:
+        res = res + out[..., coutp:coutp + cout].float()
+    return res
+
+
+def conv3x3_thin_split(x32, weight, bias, slope=0.1, reps=1):
+    """Split-precision thin layer (pwc_conv3x3_thin_split_fwd): x32 [N,H,W,cin] fp32, cin / cout in {16, 32}; returns hi + lo."""
+    from . import split as S
+    lib = _lib.load()
+    st = _lib.stream_handle()
+    dt = _h16(lib)
+    N, H, W, cin = x32.shape
+    cout = weight.shape[0]
+    dev = x32.device
+    hi, lo = S.planes(x32, dt)
+    xin = torch.cat([hi, lo], -1).contiguous()
+    w32 = weight.detach().float()
+    wv = torch.cat([w32, S.residual(w32, dt)], 1).contiguous()
+    wp = torch.zeros(9 * cout * 2 * cin, device=dev, dtype=dt)
+    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wv), _lib.ptr(wp), None, cout, 2 * cin, 2 * cin, 2 * cin, cout, st), "pack")
+    out = torch.full((N, H, W, 2 * cout), 7.0, device=dev, dtype=dt)
+    b32 = bias.detach().float().contiguous()
+
+    def launch():
+        _lib.check(lib.pwc_conv3x3_thin_split_fwd(_lib.ptr(xin), 2 * cin, 0, cin, _lib.ptr(wp), _lib.ptr(b32), cout, _lib.ptr(out),
+                                                  2 * cout, 0, N, H, W, slope, st), "pwc_conv3x3_thin_split_fwd")
+    launch()
+    if reps > 1:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps - 1):
+            launch()
+        e1.record(); e1.synchronize()
+        conv3x3_thin_split.last_ms = e0.elapsed_time(e1) / (reps - 1)
+    torch.cuda.current_stream().synchronize()
+    return out[..., :cout].float() + out[..., cout:].float()
+
+
 def conv1a_bf16(x, weight, bias, slope=0.1):
     """conv1a fused with the im1/im2 split (pwc_conv1a_bf16_fwd): x [B,6,H,W] fp32 -> bf16 NHWC [2B,H/2,W/2,16]."""
     lib = _lib.load()
