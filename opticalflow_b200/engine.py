@@ -52,7 +52,7 @@ def chan_map(lvl, start):
     return list(range(dense)) + [dense + t for t in tail_map(lvl)]
 
 
-CONV_MODES = ("fp32", "bf16", "f16")
+CONV_MODES = ("fp32", "bf16", "f16", "mixed")
 
 
 def weights_key(model):
@@ -277,4 +277,7 @@ def make_plan(model, B, H, W, device, conv_mode="fp32", align_corners=False, vid
     if conv_mode in ("bf16", "f16"):
         from .engine_bf16 import PlanBF16
         return PlanBF16(model, B, H, W, device, align_corners, video=video, half=conv_mode)
+    if conv_mode == "mixed":
+        from .engine_mixed import PlanMixed
+        return PlanMixed(model, B, H, W, device, align_corners, video=video)
     raise ValueError(f"unknown conv_mode {conv_mode!r} (expected one of {CONV_MODES})")

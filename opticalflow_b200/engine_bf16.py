@@ -16,6 +16,7 @@ import torch
 
 from . import _lib
 from .ops import pick_kc
+from . import split as S
 from .engine import (weights_key, C1_OFF, CORR_OFF, DC, DEC_START, DEC_WRITE, FLOW_SCALE, PYR_CH, UPFEAT_OFF, UPFLOW_OFF, chan_map,
                      concat_width)
 
@@ -37,7 +38,7 @@ def _s2d_weights(name, g):
       W'[(dx,co), (dx',ci), ky, KX] = W[co, ci, ky, kx],  kx = g*(KX-1) + dx' - dx + 1  when 0 <= kx <= 2, else 0
     (input pixel g*(X+KX-1)+dx' = g*X+dx + kx-1).  Same products, zeros added: results are unchanged."""
     def make(sd):
-        w, b = sd[name + ".weight"], sd[name + ".bias"]
+        w, b = name(sd) if callable(name) else (sd[name + ".weight"], sd[name + ".bias"])
         co, ci = w.shape[0], w.shape[1]
         w2 = torch.zeros(g, co, g, ci, 3, 3, device=w.device, dtype=torch.float32)
         for dx in range(g):
@@ -112,7 +113,7 @@ THIN_LAYERS = set(x for x in os.environ.get("PWC_THIN_LAYERS", "conv1aa.0,conv1b
 
 class _TcLayer:
     __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups", "kkskip",
-                 "masks_set")
+                 "masks_set", "split_in", "kpad", "mask_key")
 
 
 class PlanBF16:
@@ -190,13 +191,17 @@ class PlanBF16:
     # ------------------------------------------------------------------ layer construction
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
-            flops=None, ts=False, groups=None, kkskip=False):
+            flops=None, ts=False, groups=None, kkskip=False, in_lo=0, out_lo=0, up_lo=0, up_dup=0, kpad=None, no_small=False):
+        """in_lo / out_lo: channel offset of the lo plane of a split-precision input / output (0 = single precision);
+        up_lo / up_dup: lo / second-hi offsets of the fused upfeat outputs; kpad = (idx, lo_pos, dup_pos): the torch input
+        channels idx are also read from their lo copies / second hi copies at those slice positions (split.kpad_weights)."""
         if key in THIN_LAYERS and dil == 1 and not out_f32 and not ts and groups is None and residual is None and cmap is None \
-                and wfn is None and cin == span and cin in (16, 32, 64) and cout in (16, 32, 64) and not (stride == 2 and cin > 16):
+                and wfn is None and cin == span and cin in (16, 32, 64) and cout in (16, 32, 64) and not (stride == 2 and cin > 16) \
+                and not (in_lo or out_lo):
             return self._thin(key, cin, cout, src, src_coff, dst, dst_coff, N, hin, win, stride, slope, src2, src2_coff, dst2,
                               dst2_coff, n_split)
         if key in SMALL_LAYERS and dil == 1 and not out_f32 and not ts and groups is None and residual is None \
-                and (dst2 is None or dst2_coff == 0):
+                and (dst2 is None or dst2_coff == 0) and not (in_lo or out_lo or no_small):
             return self._small(key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride, slope, cmap, src2,
                                src2_coff, dst2, dst2_coff, n_split, wfn, flops)
         L = _TcLayer()
@@ -207,16 +212,22 @@ class PlanBF16:
         L.coutp = 128 if ts else _roundup(cout, 16)
         L.kc = pick_kc(span, stride, dil, src2 is not None, W=win, coutp=L.coutp, out_f32=bool(out_f32) or dst2 is not None)
         L.wrows = 128 if ts else cout                   # rows of the weight tensor handed to the packer
+        L.split_in, L.kpad, L.mask_key = bool(in_lo), kpad, key
+        if out_lo:
+            L.coutp = _roundup(cout, 32)                  # split stores exist in the per-warp (32-channel group) store path
         dev = self.device
-        L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp, device=dev, dtype=self.hdt)
+        L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp * (3 if in_lo else 1), device=dev, dtype=self.hdt)
         L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
         h = ctypes.c_void_p()
-        e = self.lib.pwc_tc_conv_create(
-            ctypes.byref(h), _lib.ptr(src), src.shape[-1], src_coff,
-            _lib.ptr(src2), (src2.shape[-1] if src2 is not None else 0), src2_coff, n_split, span, L.kc,
-            _lib.ptr(L.w), _lib.ptr(L.b), cout, L.coutp, _lib.ptr(dst), dst.shape[-1], dst_coff,
-            _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32) | (16 if ts else 0),
-            _lib.ptr(residual), (residual.shape[-1] if residual is not None else 0), N, hin, win, stride, dil, slope)
+        args = (ctypes.byref(h), _lib.ptr(src), src.shape[-1], src_coff,
+                _lib.ptr(src2), (src2.shape[-1] if src2 is not None else 0), src2_coff, n_split, span, L.kc,
+                _lib.ptr(L.w), _lib.ptr(L.b), cout, L.coutp, _lib.ptr(dst), dst.shape[-1], dst_coff,
+                _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32) | (16 if ts else 0),
+                _lib.ptr(residual), (residual.shape[-1] if residual is not None else 0), N, hin, win, stride, dil, slope)
+        if in_lo or out_lo or up_lo or up_dup:
+            e = self.lib.pwc_tc_conv_create_split(*args, in_lo, out_lo, up_lo, up_dup)
+        else:
+            e = self.lib.pwc_tc_conv_create(*args)
         _lib.check(e, f"pwc_tc_conv_create {key}")
         L.groups = groups
         if groups is not None and groups[1] != L.coutp // groups[0]:
@@ -442,17 +453,22 @@ class PlanBF16:
             wt, bs = (sd[key + ".weight"], sd[key + ".bias"]) if L.wfn is None else L.wfn(sd)
             wt = wt.contiguous()
             assert wt.shape[0] == L.wrows and wt.shape[1] == L.cin, (key, tuple(wt.shape), L.cin, L.wrows)
+            cm, span_pack = L.cmap, L.span
+            if getattr(L, "split_in", False):
+                # split-precision input: three weight chunks per logical chunk (W_hi | W_lo | W_hi), see split.virtual_weights
+                wt, cm, span_pack = S.virtual_weights(wt, self.hdt, L.kc, L.span, cm)
             mp = None
-            if L.cmap is not None:
-                mp = torch.tensor(L.cmap, device=dev, dtype=torch.int32); keep.append(mp)
-            _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.wrows, L.cin, L.span, L.kc,
-                                                     L.coutp, st), f"pack {key}")
+            if cm is not None:
+                mp = torch.tensor(cm, device=dev, dtype=torch.int32); keep.append(mp)
+            _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wt), _lib.ptr(L.w), _lib.ptr(mp), L.wrows, wt.shape[1], span_pack,
+                                                     L.kc, L.coutp, st), f"pack {key}")
             L.b.copy_(bs)
             if (L.kkskip or L.groups is not None) and not getattr(L, "masks_set", False):
                 # Skip masks come from the STRUCTURE of the space-to-depth weight (which (tap, K block) pairs can ever be
                 # non-zero: the weight builder applied to all-ones parameters), never from the values: they are kernel
                 # parameters baked into the captured CUDA graph and must not change when a new state_dict is loaded.
-                ones = {k: torch.ones_like(v) for k, v in sd.items() if k.startswith(key.split(".")[0] + ".")}
+                # (1 + 2^-12: its 16-bit rounding residual is non-zero too, so W_lo copies of a K-padded layer count as present)
+                ones = {k: torch.full_like(v, 1.000244140625) for k, v in sd.items()}
                 ws = (L.wfn(ones)[0] != 0)
                 if L.kkskip:
                     # single-chunk layer: all-zero 16-channel K steps of each tap's weight tile are not issued

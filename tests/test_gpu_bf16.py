@@ -161,6 +161,24 @@ def _epe(a, b):
     return (a - b).pow(2).sum(1).sqrt()
 
 
+@pytest.mark.parametrize("shape,shift", [((1, 128, 192), 1), ((2, 64, 128), 0), ((1, 448, 1024), 0), ((1, 448, 1024), 1)])
+def test_forward_mixed_epe_delta(shape, shift):
+    """conv_mode 'mixed' (split-precision pyramid / level 4-6 decoders / up_flow + up_feat, half elsewhere): the north_star
+    bar in PIXELS -- mean EPE delta <= 0.02 px on the x20 flow (script_pwc.py:72) against the fp32 reference forward, both
+    synthetic inputs of SURVEY 8(d) at 1024x448."""
+    B, H, W = shape
+    m = _model(0, False, conv_mode="mixed")
+    sd = {k: v.detach().cpu() for k, v in m.state_dict().items()}
+    x = O.shifted_pair_input(B, H, W, 3) if shift else O.synthetic_input(B, H, W, 1)
+    ref = O.forward(sd, x)
+    flow = m(x.cuda()).cpu()
+    e_px = 20 * _epe(flow, ref).mean().item()
+    print(f"mixed mode {W}x{H} shift={shift}: mean EPE delta vs fp32 reference {e_px:.4f} px (x20 flow), max-abs "
+          f"{20 * (flow - ref).abs().max().item():.3f} px; |flow| max {20 * ref.abs().max().item():.1f} px")
+    assert e_px <= 0.02
+    assert torch.equal(m(x.cuda()).cpu(), flow)
+
+
 @pytest.mark.parametrize("shape,shift", [((1, 128, 192), 1), ((1, 448, 1024), 0), ((1, 448, 1024), 1)])
 def test_forward_f16_epe_delta(shape, shift):
     """conv_mode 'f16' (IEEE-half storage, same kernels): the EPE delta in PIXELS of the x20 flow (script_pwc.py:72) must
