@@ -384,7 +384,7 @@ def run_ours(args):
     roof, roof_corr, kern_table = None, None, None
     if hasattr(plan, "time_ops"):
         ops_t = plan.time_ops(reps=3)
-        is_tc = lambda n: not (n.startswith("warp_corr") or n.startswith("deconv") or n.startswith("conv1a.") or n == "unpack_flow")  # noqa: E731
+        is_tc = lambda n: not (n.startswith("warp_corr") or n.startswith("deconv") or n.startswith("conv1a.") or n == "unpack_flow" or n.startswith("c1_copy"))  # noqa: E731
         tc = [(n, t, f) for (n, t, f) in ops_t if is_tc(n)]
         tc_t, tc_f = sum(t for _, t, _ in tc), sum(f for _, _, f in tc)
         all_t = sum(t for _, t, _ in ops_t)
@@ -444,14 +444,50 @@ def run_ours(args):
                   "epe_delta_px_over_20": epe, "epe_delta_px": 20.0 * epe, "max_abs_px": 20.0 * d_.abs().max().item(),
                   "flow_max_px": 20.0 * ref_f.abs().max().item(),
                   "bar": "fp32: max-abs <= 1e-3 px; 16-bit conv modes: mean EPE delta <= 0.02 px on the x20 flow (script_pwc.py:72)"}
+    other_modes = None
+    if world == 1 and not args.no_other_modes:
+        # the other conv modes on the same input, device-resident leg only (same protocol: CUDA-graph replay, CUDA events) + parity
+        other_modes = {}
+        ref_f = O.forward({k: v.detach().cpu() for k, v in model.state_dict().items()}, x_host[:min(B, 2)])
+        for om in ("f16", "bf16", "fp32"):
+            if om == args.mode:
+                continue
+            try:
+                mo = PWCDCNet(conv_mode=om).eval().to(dev)
+                mo.load_state_dict(model.state_dict())
+                po = mo._plan(B, H, W, dev)
+                po.pack_weights(mo)
+                if hasattr(po, "x_static"):
+                    po.x_static.copy_(x)
+                stepo = (lambda: po.run()) if hasattr(po, "x_static") else (lambda: po.run(x))
+                nst = args.steps if om != "fp32" else max(3, args.steps // 5)
+                for _ in range(3):
+                    stepo()
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(nst):
+                    stepo()
+                e1.record(); e1.synchronize()
+                to = e0.elapsed_time(e1) * 1e-3
+                go = stepo().float().cpu()[:min(B, 2)]
+                dd = go - ref_f
+                other_modes[om] = {"value": B * nst / to, "unit": "pairs/s", "ms_per_step": 1e3 * to / nst, "steps": nst,
+                                   "epe_delta_px": 20.0 * dd.pow(2).sum(1).sqrt().mean().item(),
+                                   "max_abs_px": 20.0 * dd.abs().max().item()}
+                del mo, po
+                torch.cuda.empty_cache()
+            except Exception as ex:  # noqa: BLE001
+                other_modes[om] = {"error": f"{type(ex).__name__}: {ex}"}
     if sus is not None and roof is not None:
         sus["step_tflops"] = sus["value"] * gflop_pair / 1e3 / world
         sus["frac_of_sustained_peak"] = sus["step_tflops"] / peaks["bf16_tflops_sustained"]
     line = {
         "metric": "pwcnet_frame_pairs_per_s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16", "f16": "f16", "fp32": "f32"}.get(args.mode, args.mode), "data": "synthetic",
-        "config": {"workload": f"PWCDCNet forward, batch {B}/GPU, {W}x{H}, random-init weights, conv_mode={args.mode}",
+        "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16", "f16": "f16", "mixed": "f16", "fp32": "f32"}.get(args.mode, args.mode), "data": "synthetic",
+        "config": {"workload": f"PWCDCNet forward, batch {B}/GPU, {W}x{H}, random-init weights, conv_mode={args.mode}" +
+                               (" (IEEE-half storage; feature pyramid, level 5/4 decoders and up_flow/up_feat in split precision: "
+                                "two half planes per tensor, three tensor-core products per K step)" if args.mode == "mixed" else ""),
                    "l2": "activation working set per step >> 126 MB L2 (no flush needed)", "parallelism": f"pairs sharded x{world}, no collective"},
         "e2e": {"value": pairs / t_e2e, "unit": "pairs/s", "h2d_bytes_per_step": x_host.numel() * 4 * world,
                 "d2h_bytes_per_step": out_host.numel() * 4 * world,
@@ -466,7 +502,7 @@ def run_ours(args):
         "cpu_baseline": {"value": cpu_v, "unit": "pairs/s", "cores": cpu_cores, "kind": cpu_kind, "sample": cpu_sample,
                          "one_thread_value": cpu_v1},
         "gpu_baseline": gpu_base,
-        "clocks": clocks, "sustained": sus, "parity": parity,
+        "clocks": clocks, "sustained": sus, "parity": parity, "other_modes": other_modes,
     }
     if kern_table and os.environ.get("PWC_BENCH_KERNELS"):
         line["kernel_us"] = kern_table
@@ -481,9 +517,10 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "f16"), choices=["fp32", "bf16", "f16", "mixed"])
+    ap.add_argument("--mode", default=os.environ.get("PWC_BENCH_MODE", "mixed"), choices=["fp32", "bf16", "f16", "mixed"])
     ap.add_argument("--sustain", type=float, default=float(os.environ.get("PWC_BENCH_SUSTAIN", "3")),
                     help="seconds of the back-to-back sustained leg (0 = off)")
+    ap.add_argument("--no-other-modes", action="store_true", help="skip the short device-resident legs of the other conv modes")
     ap.add_argument("--batch", type=int, default=B_DEF)
     ap.add_argument("--height", type=int, default=H_DEF)
     ap.add_argument("--width", type=int, default=W_DEF)

@@ -40,6 +40,9 @@ struct TcConvParams {
   const float* residual; long res_pitch;
   int fp16;                                       // 16-bit operands / outputs are IEEE half instead of bf16
   int split, lo_off, out_lo_off;                  // split precision: see WmParams::split (conv_tc_wm.cuh)
+  int fused;                                      // split input whose planes are adjacent and fit one swizzle row ([hi | lo] <= 64
+                                                  // channels): kc counts BOTH planes, one stage = the A box + two weight tiles
+                                                  // [W_hi | W_hi] and [W_lo | 0]; the second runs on the hi half only
 };
 
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -58,7 +61,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - ptx::smem_addr(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ksteps = 9 * p.nchunk;
+  const int ksteps = p.fused ? 9 : 9 * p.nchunk;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA0); ptx::prefetch_tmap(&tmA1); ptx::prefetch_tmap(&tmB);
@@ -88,6 +91,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         for (int tap = 0; tap < 9; ++tap) {
           const int ky = tap / 3, kx = tap - 3 * ky;
           const int y = ty0 * p.stride + (ky - 1) * p.dil, x = tx0 * p.stride + (kx - 1) * p.dil;
+          if (p.fused) {
+            ptx::mbar_wait(empty_bar(s), ph ^ 1);
+            if (ptx::elect_one()) {
+              const uint32_t sa = base + s * p.stage_bytes, bb = (uint32_t)p.coutp * p.kc * 2;
+              ptx::mbar_expect_tx(full_bar(s), p.a_bytes + 2 * bb);
+              ptx::tma_load_4d(sa, tmA, full_bar(s), 0, x, y, nn);
+              ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * 2) * p.coutp);
+              ptx::tma_load_2d(sa + p.a_bytes + bb, &tmB, full_bar(s), 0, (tap * 2 + 1) * p.coutp);
+            }
+            __syncwarp();
+            if (++s == p.stages) { s = 0; ph ^= 1; }
+            continue;
+          }
           for (int ch = 0; ch < p.nchunk; ++ch) {
             ptx::mbar_wait(empty_bar(s), ph ^ 1);
             if (ptx::elect_one()) {
@@ -124,6 +140,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             const uint64_t db = ptx::make_kmajor_desc(sa + p.a_bytes, 8 * row_bytes, ltype);
             for (int kk = 0; kk < p.kc / 16; ++kk)
               ptx::umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (k | kk) ? 1u : 0u);
+            if (p.fused) {                            // x_hi * W_lo: the hi half of the box against the second weight tile
+              const uint64_t db2 = ptx::make_kmajor_desc(sa + p.a_bytes + (uint32_t)p.coutp * row_bytes, 8 * row_bytes, ltype);
+              for (int kk = 0; kk < p.kc / 32; ++kk) ptx::umma_bf16(d_tmem, da + 2 * kk, db2 + 2 * kk, idesc, 1u);
+            }
             ptx::umma_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
             if (k == ksteps - 1) ptx::umma_commit(tfull_bar(acc));   // accumulator complete -> epilogue
           }
@@ -521,17 +541,25 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   // OPT-IN (PWC_TC_WM_KSPLIT=1): measured on B200 it only pays for >= 8 chunks (conv6_4 24 -> 18 us) and loses on short
   // K loops (conv5aa 16 -> 34 us: the rendezvous costs ~5 us), and the atomic summation order makes replays differ in
   // the last bit, which the parity tests do not accept.
-  p.ksplit = 1; p.cps = p.nchunk; p.scratch = nullptr; p.counters = nullptr;
-  if (p.wstore && !ts && !p.out_lo_off && p.nchunk >= 2 && env_int("PWC_TC_WM_KSPLIT", 0)) {
+  p.ksplit = 1; p.cps = p.nchunk; p.scratch = nullptr; p.counters = nullptr; p.ks2pass = 0;
+  // Deterministic two-pass split-K (default ON, PWC_TC_WM_KSPLIT2=0 turns it off): layers whose pixel tiles fill less than half
+  // of the SMs and whose K loop has >= PWC_TC_WM_KSPLIT2_MINCH (6) chunks -- levels 5-6, and the split-precision level 4-6
+  // decoders whose K loops are three times as long -- run ks CTAs per tile on contiguous chunk ranges; each stores its fp32
+  // partial tile to its own scratch slab and wm_splitk_reduce_kernel (a second launch) sums the slabs in order.
+  const bool two_pass = env_int("PWC_TC_WM_KSPLIT2", 1) && dil == 1 && !p.xsplit && p.out_groups == 1 &&
+                        2 * p.num_items <= g_num_sms && p.nchunk >= env_int("PWC_TC_WM_KSPLIT2_MINCH", 6);
+  if (p.wstore && !ts && p.nchunk >= 2 && (two_pass || (!p.out_lo_off && env_int("PWC_TC_WM_KSPLIT", 0)))) {
     int ks = g_num_sms / p.num_items;
     if (ks > 8) ks = 8;
+    if (two_pass && ks > p.nchunk / 3) ks = p.nchunk / 3;            // at least 3 chunks per CTA: below that the pipeline fill dominates
     if (ks > p.nchunk) ks = p.nchunk;
     const int forced_ks = env_int("PWC_TC_WM_KSPLIT_N", 0);
     if (forced_ks > 0) ks = forced_ks < p.nchunk ? forced_ks : p.nchunk;
     if (ks >= 2) {
       p.cps = cdiv(p.nchunk, ks);
       p.ksplit = cdiv(p.nchunk, p.cps);
-      const size_t fl = (size_t)p.num_items * p.npx * 128;
+      p.ks2pass = two_pass ? 1 : 0;
+      const size_t fl = (size_t)p.num_items * p.npx * 128 * (two_pass ? p.ksplit : 1);
       const size_t bytes = fl * sizeof(float) + (size_t)p.num_items * sizeof(int);
       if (cudaMalloc(&h->scratch, bytes) != cudaSuccess || cudaMemset(h->scratch, 0, bytes) != cudaSuccess) {
         delete h; return (int)cudaErrorMemoryAllocation;
@@ -601,10 +629,12 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   p.split = g_split.in_lo_off ? 1 : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
   if ((p.lo_off & 7) || (p.out_lo_off & 7) || (p.out_lo_off && out_f32)) { delete h; return (int)cudaErrorInvalidValue; }
   p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = (cin_span / kc) * (p.split ? 3 : 1);
+  p.fused = (p.split && p.lo_off == cin_span && cin_span == kc && kc <= 32 && env_int("PWC_TC_FUSED_SPLIT", 1)) ? 1 : 0;
+  if (p.fused) { p.kc = kc = 2 * kc; p.nchunk = 2; p.split = 0; }      // weights: [tap][2][coutp][2*cin] = [W_hi|W_hi], [W_lo|0]
   p.n_split = (in2 || out2) ? n_split : N;
   p.tiles_x = cdiv(p.Wout, kTcTW); p.tiles_y = cdiv(p.Hout, kTcTH); p.num_tiles = p.tiles_x * p.tiles_y * N;
   p.a_bytes = (uint32_t)kTcM * kc * 2;
-  p.stage_bytes = (p.a_bytes + (uint32_t)coutp * kc * 2 + 1023u) & ~1023u;
+  p.stage_bytes = (p.a_bytes + (uint32_t)coutp * kc * 2 * (p.fused ? 2 : 1) + 1023u) & ~1023u;
   int stages = (int)((200u * 1024u) / p.stage_bytes);
   p.stages = stages > 8 ? 8 : (stages < 2 ? 2 : stages);
   uint32_t cols = 32; while (cols < 2u * coutp) cols <<= 1;
@@ -618,12 +648,13 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   h->smem_bytes = (size_t)p.stages * p.stage_bytes + 8 * (2 * p.stages + 5) + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
-  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span + p.lo_off, Win, Hin,
+  if (p.fused) cin_span = kc;                                        // both planes are one box now
+  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span + (p.fused ? 0 : p.lo_off), Win, Hin,
                          in2 ? p.n_split : N, kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
   if (!e) {
     if (in2) {
       const __nv_bfloat16* a1 = reinterpret_cast<const __nv_bfloat16*>(in2) + in2_coff;
-      e = make_tmap_nhwc(&h->tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a1, in2_pitch, cin_span + p.lo_off, Win, Hin, N - p.n_split,
+      e = make_tmap_nhwc(&h->tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a1, in2_pitch, cin_span + (p.fused ? 0 : p.lo_off), Win, Hin, N - p.n_split,
                          kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
     } else {
       h->tmA1 = h->tmA0;
@@ -677,6 +708,10 @@ extern "C" int pwc_tc_conv_set_out_groups(pwc_tc_conv* h, int g, long group_pitc
   if (!h || h->halo != 2 || g < 2 || g > 8) return (int)cudaErrorInvalidValue;
   WmParams& p = h->wp;
   if (!p.tma_store || p.coutp % g || p.out2 || p.dil != 1 || (group_pitch & 7)) return (int)cudaErrorInvalidValue;
+  if (p.ks2pass) {                               // the split-K reduce pass writes plain NHWC slices: grouped layers run unsplit
+    p.ksplit = 1; p.cps = p.nchunk; p.ks2pass = 0;
+    h->grid = p.num_items < g_num_sms ? p.num_items : g_num_sms;
+  }
   EncodeTiledFn enc = get_encode_tiled();
   if (!enc) return (int)cudaErrorNotSupported;
   const int cg = p.coutp / g;
@@ -708,6 +743,11 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
     else if (h->wp.has_kk) PWC_WM_LAUNCH(3);
     else PWC_WM_LAUNCH(0);
 #undef PWC_WM_LAUNCH
+    if (h->wp.ks2pass) {
+      const long total = (long)h->wp.num_items * h->wp.npx * (h->wp.coutp >> 2);
+      const unsigned nb = (unsigned)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+      pwc::launch_pdl(pwc::wm_splitk_reduce_kernel, dim3(nb), dim3(256), 0, st, h->wp);
+    }
     return (int)cudaGetLastError();
   }
   if (h->halo) {
@@ -766,6 +806,7 @@ extern "C" int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* h, int ksplit
   using namespace pwc;
   if (!h || h->halo != 2) return (int)cudaErrorInvalidValue;
   WmParams p = h->wp;                                               // by-value copy: the handle itself is not modified
+  p.ks2pass = 0;                                                    // this entry point runs the one-pass (atomic) form
   if (!p.wstore || p.ts || p.nchunk < 2 || ksplit < 0 || p.out_lo_off) {
     fprintf(stderr, "pwc_tc_conv_launch_static_splitk: the layer has no split-K form (needs >= 2 channel chunks, "
                     "16-bit per-warp output stores, no tap stacking)\n");

@@ -23,6 +23,9 @@ struct WmParams {
   int cout, coutp, kc, nchunk, rows, npx;       // npx = 8*rows = MMA N
   int ksplit, cps;                                // split-K: ksplit CTAs share one pixel tile, cps chunks each; partial sums
   float* scratch; int* counters;                  // meet in an fp32 scratch (red.add), the last CTA to arrive finishes the tile
+  int ks2pass;                                    // deterministic form: every CTA stores its partial tile to its own scratch
+                                                  // slab [ks][item][pixel][128 ch]; wm_splitk_reduce_kernel sums the slabs in
+                                                  // order and does bias / LeakyReLU / 16-bit (hi | lo) stores
   int x_stages;                                   // halo-tile pipeline depth (2 for big tiles, up to 4 for small ones)
   int cin_span, tps, rep, cg;                   // tps: taps per weight stage (1|3|9); rep: weight-tile replicas on M
                                                 // (lane groups rep*cg <= 4 hold the same channels -> epilogue splits pixels)
@@ -343,7 +346,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
                 if (c0 + q * 16 < R * 8) {
 #pragma unroll
                   for (int i = 0; i < 16; ++i)
-                    if (c0 + q * 16 + i < R * 8) atomicAdd(scr + (size_t)(c0 + q * 16 + i) * 128, __uint_as_float(v[q][i]));
+                    if (c0 + q * 16 + i < R * 8) {
+                      if (p.ks2pass) __stcg(scr + (size_t)ks * p.num_items * p.npx * 128 + (size_t)(c0 + q * 16 + i) * 128, __uint_as_float(v[q][i]));
+                      else atomicAdd(scr + (size_t)(c0 + q * 16 + i) * 128, __uint_as_float(v[q][i]));
+                    }
                 }
             }
           }
@@ -351,6 +357,10 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(t_empty(acc));
+          if (p.ks2pass) {                                   // the reduce kernel finishes the tile
+            if (++acc == 2) { acc = 0; tph ^= 1; }
+            continue;
+          }
           __threadfence();
           named_bar(2, 128);
           if (threadIdx.x == 64) {
@@ -515,6 +525,47 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+// Second pass of the deterministic split-K (WmParams::ks2pass): out[pixel][c] = act(bias[c] + sum_ks partial[ks][item][pixel][c]),
+// slabs summed in ks order; thread = (pixel of an item, 4 output channels).  dil == 1 layers only.
+__global__ void __launch_bounds__(256) wm_splitk_reduce_kernel(const WmParams p) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int cq = p.coutp >> 2;
+  const long total = (long)p.num_items * p.npx * cq;
+  const size_t slab = (size_t)p.num_items * p.npx * 128;
+  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (long)gridDim.x * blockDim.x) {
+    const int c4 = (int)(e % cq); const long r = e / cq;
+    const int pix = (int)(r % p.npx), item = (int)(r / p.npx);
+    const int n = item / p.tiles_per_img, t = item - n * p.tiles_per_img;
+    const int oy = (t / p.tiles_x) * p.rows + (pix >> 3), ox = (t % p.tiles_x) * 8 + (pix & 7);
+    if (oy >= p.H || ox >= p.W) continue;
+    const float* src = p.scratch + ((size_t)item * p.npx + pix) * 128 + 4 * c4;
+    float4 a = __ldcg(reinterpret_cast<const float4*>(src));
+    for (int ks = 1; ks < p.ksplit; ++ks) {
+      const float4 b = __ldcg(reinterpret_cast<const float4*>(src + ks * slab));
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    const int c = 4 * c4;
+    float v[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[i] += (c + i < p.cout) ? __ldg(p.bias + c + i) : 0.f;
+      v[i] = fmaxf(v[i], v[i] * p.slope);
+    }
+    const bool second = (n >= p.n_split) && (p.out2 != nullptr);
+    const int nn = second ? n - p.n_split : n;
+    uint16_t* o = second ? reinterpret_cast<uint16_t*>(p.out2) + (((long)nn * p.H + oy) * p.W + ox) * p.out2_pitch + p.out2_coff
+                         : reinterpret_cast<uint16_t*>(p.out) + (((long)nn * p.H + oy) * p.W + ox) * p.out_pitch + p.out_coff;
+    const uint32_t h0 = pack2_h16(v[0], v[1], p.fp16), h1 = pack2_h16(v[2], v[3], p.fp16);
+    *reinterpret_cast<uint2*>(o + c) = make_uint2(h0, h1);
+    if (p.out_lo_off) {
+      const float2 f0 = unpack2_h16(h0, p.fp16), f1 = unpack2_h16(h1, p.fp16);
+      *reinterpret_cast<uint2*>(o + c + p.out_lo_off) =
+          make_uint2(pack2_h16(v[0] - f0.x, v[1] - f0.y, p.fp16), pack2_h16(v[2] - f1.x, v[3] - f1.y, p.fp16));
+    }
+  }
 }
 
 }  // namespace pwc

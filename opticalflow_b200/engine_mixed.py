@@ -7,7 +7,9 @@ amplified by five coarse-to-fine warps), most of the rest from the level 4-6 dec
 of each decoder.  The cost volume itself tolerates half inputs (0.0005 px).  So this plan keeps, in SPLIT precision (two
 half planes hi + lo per tensor, three tensor-core products per K step: include/pwc_b200.h "Split precision"):
   * the whole feature pyramid (conv1a .. conv6b) -- the cost volumes and the c1 decoder inputs read its hi plane;
-  * the level 6, 5, 4 decoders (conv{6,5,4}_0..4), their flow / upfeat heads and concat buffers;
+  * the level 5 and 4 decoders (conv{5,4}_0..4), their flow / upfeat heads and concat buffers (measured on the B200, mean
+    EPE delta at 1024x448 for three inputs: no split decoder level 0.0196 / 0.0133 / 0.0194 px, level 4 only 0.0160 / 0.0110 /
+    0.0159, levels 5+4 0.0131 / 0.0091 / 0.0130, levels 6+5+4 0.0130 / 0.0090 / 0.0127: level 6 buys nothing);
   * up_flow / up_feat of levels 3 and 2, as three 16-bit copies (hi, lo, hi) in the spare channels of the concat buffer
     ("K padding": the single-precision consumers read them with weights W_hi, W_hi, W_lo);
 and runs the level 3 / 2 decoders and the context network -- 80% of the FLOPs -- as the 'f16' plan does.
@@ -25,7 +27,9 @@ from .engine import (C1_OFF, CORR_OFF, DC, DEC_START, DEC_WRITE, FLOW_SCALE, PYR
 from .engine_bf16 import PlanBF16, _TcLayer, _pfup_weights, _roundup, _s2d_weights, S2D_DEC, S2D_DEC_MAXCOUT, S2D_DEC_MAXLVL
 
 CPM = [4, 16, 32, 64, 96, 128, 224]     # channels per PLANE of the pyramid tensors (level 6: 196 -> 128 + 96 output groups)
-SPLIT_LEVELS = (6, 5, 4)                # decoder levels kept in split precision
+import os
+# decoder levels kept in split precision (PWC_MIXED_LEVELS: error-budget experiments, see the module docstring)
+SPLIT_LEVELS = tuple(int(v) for v in os.environ.get("PWC_MIXED_LEVELS", "5,4").split(",") if v)
 KP_LO, KP_DUP = 4, 8                    # K padding: lo copies of up_flow|up_feat at +4 (533..536), second hi copies at +8
 
 
@@ -168,6 +172,9 @@ class PlanMixed(PlanBF16):
                     self._tc(key, len(cm), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w, cmap=cm,
                              in_lo=lo, out_lo=lo, no_small=True)
                     continue
+                if l == 6:                                  # no up_flow / up_feat inputs at the coarsest level: the f16 plan's layer
+                    self._tc(key, len(cm), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w, cmap=cm)
+                    continue
                 kp, cme = _kpad(key, l, DEC_START[k])
                 kpf = (lambda f: (lambda sd: f(sd, self.hdt)))(kp)
                 g = 128 // cout
@@ -189,6 +196,9 @@ class PlanMixed(PlanBF16):
                     self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
                              dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True, in_lo=lo, up_lo=up_lo,
                              up_dup=up_dup)
+                elif l == 6:
+                    self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
+                             dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True, up_lo=up_lo, up_dup=up_dup)
                 else:
                     kp, cme = _kpad(_pfup_weights(l), l, 0)
                     self._tc(f"pfup{l}", len(cme), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cme, out_f32=2,

@@ -215,14 +215,19 @@ def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, spli
     if split_in:
         xin[..., P:P + cin] = lo
     w32 = weight.detach().float().contiguous()
-    if split_in:
+    import os
+    fused = split_in and stride == 2 and P == span == kc and kc <= 32 and os.environ.get("PWC_TC_FUSED_SPLIT", "1") != "0"
+    kc_pack = kc
+    if fused:                                   # adjacent planes in one swizzle row (TcConvParams::fused): [W_hi|W_hi], [W_lo|0]
+        wv, cm, vspan, kc_pack = torch.cat([w32, w32, S.residual(w32, dt)], 1).contiguous(), list(range(3 * cin)), 4 * span, 2 * span
+    elif split_in:
         wv, cm, vspan = S.virtual_weights(w32.cpu(), dt, kc, span)
         wv = wv.to(dev)
     else:
         wv, cm, vspan = w32, list(range(cin)), (span + kc - 1) // kc * kc
     wp = torch.zeros(9 * vspan * coutp, device=dev, dtype=dt)
     mp = torch.tensor(cm, device=dev, dtype=torch.int32)
-    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wv), _lib.ptr(wp), _lib.ptr(mp), cout, wv.shape[1], vspan, kc, coutp, st), "pack")
+    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wv), _lib.ptr(wp), _lib.ptr(mp), cout, wv.shape[1], vspan, kc_pack, coutp, st), "pack")
     ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     out = torch.zeros(N, ho, wo, 2 * coutp if split_out else coutp, device=dev, dtype=dt)
     b32 = bias.detach().float().contiguous()
