@@ -208,6 +208,8 @@ int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* handle, int ksplit, void
  *       in_lo_off  != 0 : the input is split; w_packed then holds THREE 64-channel weight chunks per logical chunk ch, in
  *                         the order 3ch: W_hi (for x_hi), 3ch+1: W_lo (for x_hi), 3ch+2: W_hi (for x_lo): pack a virtual
  *                         [Cout, 3*Cin] tensor with cin_span = 3*kc*ceil(span/kc).  cin_span here stays the logical span.
+ *       in_lo_off  <  0 : split ACTIVATIONS only, lo plane at -in_lo_off: two chunks per logical chunk, 2ch: W_hi (for x_hi),
+ *                         2ch+1: W_hi (for x_lo) -- weights in single precision (the level 5/4 decoders: costs 0.002 px).
  *       out_lo_off != 0 : the 16-bit output is stored as both planes (out_coff + c and out_coff + out_lo_off + c).
  *       up_lo_off / up_dup_off (out_f32 == 2 only): the fused upfeat outputs also go to out2_coff + up_lo_off + j (lo plane)
  *                         and out2_coff + up_dup_off + j (second copy of hi; see pwc_deconv4x4s2_c2_split_fwd).

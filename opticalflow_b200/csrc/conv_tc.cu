@@ -109,7 +109,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             if (ptx::elect_one()) {
               const uint32_t sa = base + s * p.stage_bytes;
               ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (uint32_t)p.coutp * p.kc * 2);
-              ptx::tma_load_4d(sa, tmA, full_bar(s), p.split ? (ch / 3) * p.kc + ((ch % 3) == 2 ? p.lo_off : 0) : ch * p.kc, x, y, nn);
+              ptx::tma_load_4d(sa, tmA, full_bar(s), p.split ? (ch / p.split) * p.kc + ((ch % p.split) == p.split - 1 ? p.lo_off : 0) : ch * p.kc, x, y, nn);
               ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * p.nchunk + ch) * p.coutp);
             }
             __syncwarp();
@@ -262,8 +262,8 @@ __global__ void pack_conv_weight_bf16_kernel(const float* __restrict__ wt, __nv_
 static int g_num_sms = 0;
 static thread_local int g_half_format = 0;        // 0 = bf16, 1 = IEEE half (pwc_set_half_format)
 // split-precision options of the create call in progress (pwc_tc_conv_create_split sets them around pwc_tc_conv_create)
-struct SplitOpts { int in_lo_off, out_lo_off, up_lo_off, up_dup_off; };
-static thread_local SplitOpts g_split = {0, 0, 0, 0};
+struct SplitOpts { int in_lo_off, out_lo_off, up_lo_off, up_dup_off, products; };
+static thread_local SplitOpts g_split = {0, 0, 0, 0, 3};
 int half_format() { return g_half_format; }
 
 static int env_int(const char* name, int dflt) {
@@ -377,9 +377,9 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   for (int i = 0; i < 9; ++i) p.kk_mask[i] = 0;
   for (int i = 0; i < 9; ++i) p.skip[i] = 0ull;
   p.N = N; p.H = H; p.W = W; p.dil = dil;
-  p.split = g_split.in_lo_off ? 1 : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
+  p.split = g_split.in_lo_off ? g_split.products : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
   p.up_lo_off = g_split.up_lo_off; p.up_dup_off = g_split.up_dup_off;
-  const int vmul = p.split ? 3 : 1;                 // virtual chunks per logical chunk (see WmParams::split)
+  const int vmul = p.split ? p.split : 1;           // virtual chunks per logical chunk (see WmParams::split)
   p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc) * vmul;
   if ((p.split || p.out_lo_off) && (dil != 1 || kc != 64 || (p.lo_off & 7) || (p.out_lo_off & 7))) { delete h; return (int)cudaErrorInvalidValue; }
   // large dilations: phases in x only, the y dilation is a row shift inside a (rows + 2*dil)-row halo tile -- 16 x fewer,
@@ -626,10 +626,10 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   TcConvParams& p = h->p;
   p.N = N; p.Hin = Hin; p.Win = Win; p.stride = stride; p.dil = dil;
   p.Hout = (Hin - 1) / stride + 1; p.Wout = (Win - 1) / stride + 1;
-  p.split = g_split.in_lo_off ? 1 : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
+  p.split = g_split.in_lo_off ? g_split.products : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
   if ((p.lo_off & 7) || (p.out_lo_off & 7) || (p.out_lo_off && out_f32)) { delete h; return (int)cudaErrorInvalidValue; }
-  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = (cin_span / kc) * (p.split ? 3 : 1);
-  p.fused = (p.split && p.lo_off == cin_span && cin_span == kc && kc <= 32 && env_int("PWC_TC_FUSED_SPLIT", 1)) ? 1 : 0;
+  p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = (cin_span / kc) * (p.split ? p.split : 1);
+  p.fused = (p.split == 3 && p.lo_off == cin_span && cin_span == kc && kc <= 32 && env_int("PWC_TC_FUSED_SPLIT", 1)) ? 1 : 0;
   if (p.fused) { p.kc = kc = 2 * kc; p.nchunk = 2; p.split = 0; }      // weights: [tap][2][coutp][2*cin] = [W_hi|W_hi], [W_lo|0]
   p.n_split = (in2 || out2) ? n_split : N;
   p.tiles_x = cdiv(p.Wout, kTcTW); p.tiles_y = cdiv(p.Hout, kTcTH); p.num_tiles = p.tiles_x * p.tiles_y * N;
@@ -771,12 +771,13 @@ extern "C" int pwc_tc_conv_create_split(pwc_tc_conv** handle,
                                         const float* residual, long res_pitch,
                                         int N, int Hin, int Win, int stride, int dil, float slope,
                                         int in_lo_off, int out_lo_off, int up_lo_off, int up_dup_off) {
-  if (in_lo_off < 0 || out_lo_off < 0 || up_lo_off < 0 || up_dup_off < 0) return (int)cudaErrorInvalidValue;
-  pwc::g_split = {in_lo_off, out_lo_off, up_lo_off, up_dup_off};
+  if (out_lo_off < 0 || up_lo_off < 0 || up_dup_off < 0) return (int)cudaErrorInvalidValue;
+  // in_lo_off < 0: split ACTIVATIONS only (two products per K step, x_hi*W_hi + x_lo*W_hi; lo plane at -in_lo_off)
+  pwc::g_split = {in_lo_off < 0 ? -in_lo_off : in_lo_off, out_lo_off, up_lo_off, up_dup_off, in_lo_off < 0 ? 2 : 3};
   const int e = pwc_tc_conv_create(handle, in, in_pitch, in_coff, in2, in2_pitch, in2_coff, n_split, cin_span, kc, w_packed, bias,
                                    cout, coutp, out, out_pitch, out_coff, out2, out2_pitch, out2_coff, out_f32, residual,
                                    res_pitch, N, Hin, Win, stride, dil, slope);
-  pwc::g_split = {0, 0, 0, 0};
+  pwc::g_split = {0, 0, 0, 0, 3};
   return e;
 }
 

@@ -38,7 +38,8 @@ struct WmParams {
   // split precision (conv_mode 'mixed'): an fp32-grade tensor is stored as two 16-bit planes of the same pixel row, hi = RN16(v)
   // at channel c and lo = RN16(v - hi) at channel c + lo_off.  split != 0: nchunk counts VIRTUAL chunks, three per logical
   // 64-channel chunk -- (x_hi, W_hi), (x_hi, W_lo), (x_lo, W_hi) -- whose products meet in the same fp32 accumulator (the
-  // dropped x_lo * W_lo term is 2^-22 relative).  out_lo_off != 0: the epilogue stores both planes of its output.
+  // dropped x_lo * W_lo term is 2^-22 relative).  split == 2: two virtual chunks, (x_hi, W_hi), (x_lo, W_hi): split activations,
+  // single-precision weights.  out_lo_off != 0: the epilogue stores both planes of its output.
   int split, lo_off, out_lo_off;
   int up_lo_off, up_dup_off;                      // fused upfeat outputs (out_f32 == 2): lo plane / second hi copy, 0 = none
   unsigned long long skip[9];                    // bit ch of skip[tap]: weight block (tap, chunk ch) is all zero -> no load, no MMA
@@ -146,7 +147,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         if (ch == ch_lo) wm_mark(trp, 0, it_idx, 1);
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
-          const int xc = p.split ? (ch / 3) * p.kc + ((ch % 3) == 2 ? p.lo_off : 0) : ch * p.kc;
+          const int xc = p.split ? (ch / p.split) * p.kc + ((ch % p.split) == p.split - 1 ? p.lo_off : 0) : ch * p.kc;
           if (p.xsplit) ptx::tma_load_5d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, rx, tx0 - 1, ya, n);
           else ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, xa, ya, n);
         }
@@ -193,7 +194,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         ptx::tc_fence_after();
         if (ch == ch_lo) wm_mark(trm, 1, it_idx, 2);
         const uint32_t sx = x_base + xb * p.x_bytes;
-        const int nkk = min(p.kc, p.cin_span - (p.split ? ch / 3 : ch) * p.kc + 15) >> 4;     // K=16 steps holding real channels
+        const int nkk = min(p.kc, p.cin_span - (p.split ? ch / p.split : ch) * p.kc + 15) >> 4;     // K=16 steps holding real channels
         const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
         int ftap = 0;                                        // first tap actually issued for this chunk
         if ((kMode == 2)) while (ftap < 8 && ((p.skip[ftap] >> ch) & 1ull)) ++ftap;

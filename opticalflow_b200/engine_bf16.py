@@ -113,7 +113,7 @@ THIN_LAYERS = set(x for x in os.environ.get("PWC_THIN_LAYERS", "conv1aa.0,conv1b
 
 class _TcLayer:
     __slots__ = ("key", "w", "b", "handle", "cmap", "cin", "cout", "span", "kc", "coutp", "wfn", "wrows", "groups", "kkskip",
-                 "masks_set", "split_in", "kpad", "mask_key", "fused")
+                 "masks_set", "split_in", "kpad", "mask_key", "fused", "products")
 
 
 class PlanBF16:
@@ -213,13 +213,14 @@ class PlanBF16:
         L.kc = pick_kc(span, stride, dil, src2 is not None, W=win, coutp=L.coutp, out_f32=bool(out_f32) or dst2 is not None)
         L.wrows = 128 if ts else cout                   # rows of the weight tensor handed to the packer
         L.split_in, L.kpad, L.mask_key = bool(in_lo), kpad, key
+        L.products = 2 if in_lo < 0 else 3                # in_lo < 0: split activations only (lo plane at -in_lo)
         # adjacent [hi | lo] planes that fit one swizzle row run the fused form of the stride-2 kernel (TcConvParams::fused)
-        L.fused = bool(in_lo) and stride == 2 and in_lo == span == L.kc and L.kc <= 32 and cmap is None and \
+        L.fused = in_lo > 0 and stride == 2 and in_lo == span == L.kc and L.kc <= 32 and cmap is None and \
             os.environ.get("PWC_TC_FUSED_SPLIT", "1") != "0"
         if out_lo:
             L.coutp = _roundup(cout, 32)                  # split stores exist in the per-warp (32-channel group) store path
         dev = self.device
-        L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp * ((4 if L.fused else 3) if in_lo else 1), device=dev, dtype=self.hdt)
+        L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp * ((4 if L.fused else L.products) if in_lo else 1), device=dev, dtype=self.hdt)
         L.b = torch.zeros(cout, device=dev, dtype=torch.float32)
         h = ctypes.c_void_p()
         args = (ctypes.byref(h), _lib.ptr(src), src.shape[-1], src_coff,
@@ -463,7 +464,7 @@ class PlanBF16:
                 span_pack, kc_pack = 4 * L.span, 2 * L.span
             elif getattr(L, "split_in", False):
                 # split-precision input: three weight chunks per logical chunk (W_hi | W_lo | W_hi), see split.virtual_weights
-                wt, cm, span_pack = S.virtual_weights(wt, self.hdt, L.kc, L.span, cm)
+                wt, cm, span_pack = S.virtual_weights(wt, self.hdt, L.kc, L.span, cm, L.products)
             mp = None
             if cm is not None:
                 mp = torch.tensor(cm, device=dev, dtype=torch.int32); keep.append(mp)

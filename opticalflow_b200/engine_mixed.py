@@ -30,6 +30,10 @@ CPM = [4, 16, 32, 64, 96, 128, 224]     # channels per PLANE of the pyramid tens
 import os
 # decoder levels kept in split precision (PWC_MIXED_LEVELS: error-budget experiments, see the module docstring)
 SPLIT_LEVELS = tuple(int(v) for v in os.environ.get("PWC_MIXED_LEVELS", "5,4").split(",") if v)
+# the split decoder levels keep their WEIGHTS in single precision (two products per K step instead of three): measured on
+# the B200 0.0131 -> 0.0149 / 0.0091 -> 0.0103 / 0.0130 -> 0.0151 px at 1024x448 for a third less tensor work there; dropping
+# W_lo in the pyramid instead costs 0.025-0.028 px (PWC_MIXED_DEC_PRODUCTS=3 restores the full split)
+DEC_PRODUCTS = int(os.environ.get("PWC_MIXED_DEC_PRODUCTS", "2"))
 KP_LO, KP_DUP = 4, 8                    # K padding: lo copies of up_flow|up_feat at +4 (533..536), second hi copies at +8
 
 
@@ -170,7 +174,7 @@ class PlanMixed(PlanBF16):
                 key = f"conv{l}_{k}.0"
                 if sp:
                     self._tc(key, len(cm), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w, cmap=cm,
-                             in_lo=lo, out_lo=lo, no_small=True)
+                             in_lo=(-lo if DEC_PRODUCTS == 2 else lo), out_lo=lo, no_small=True)
                     continue
                 if l == 6:                                  # no up_flow / up_feat inputs at the coarsest level: the f16 plan's layer
                     self._tc(key, len(cm), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w, cmap=cm)
@@ -194,8 +198,8 @@ class PlanMixed(PlanBF16):
                 up_lo, up_dup = (twd, 0) if tsp else (KP_LO, KP_DUP)
                 if sp:
                     self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
-                             dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True, in_lo=lo, up_lo=up_lo,
-                             up_dup=up_dup)
+                             dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True,
+                             in_lo=lo, up_lo=up_lo, up_dup=up_dup)     # the flow / upfeat heads keep all three products
                 elif l == 6:
                     self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
                              dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True, up_lo=up_lo, up_dup=up_dup)

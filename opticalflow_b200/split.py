@@ -16,16 +16,18 @@ def residual(w, dtype):
     return w - w.to(dtype).float()
 
 
-def virtual_weights(w, dtype, kc, span, cmap=None):
+def virtual_weights(w, dtype, kc, span, cmap=None, products=3):
     """w [rows, cin, 3, 3] fp32 whose input channel i sits at position cmap[i] (default i) of a `span`-channel slice that the
     kernel walks in chunks of kc.  Returns (w_virtual [rows, 3*cin, 3, 3], cmap_virtual, span_virtual) for
     pwc_pack_conv_weight_bf16: virtual chunk 3*ch multiplies x_hi by W_hi, 3*ch+1 x_hi by W_lo, 3*ch+2 x_lo by W_hi."""
     cin = w.shape[1]
     pos = torch.arange(cin) if cmap is None else torch.as_tensor(cmap, dtype=torch.long)
     ch, k = pos // kc, pos % kc
+    nch = (span + kc - 1) // kc
+    if products == 2:        # split activations, single-precision weights: 2*ch multiplies x_hi by W_hi, 2*ch+1 x_lo by W_hi
+        return torch.cat([w, w], 1).contiguous(), torch.cat([(2 * ch) * kc + k, (2 * ch + 1) * kc + k]).tolist(), 2 * kc * nch
     wv = torch.cat([w, residual(w, dtype), w], 1).contiguous()
     cm = torch.cat([(3 * ch) * kc + k, (3 * ch + 1) * kc + k, (3 * ch + 2) * kc + k]).tolist()
-    nch = (span + kc - 1) // kc
     return wv, cm, 3 * kc * nch
 
 
