@@ -63,6 +63,20 @@ __device__ __forceinline__ void tc_decode(const WarpCorrTcParams& p, int item, i
   T = q + (rg < rem ? 1 : 0);
 }
 
+// LeakyReLU (0 <= slope <= 1) of two packed 16-bit values: max(x, x*s1 + x*s2) with s1 + s2 = slope to ~2^-20
+template <bool F16>
+__device__ __forceinline__ uint32_t tc_lrelu2(uint32_t x, uint32_t s1, uint32_t s2) {
+  if (F16) {
+    const __half2 v = *reinterpret_cast<const __half2*>(&x);
+    const __half2 y = __hmax2(v, __hfma2(v, *reinterpret_cast<const __half2*>(&s1), __hmul2(v, *reinterpret_cast<const __half2*>(&s2))));
+    return *reinterpret_cast<const uint32_t*>(&y);
+  }
+  const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(&x);
+  const __nv_bfloat162 y = __hmax2(v, __hfma2(v, *reinterpret_cast<const __nv_bfloat162*>(&s1),
+                                            __hmul2(v, *reinterpret_cast<const __nv_bfloat162*>(&s2))));
+  return *reinterpret_cast<const uint32_t*>(&y);
+}
+
 template <bool F16>
 __global__ void __launch_bounds__(kTcThreads, 1)
 warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_constant__ CUtensorMap tmOut,
@@ -178,8 +192,14 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
     const int q = warp & 3;                               // TMEM lane quarter = tile row
     uint16_t* stg = stg_all + q * 32 * kTcStgStride;
     const uint32_t stg_addr = a_base + 2 * kTcABytes + kTcScrBytes + (uint32_t)(q * 32 * kTcStgStride * 2);
-    const float rc = __frcp_rn((float)C);
     const bool b16 = lane & 16, b8 = lane & 8, b4 = lane & 4, b2 = lane & 2, b1 = lane & 1;
+    // byte-permute selectors of the last shifter level (lane parity): even / odd channel position, carry, merge with the carry
+    const uint32_t selE = b1 ? 0x5432u : 0x3210u, selO = b1 ? 0x7654u : 0x5432u;
+    const uint32_t selC = b1 ? 0x4432u : 0x4410u, selM = b1 ? 0x7610u : 0x5410u;
+    // LeakyReLU slope as hi + lo of the storage format, both halves of a packed register
+    const uint32_t sl1 = pack2_h16(g.slope, g.slope, F16);
+    const float sl1f = unpack2_h16(sl1, F16).x;
+    const uint32_t sl2 = pack2_h16(g.slope - sl1f, g.slope - sl1f, F16);
     int db = 0; uint32_t dph = 0;
     int tcount = 0;
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
@@ -189,9 +209,16 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
         const int y = (ty0 + t) * kTcR + q;
         const bool tr = p.dbg && blockIdx.x == 0 && warp == 2 && lane == 0;
         const bool tr2 = tr && tcount == 2;
-        float carry[8];                                   // channels not yet forming a full 16-byte chunk
+        // The epilogue works on PACKED 16-bit pairs: the 40 accumulator columns of a (row, dy) are rounded to the storage
+        // format first (the 1/C scale is folded into the gather weights, exact for C = 16 / 32 / 64), then the band [lane+j],
+        // j = 0..8, is extracted by a 4-level barrel shifter on 20 packed registers (31 selects) plus one byte permute per
+        // output word (the lane's parity and the parity of the channel position 9*dy pick the halves) -- 36 instead of 71
+        // selects per 9 outputs -- and LeakyReLU runs on packed words (HMUL2 + HFMA2 + HMNMX2 per two channels, the slope
+        // as a two-term sum so that the product is correctly rounded).  ow[] = the pixel's 80 channels, 40 words.
+        uint32_t ow[40];
+        uint32_t carry = 0;                               // a 9-element group ends on an odd position every other dy
         uint16_t ch80 = 0;
-        uint16_t* srow = stg + lane * kTcStgStride;       // this lane's pixel: [81] bf16, 176-byte rows
+        uint16_t* srow = stg + lane * kTcStgStride;       // this lane's pixel: [80] halfwords, 160-byte rows
 #pragma unroll
         for (int ps = 0; ps < 3; ++ps) {
           if (ps == 0) tc_mark(tr, 2, tcount, 0);
@@ -199,17 +226,12 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
           ptx::tc_fence_after();
           if (ps == 0) tc_mark(tr, 2, tcount, 1);
           if (ps == 2) tc_mark(tr, 2, tcount, 2);
-          constexpr int kNcTab[3] = {0, 3, 6};
-          const int nc = kNcTab[ps];                      // carried values: channels 27*ps - nc .. 27*ps - 1
-          float pend[36];
-#pragma unroll
-          for (int i = 0; i < 6; ++i) if (i < nc) pend[i] = carry[i];
 #pragma unroll
           for (int d = 0; d < 3; ++d) {
             tc_mark(tr2, 2, 20 + 3 * ps + d, 0);
             // tile row q at displacement dy = 3*ps + d reads window row q + d, columns lane .. lane+8 of its 40
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(db * 256 + (q + d) * kTcBW);
-            uint32_t v[40];
+            uint32_t P[20];
             {
               uint32_t v0[16], v1[16], v2[8];
               ptx::tmem_ld16(taddr, v0);
@@ -217,9 +239,12 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
               ptx::tmem_ld8(taddr + 32, v2);
               ptx::tmem_ld_wait();
 #pragma unroll
-              for (int i = 0; i < 16; ++i) { v[i] = v0[i]; v[16 + i] = v1[i]; }
+              for (int i = 0; i < 8; ++i) {
+                P[i] = pack2_h16(__uint_as_float(v0[2 * i]), __uint_as_float(v0[2 * i + 1]), F16);
+                P[8 + i] = pack2_h16(__uint_as_float(v1[2 * i]), __uint_as_float(v1[2 * i + 1]), F16);
+              }
 #pragma unroll
-              for (int i = 0; i < 8; ++i) v[32 + i] = v2[i];
+              for (int i = 0; i < 4; ++i) P[16 + i] = pack2_h16(__uint_as_float(v2[2 * i]), __uint_as_float(v2[2 * i + 1]), F16);
             }
             tc_mark(tr2, 2, 20 + 3 * ps + d, 1);
             if (d == 2) {                                 // accumulator buffer fully read: hand it back to the MMA warp
@@ -227,45 +252,36 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
               __syncwarp();
               if (lane == 0) ptx::mbar_arrive(d_empty(db));
             }
-            // band extraction in registers: a 5-level barrel shifter on the lane index (71 selects, no shared memory)
-            uint32_t s1[24], s2[16], s3[12], s4[10];
+            uint32_t s1[12], s2[8], s3[6], s4[5];
 #pragma unroll
-            for (int i = 0; i < 24; ++i) s1[i] = b16 ? v[i + 16] : v[i];
+            for (int i = 0; i < 12; ++i) s1[i] = b16 ? P[i + 8] : P[i];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) s2[i] = b8 ? s1[i + 8] : s1[i];
+            for (int i = 0; i < 8; ++i) s2[i] = b8 ? s1[i + 4] : s1[i];
 #pragma unroll
-            for (int i = 0; i < 12; ++i) s3[i] = b4 ? s2[i + 4] : s2[i];
+            for (int i = 0; i < 6; ++i) s3[i] = b4 ? s2[i + 2] : s2[i];
 #pragma unroll
-            for (int i = 0; i < 10; ++i) s4[i] = b2 ? s3[i + 2] : s3[i];
+            for (int i = 0; i < 5; ++i) s4[i] = b2 ? s3[i + 1] : s3[i];
+            const int dy = 3 * ps + d, pos = 9 * dy;      // compile time
+            if ((pos & 1) == 0) {
 #pragma unroll
-            for (int j = 0; j < 9; ++j) {
-              const float q1 = __uint_as_float(b1 ? s4[j + 1] : s4[j]) * rc;   // RN(1/C) multiply (bf16 output)
-              pend[nc + d * 9 + j] = fmaxf(q1, q1 * g.slope);
+              for (int k = 0; k < 4; ++k) ow[pos / 2 + k] = tc_lrelu2<F16>(__byte_perm(s4[k], s4[k + 1], selE), sl1, sl2);
+              carry = __byte_perm(s4[4], 0u, selC);       // element 8 in the low half
+            } else {
+              ow[(pos - 1) / 2] = tc_lrelu2<F16>(__byte_perm(carry, s4[0], selM), sl1, sl2);
+#pragma unroll
+              for (int k = 1; k < 5; ++k) ow[(pos - 1) / 2 + k] = tc_lrelu2<F16>(__byte_perm(s4[k - 1], s4[k], selO), sl1, sl2);
             }
             tc_mark(tr2, 2, 20 + 3 * ps + d, 3);
           }
-          // 16-byte chunks of 8 channels -> this lane's staged row (conflict-free STS.128)
-          if (ps == 0) {                                  // the previous tile's TMA store has read the staging rows
-            if (lane == 0) ptx::bulk_wait_read0();
-            __syncwarp();
-          }
-          const int npend = nc + 27, nchunk = npend / 8, chunk0 = (27 * ps - nc) / 8;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            if (k < nchunk) {
-              uint32_t w[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) w[e] = pack2_h16(pend[8 * k + 2 * e], pend[8 * k + 2 * e + 1], F16);
-              *reinterpret_cast<uint4*>(srow + (chunk0 + k) * 8) = make_uint4(w[0], w[1], w[2], w[3]);
-            }
-          }
-#pragma unroll
-          for (int i = 0; i < 6; ++i) if (8 * nchunk + i < npend) carry[i] = pend[8 * nchunk + i];
-          if (ps == 2) {                                  // channel 80 goes out from the register
-            ch80 = pack1_h16(pend[32], F16);
-          }
           if (++db == 2) { db = 0; dph ^= 1; }
         }
+        ch80 = (uint16_t)(tc_lrelu2<F16>(carry, sl1, sl2) & 0xffffu);      // channel 80 goes out from the register
+        // the previous tile's TMA store has read the staging rows: now this lane's row may be rewritten (conflict-free STS.128)
+        if (lane == 0) ptx::bulk_wait_read0();
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 10; ++k)
+          *reinterpret_cast<uint4*>(srow + 8 * k) = make_uint4(ow[4 * k], ow[4 * k + 1], ow[4 * k + 2], ow[4 * k + 3]);
         // ---- write-out: the warp's 32 pixels x 80 channels leave as ONE TMA tensor store (box 160 B x 32 px, clipped
         //      at the image edge) into the concat slice; channel 80 is stored from the register ----
         tc_mark(tr2, 2, 40, 0);
@@ -296,6 +312,7 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
     uint2* txy = tabxy + team * kTcN;
     const __nv_bfloat16* f2 = reinterpret_cast<const __nv_bfloat16*>(g.f2);
     const int sh = (C == 64) ? 3 : (C == 32) ? 2 : 1;     // 16-byte channel groups per pixel = 1 << sh
+    const float rcC = 1.0f / (float)C;
     const int ntask = kTcN << sh;
     int gcount = 0;
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
@@ -323,6 +340,9 @@ warp_corr_tc_kernel(const __grid_constant__ CUtensorMap tmF1, const __grid_const
               warp_entry(g, fl.x, fl.y, xx, yy, w, xy);
             }
           }
+          // the cost volume's 1/C (correlation_cuda_kernel.cu:143) rides on the warped operand: C is 16, 32 or 64 here, so the
+          // scale is a power of two and commutes with every rounding of the blend and of the dot product
+          w.x *= rcC; w.y *= rcC; w.z *= rcC; w.w *= rcC;
           tw[e] = w; txy[e] = xy;
         }
         named_bar_sync(1 + team, kP);
