@@ -340,6 +340,11 @@ int pwc_preprocess_u8_fwd(const uint8_t* im1, const uint8_t* im2, long img_strid
                           int B, int H, int W, int Hp, int Wp, int swap_rb, float* out, void* stream);
 /* frame-stack variants for consecutive pairs of one video (pair k = frames k, k+1: every frame is converted and run through
  * the feature pyramid ONCE): N uint8 frames -> [N,3,Hp,Wp] fp32, and conv1a on such a stack (N frames -> [N,H/2,W/2,16] bf16). */
+/* ImageNet-normalised variant of the KITTI drivers (T.ToTensor + T.Normalize, inference_kitti.py:175-179, inference.py:305-310):
+ * out = (byte / 255 - mean[c]) / std[c] per output channel c (mean3 / std3: 3 HOST floats), then replicate pad + cat. */
+int pwc_preprocess_u8_norm_fwd(const uint8_t* im1, const uint8_t* im2, long img_stride, long row_stride,
+                               int B, int H, int W, int Hp, int Wp, int swap_rb, const float* mean3, const float* std3,
+                               float* out, void* stream);
 int pwc_preprocess_frames_u8_fwd(const uint8_t* frames, long img_stride, long row_stride,
                                  int N, int H, int W, int Hp, int Wp, int swap_rb, float* out, void* stream);
 int pwc_conv1a_frames_bf16_fwd(const float* frames, const float* w, const float* bias, void* out,

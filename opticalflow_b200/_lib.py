@@ -58,6 +58,7 @@ SIGNATURES = {
                                   _i, _i, _i, _i, _f, _vp]),
     "pwc_conv3x3_flow_head_fwd": (_i, [_vp, _l, _i, _i, _vp, _vp, _vp, _l, _vp, _i, _i, _i, _vp]),
     "pwc_preprocess_u8_fwd": (_i, [_vp, _vp, _l, _l, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "pwc_preprocess_u8_norm_fwd": (_i, [_vp, _vp, _l, _l, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "pwc_preprocess_frames_u8_fwd": (_i, [_vp, _l, _l, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "pwc_conv1a_frames_bf16_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     "pwc_flow_postprocess_fwd": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _i, _f, _i, _vp]),

@@ -14,7 +14,8 @@ namespace pwc {
 // one thread = 4 consecutive output x of one (n, image, y) row, all 3 colour planes: 12 source bytes -> 3 float4 stores
 __global__ void __launch_bounds__(256)
 preprocess_u8_kernel(const uint8_t* __restrict__ im1, const uint8_t* __restrict__ im2, long img_stride, long row_stride,
-                     int B, int H, int W, int Hp, int Wp, int swap_rb, float* __restrict__ out, int pairs) {
+                     int B, int H, int W, int Hp, int Wp, int swap_rb, float* __restrict__ out, int pairs,
+                     int norm, float3 mean, float3 std) {
   // pairs = 1: out [B,6,Hp,Wp] (frame 1 | frame 2 of pair n); pairs = 0: out [B,3,Hp,Wp], a plain frame stack from im1
   const int Wq = Wp >> 2;
   const long total = (long)B * (pairs ? 2 : 1) * Hp * Wq;
@@ -30,6 +31,11 @@ preprocess_u8_kernel(const uint8_t* __restrict__ im1, const uint8_t* __restrict_
       const uint8_t* px = src + 3 * x;
 #pragma unroll
       for (int c = 0; c < 3; ++c) v[c][k] = __fdiv_rn((float)px[swap_rb ? 2 - c : c], 255.0f);        // arr.astype(float32) / 255.0
+      if (norm) {      // T.Normalize after T.ToTensor (inference_kitti.py:175-179, inference.py:305-310): tensor.sub_(mean).div_(std)
+        v[0][k] = __fdiv_rn(__fsub_rn(v[0][k], mean.x), std.x);
+        v[1][k] = __fdiv_rn(__fsub_rn(v[1][k], mean.y), std.y);
+        v[2][k] = __fdiv_rn(__fsub_rn(v[2][k], mean.z), std.z);
+      }
     }
     float* dst = out + (((long)n * (pairs ? 6 : 3) + 3 * im) * Hp + y) * Wp + 4 * xq;
 #pragma unroll
@@ -130,7 +136,22 @@ extern "C" int pwc_preprocess_u8_fwd(const uint8_t* im1, const uint8_t* im2, lon
     return (int)cudaErrorInvalidValue;
   const long work = (long)B * 2 * Hp * (Wp >> 2);
   pwc::preprocess_u8_kernel<<<pwc::grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(
-      im1, im2, img_stride, row_stride, B, H, W, Hp, Wp, swap_rb, out, 1);
+      im1, im2, img_stride, row_stride, B, H, W, Hp, Wp, swap_rb, out, 1, 0, make_float3(0.f, 0.f, 0.f), make_float3(1.f, 1.f, 1.f));
+  return (int)cudaGetLastError();
+}
+
+// The KITTI drivers' variant (inference_kitti.py:175-179, inference.py:305-310): ToTensor (/255) followed by
+// Normalize(mean, std) per OUTPUT channel (after the optional R<->B swap), then replicate pad + cat as above.
+extern "C" int pwc_preprocess_u8_norm_fwd(const uint8_t* im1, const uint8_t* im2, long img_stride, long row_stride,
+                                          int B, int H, int W, int Hp, int Wp, int swap_rb, const float* mean3,
+                                          const float* std3, float* out, void* stream) {
+  if (B <= 0 || H <= 0 || W <= 0 || Hp < H || Wp < W || (Wp & 3) || row_stride < 3L * W || !mean3 || !std3 ||
+      (reinterpret_cast<uintptr_t>(out) & 15))
+    return (int)cudaErrorInvalidValue;
+  const long work = (long)B * 2 * Hp * (Wp >> 2);
+  pwc::preprocess_u8_kernel<<<pwc::grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(
+      im1, im2, img_stride, row_stride, B, H, W, Hp, Wp, swap_rb, out, 1, 1, make_float3(mean3[0], mean3[1], mean3[2]),
+      make_float3(std3[0], std3[1], std3[2]));
   return (int)cudaGetLastError();
 }
 
@@ -141,7 +162,7 @@ extern "C" int pwc_preprocess_frames_u8_fwd(const uint8_t* frames, long img_stri
     return (int)cudaErrorInvalidValue;
   const long work = (long)N * Hp * (Wp >> 2);
   pwc::preprocess_u8_kernel<<<pwc::grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(
-      frames, frames, img_stride, row_stride, N, H, W, Hp, Wp, swap_rb, out, 0);
+      frames, frames, img_stride, row_stride, N, H, W, Hp, Wp, swap_rb, out, 0, 0, make_float3(0.f, 0.f, 0.f), make_float3(1.f, 1.f, 1.f));
   return (int)cudaGetLastError();
 }
 

@@ -26,10 +26,14 @@ def _need_cuda(t, what):
         raise RuntimeError(f"{what}: CUDA tensors required (no CPU fallback)")
 
 
-def frames_to_input(frames1, frames2, swap_rb=True, multiple=64, out=None):
+IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)     # inference_kitti.py:177-178
+
+
+def frames_to_input(frames1, frames2, swap_rb=True, multiple=64, out=None, mean=None, std=None):
     """frames1, frames2: uint8 CUDA tensors [B,H,W,3] (or [H,W,3]) as cv2 delivers them (BGR).  Returns
     (x [B,6,Hp,Wp] fp32, pad_h, pad_w): x[:, :3] = frame 1 / 255 (RGB if swap_rb), x[:, 3:] = frame 2, replicate-padded
-    to multiples of `multiple`."""
+    to multiples of `multiple`.  mean / std (3 floats each, e.g. IMAGENET_MEAN / IMAGENET_STD): the KITTI drivers' variant,
+    T.ToTensor followed by T.Normalize (inference_kitti.py:175-179; their PIL images are RGB: swap_rb=False)."""
     _need_cuda(frames1, "frames_to_input"); _need_cuda(frames2, "frames_to_input")
     if frames1.dim() == 3:
         frames1, frames2 = frames1[None], frames2[None]
@@ -47,6 +51,15 @@ def frames_to_input(frames1, frames2, swap_rb=True, multiple=64, out=None):
     if out is None:
         out = torch.empty(B, 6, Hp, Wp, device=frames1.device, dtype=torch.float32)
     lib = _lib.load()
+    if (mean is None) != (std is None):
+        raise RuntimeError("frames_to_input: mean and std come together")
+    if mean is not None:
+        import ctypes
+        m3, s3 = (ctypes.c_float * 3)(*[float(v) for v in mean]), (ctypes.c_float * 3)(*[float(v) for v in std])
+        e = lib.pwc_preprocess_u8_norm_fwd(_lib.ptr(frames1), _lib.ptr(frames2), img_stride, W * 3, B, H, W, Hp, Wp,
+                                           int(bool(swap_rb)), m3, s3, _lib.ptr(out), _lib.stream_handle())
+        _lib.check(e, "pwc_preprocess_u8_norm_fwd")
+        return out, ph, pw
     e = lib.pwc_preprocess_u8_fwd(_lib.ptr(frames1), _lib.ptr(frames2), img_stride, W * 3, B, H, W, Hp, Wp,
                                   int(bool(swap_rb)), _lib.ptr(out), _lib.stream_handle())
     _lib.check(e, "pwc_preprocess_u8_fwd")

@@ -26,6 +26,27 @@ def frames_to_input(frame1, frame2, swap_rb=True, multiple=64):
     return torch.cat(ts, 1), ph, pw
 
 
+def frames_to_input_normalized(frame1, frame2, mean, std, swap_rb=False, multiple=64):
+    """The KITTI drivers' transform (inference_kitti.py:175-179, inference.py:305-310): T.ToTensor -- HWC uint8 -> CHW,
+    .float().div(255) -- then T.Normalize(mean, std) -- tensor.sub_(mean[:,None,None]).div_(std[:,None,None]) with fp32 mean / std
+    (torchvision.transforms.functional.normalize) --, followed by the replicate pad + cat of model_infer (inference_kitti.py:53-63,
+    216-217).  torchvision is not installed in this image: its two transforms are restated with the torch ops they are made of;
+    PIL delivers RGB, hence swap_rb=False."""
+    m = torch.as_tensor(mean, dtype=torch.float32)[:, None, None]
+    sd = torch.as_tensor(std, dtype=torch.float32)[:, None, None]
+    ts = []
+    for fr in (frame1, frame2):
+        a = np.asarray(fr)
+        if swap_rb:
+            a = a[:, :, ::-1]
+        t = torch.from_numpy(np.ascontiguousarray(a)).permute(2, 0, 1).contiguous().float().div(255)
+        ts.append(t.sub_(m).div_(sd)[None])
+    h, w = ts[0].shape[-2:]
+    ph, pw = (multiple - h % multiple) % multiple, (multiple - w % multiple) % multiple
+    ts = [F.pad(t, (0, pw, 0, ph), mode="replicate") for t in ts]
+    return torch.cat(ts, 1), ph, pw
+
+
 def unpad(x, pad_h, pad_w):
     """inference_kitti.py:66-71."""
     if pad_h == 0 and pad_w == 0:

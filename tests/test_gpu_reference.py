@@ -80,3 +80,49 @@ def test_fp32_forward_vs_reference_eager_on_gpu(shape):
         cpu = O.forward({k: v.cpu() for k, v in sd.items()}, x)
         assert 20.0 * (ref - cpu).abs().max().item() <= 1e-3               # the two oracles agree (px on the x20 flow)
         assert 20.0 * (got - ref).abs().max().item() <= 1e-3               # product fp32 mode == reference on the GPU
+
+
+def _reference_correlation_over_the_shim():
+    """the UNMODIFIED reference correlation.py, bound to opticalflow_b200.correlation_cuda instead of the pybind extension"""
+    import importlib.util
+    import os
+    import sys
+    from opticalflow_b200 import correlation_cuda as shim
+    saved = sys.modules.get("correlation_cuda")
+    sys.modules["correlation_cuda"] = shim
+    try:
+        path = os.path.join(R.PKG_DIR, "models", "correlation_package", "correlation.py")
+        spec = importlib.util.spec_from_file_location("reference_correlation_over_shim", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)                       # correlation.py:4 `import correlation_cuda` binds the shim
+    finally:
+        if saved is not None:
+            sys.modules["correlation_cuda"] = saved
+        else:
+            del sys.modules["correlation_cuda"]
+    assert mod.correlation_cuda is shim
+    return mod
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.float16, 2e-3), (torch.float64, 1e-5)])
+def test_unmodified_reference_correlation_py_runs_on_the_shim(dtype, tol):
+    """drop-in at the pybind boundary (correlation_cuda.cc:10-16,169-172): forward through the reference's own
+    CorrelationFunction / Correlation classes, every dtype AT_DISPATCH_FLOATING_TYPES_AND_HALF serves; backward via autograd"""
+    mod = _reference_correlation_over_the_shim()
+    d = torch.device("cuda:0")
+    f1, f2, _ = O.corr_microbench_inputs(4, 2, 28, 64, 96, with_flow=False)
+    a, b = f1.to(d, dtype), f2.to(d, dtype)
+    out = mod.Correlation(pad_size=4, kernel_size=1, max_displacement=4, stride1=1, stride2=1, corr_multiply=1)(a, b)
+    assert out.dtype == dtype and out.shape == (2, 81, 28, 64)
+    ref = _ref_corr(a, b)                                  # the reference's own CUDA extension, same dtype
+    assert (out.float() - ref.float()).abs().max().item() <= tol * ref.float().abs().max().item()
+    if dtype == torch.float32:
+        a.requires_grad_(True); b.requires_grad_(True)
+        go = torch.randn(2, 81, 28, 64, device=d)
+        mod.CorrelationFunction.apply(a, b, 4, 1, 4, 1, 1, 1).backward(go)
+        ga, gb = a.grad.clone(), b.grad.clone()
+        a.grad = b.grad = None
+        _, corr_mod, _ = R.load()
+        corr_mod.CorrelationFunction.apply(a, b, 4, 1, 4, 1, 1, 1).backward(go)
+        assert (ga - a.grad).abs().max().item() <= 1e-5 * a.grad.abs().max().item()
+        assert (gb - b.grad).abs().max().item() <= 1e-5 * b.grad.abs().max().item()

@@ -115,6 +115,26 @@ def test_gpu_preprocess_bit_exact(shape, swap):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(1, 37, 50), (2, 375, 1242)])
+@pytest.mark.parametrize("swap", [False, True])
+def test_gpu_preprocess_imagenet_normalised_bit_exact(shape, swap):
+    """T.ToTensor + T.Normalize(ImageNet) of the KITTI drivers (inference_kitti.py:175-179) fused into the pre-processing kernel"""
+    from opticalflow_b200 import prepost
+    B, H, W = shape
+    g = np.random.default_rng(77 + H)
+    f1 = g.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    f2 = g.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    f1[0, 0, :4] = [[0, 0, 0], [255, 255, 255], [1, 128, 254], [124, 116, 104]]
+    x, ph, pw = prepost.frames_to_input(torch.from_numpy(f1).cuda(), torch.from_numpy(f2).cuda(), swap_rb=swap,
+                                        mean=prepost.IMAGENET_MEAN, std=prepost.IMAGENET_STD)
+    x = x.cpu()
+    for n in range(B):
+        ref, rph, rpw = PO.frames_to_input_normalized(f1[n], f2[n], prepost.IMAGENET_MEAN, prepost.IMAGENET_STD, swap_rb=swap)
+        assert (ph, pw) == (rph, rpw)
+        assert torch.equal(x[n], ref[0])
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("case", [
     # B, h, w, pad_h, pad_w, H, W, mult
     (2, 16, 16, 5, 3, 37, 50, 1.0), (2, 16, 16, 0, 0, 64, 64, 1.0), (1, 96, 320, 9, 38, 375, 1242, 20.0),
