@@ -366,13 +366,17 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   if (coutp % 16 || coutp < 16 || coutp > 128 || cout > coutp || (in_pitch & 7) || (in_coff & 7))
     return (int)cudaErrorInvalidValue;
   const int ts = (out_f32 >> 4) & 1;              // tap-stacked weights ([chunk][tap*cout + co][64] in the tap-0 section)
+  const int tlf = (out_f32 >> 5) & 1;             // tap-lane weights (WmParams::tl): cout <= 64 real channels, coutp = 128 rows
   out_f32 &= 3;
+  if (tlf && (ts || dil != 1 || cout > 64 || coutp != 128 || out_f32 || kc != 64 || out2 || g_split.out_lo_off)) return (int)cudaErrorInvalidValue;
   if (ts && (dil != 1 || 9 * cout > 128 || coutp != 128 || !out_f32 || kc != 64)) return (int)cudaErrorInvalidValue;
   pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
   if (!h) return (int)cudaErrorMemoryAllocation;
   h->halo = 2;
   WmParams& p = h->wp;
   p.ts = ts; p.ntaps = ts ? 1 : 9; p.s_stride = 0; p.s_bytes = 0;
+  p.tl = tlf ? (cout <= 32 ? 3 : 2) : 0;
+  if (p.tl) p.ntaps = p.tl == 3 ? 3 : 6;
   p.has_skip = 0; p.out_groups = 1; p.has_kk = 0; p.kk_first_tap = 0; p.kk_first_kk = 0;
   for (int i = 0; i < 9; ++i) p.kk_mask[i] = 0;
   for (int i = 0; i < 9; ++i) p.skip[i] = 0ull;
@@ -419,12 +423,28 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     rows = cdiv(H, cdiv(H, 23));
     while (ntiles(rows) < g_num_sms && rows > 6) rows = cdiv(rows, 2);
   }
-  p.rows = rows; p.npx = ts ? (((rows + 2) * 10 + 15) & ~15) : 8 * rows;
+  if (p.tl) {
+    // rows: a multiple of the lane count (equal pixel blocks per epilogue phase), even, N = 8 * (rows + 2) <= 256; fewest
+    // waves x (MMA time per item + fixed cost), then least padding
+    long best = -1; rows = 0;
+    for (int r = 2; r <= 30; r += 2) {
+      if (r % p.tl) continue;
+      const long waves = (ntiles(r) + g_num_sms - 1) / g_num_sms;
+      const long cost = waves * ((long)cdiv(cin_span, kc) * vmul * p.ntaps * 4 * (4L * (r + 2) > 68 ? 4L * (r + 2) : 68) + 2500);
+      if (best < 0 || cost < best || (cost == best && cdiv(Hd, r) * r <= cdiv(Hd, rows) * rows)) { best = cost; rows = r; }
+    }
+    const int forced_tl = env_int("PWC_TC_TL_ROWS", 0);
+    if (forced_tl >= 2 && forced_tl <= 30 && !(forced_tl & 1) && forced_tl % p.tl == 0) rows = forced_tl;
+  }
+  p.rows = rows; p.npx = ts ? (((rows + 2) * 10 + 15) & ~15) : p.tl ? 8 * (rows + 2) : 8 * rows;
   p.tiles_x = cdiv(Wd, 8); p.tiles_y = cdiv(Hd, rows);
   p.tiles_per_img = nph * p.tiles_x * p.tiles_y;
   p.num_items = (int)ntiles(rows);
   const uint32_t row_bytes = (uint32_t)kc * 2;
-  p.x_bytes_tx = (uint32_t)(rows + 2 * p.kyr) * 10u * row_bytes;
+  // two-lane tap stacking: the single-lane ky = 2 slots read halo rows up to rows + 3; the second lane multiplies them by zero
+  // weights, so they must be finite: the box carries two more (real or zero-filled) rows
+  const int xextra = p.tl == 2 ? 2 : 0;
+  p.x_bytes_tx = (uint32_t)(rows + 2 * p.kyr + xextra) * 10u * row_bytes;
   p.x_bytes = (p.x_bytes_tx + 1023u) & ~1023u;
   if (ts) {
     const uint32_t need = (uint32_t)p.npx * row_bytes;        // the MMA reads npx pixel rows (tail rows: don't-care columns)
@@ -483,15 +503,24 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     if (ws_ok) { p.wstore = 1; p.o_rs = rs; p.o_half = o_half; p.o_nbuf = 2; p.o_bytes = o_bytes; }
     break;
   }
+  if (p.tl) {
+    if (!p.tma_store) { delete h; return (int)cudaErrorInvalidValue; }
+    const int bh = rows / p.tl;
+    int rs = bh < 8 ? bh : 8;
+    while (bh % rs) --rs;
+    p.cg = cdiv(cout, 32); p.rep = 1; p.wstore = 1; p.o_rs = rs; p.o_half = (uint32_t)rs * 8u * 64u; p.o_nbuf = 2;
+    p.o_bytes = 4u * 2u * p.o_half;
+    p.s_bytes = ((uint32_t)p.cg * rows * 8u * 32u * 4u + 1023u) & ~1023u;        // fp32 lane sums [cg][pixel][32 ch]
+  }
   p.w_bytes = p.rep > 1 ? full_tile : ((p.w_bytes_tx + 1023u) & ~1023u);
   p.w_pad = full_tile > p.w_bytes ? full_tile - p.w_bytes : 0u;
   const uint32_t budget = 216u * 1024u - (uint32_t)p.x_stages * p.x_bytes - p.w_pad - p.o_bytes - p.s_bytes;
   const uint32_t all_w = 9u * p.nchunk * p.w_bytes;
-  p.w_resident = (!ts && all_w <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
+  p.w_resident = (!ts && !p.tl && all_w <= budget && env_int("PWC_TC_HALO_RESIDENT", 1)) ? 1u : 0u;
   if (!p.w_resident && p.rep > 1) { delete h; return (int)cudaErrorInvalidValue; }
   // streamed weights: 3 taps per stage when the pixel tile is small (per-stage handshakes would dominate the MMAs)
   p.tps = 1;
-  if (!ts && !p.w_resident && p.npx <= 128 && budget / (3u * p.w_bytes) >= 3 && env_int("PWC_TC_WM_TPS", 3) == 3) p.tps = 3;
+  if (!ts && !p.tl && !p.w_resident && p.npx <= 128 && budget / (3u * p.w_bytes) >= 3 && env_int("PWC_TC_WM_TPS", 3) == 3) p.tps = 3;
   uint32_t stages = budget / (p.w_bytes * p.tps);
   p.w_stages = stages > 12 ? 12 : (stages < 2 ? 2 : stages);
   uint32_t cols = 32; while (cols < 2u * p.npx) cols <<= 1;
@@ -514,7 +543,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     // split input: one map spans both planes (the hi plane's partial last chunk then reads real neighbouring channels
     // instead of zero fill: their weight rows are zero and all stored values are finite)
     e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span + p.lo_off, W, H, N,
-                       kc, 10 * dil, ydense ? rows + 2 * dil : (rows + 2) * dil, dil, p.dy, swz);
+                       kc, 10 * dil, ydense ? rows + 2 * dil : (rows + 2 + xextra) * dil, dil, p.dy, swz);
   }
   if (!e) e = make_tmap_2d(&h->tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, w_packed, (long)9 * p.nchunk * coutp, kc, kc, coutp, swz);
   h->tmO = h->tmA0; h->tmO2 = h->tmA0;
@@ -527,6 +556,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     if ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7)))) e = (int)cudaErrorInvalidValue;
     const int n1 = out2 ? p.n_split : N;
     const int bc = p.wstore ? 32 : coutp, br = p.wstore ? p.o_rs : rows / 2;
+    if (p.tl) coutp = 32 * p.cg;                   // the map covers the real channel groups only (coutp = 128 counted MMA rows)
     if (p.out_lo_off && !p.wstore) e = (int)cudaErrorInvalidValue;     // split output exists in the per-warp store path only
     if (!e) e = make_tmap_nhwc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out) + out_coff,
                                out_pitch, coutp + p.out_lo_off, W, H, n1, bc, 8 * dil, br * p.dy, dil, p.dy, CU_TENSOR_MAP_SWIZZLE_NONE);
@@ -546,9 +576,9 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   // of the SMs and whose K loop has >= PWC_TC_WM_KSPLIT2_MINCH (6) chunks -- levels 5-6, and the split-precision level 4-6
   // decoders whose K loops are three times as long -- run ks CTAs per tile on contiguous chunk ranges; each stores its fp32
   // partial tile to its own scratch slab and wm_splitk_reduce_kernel (a second launch) sums the slabs in order.
-  const bool two_pass = env_int("PWC_TC_WM_KSPLIT2", 1) && dil == 1 && !p.xsplit && p.out_groups == 1 &&
+  const bool two_pass = env_int("PWC_TC_WM_KSPLIT2", 1) && dil == 1 && !p.xsplit && p.out_groups == 1 && !p.tl &&
                         2 * p.num_items <= g_num_sms && p.nchunk >= env_int("PWC_TC_WM_KSPLIT2_MINCH", 6);
-  if (p.wstore && !ts && p.nchunk >= 2 && (two_pass || (!p.out_lo_off && env_int("PWC_TC_WM_KSPLIT", 0)))) {
+  if (p.wstore && !ts && !p.tl && p.nchunk >= 2 && (two_pass || (!p.out_lo_off && env_int("PWC_TC_WM_KSPLIT", 0)))) {
     int ks = g_num_sms / p.num_items;
     if (ks > 8) ks = 8;
     if (two_pass && ks > p.nchunk / 3) ks = p.nchunk / 3;            // at least 3 chunks per CTA: below that the pipeline fill dominates
@@ -599,6 +629,7 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
       cudaFuncSetAttribute(conv_tc_wm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
       cudaFuncSetAttribute(conv_tc_wm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
       cudaFuncSetAttribute(conv_tc_wm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(conv_tc_wm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
       attr_dev = dev;
     }
   }
@@ -672,7 +703,7 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
 extern "C" int pwc_tc_conv_set_skip(pwc_tc_conv* h, const unsigned long long* masks) {
   if (!h || !masks || h->halo != 2) return (int)cudaErrorInvalidValue;
   pwc::WmParams& p = h->wp;
-  if (p.ts || p.nchunk > 64) return (int)cudaErrorInvalidValue;
+  if (p.ts || p.tl || p.nchunk > 64) return (int)cudaErrorInvalidValue;
   if (p.w_resident) return 0;                    // whole weight set lives in shared memory: nothing to skip loading
   p.tps = 1;                                     // one tap per ring stage (uses the first w_stages buffers of the ring)
   bool any = false;
@@ -738,7 +769,8 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
 #define PWC_WM_LAUNCH(MODE) \
   pwc::launch_pdl(pwc::conv_tc_wm_kernel<MODE>, dim3(h->grid), dim3(pwc::kHaloThreads), h->smem_bytes, st, h->tmA0, h->tmB, h->tmO, \
                   h->tmO2, h->wp)
-    if (h->wp.ts) PWC_WM_LAUNCH(1);
+    if (h->wp.tl) PWC_WM_LAUNCH(4);
+    else if (h->wp.ts) PWC_WM_LAUNCH(1);
     else if (h->wp.has_skip) PWC_WM_LAUNCH(2);
     else if (h->wp.has_kk) PWC_WM_LAUNCH(3);
     else PWC_WM_LAUNCH(0);
@@ -808,7 +840,7 @@ extern "C" int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* h, int ksplit
   if (!h || h->halo != 2) return (int)cudaErrorInvalidValue;
   WmParams p = h->wp;                                               // by-value copy: the handle itself is not modified
   p.ks2pass = 0;                                                    // this entry point runs the one-pass (atomic) form
-  if (!p.wstore || p.ts || p.nchunk < 2 || ksplit < 0 || p.out_lo_off) {
+  if (!p.wstore || p.ts || p.tl || p.nchunk < 2 || ksplit < 0 || p.out_lo_off) {
     fprintf(stderr, "pwc_tc_conv_launch_static_splitk: the layer has no split-K form (needs >= 2 channel chunks, "
                     "16-bit per-warp output stores, no tap stacking)\n");
     return (int)cudaErrorInvalidValue;

@@ -42,6 +42,12 @@ struct WmParams {
   // single-precision weights.  out_lo_off != 0: the epilogue stores both planes of its output.
   int split, lo_off, out_lo_off;
   int up_lo_off, up_dup_off;                      // fused upfeat outputs (out_f32 == 2): lo plane / second hi copy, 0 = none
+  // tap-lane stacking (kMode 4; Cout <= 64): the 128 MMA rows hold tl LANES of output channels, lane l = the weights of kernel
+  // row ky = l (tl = 3, Cout <= 32) or of ky = 0 | 1 (tl = 2, Cout <= 64, ky = 2 follows as single-lane slots); one MMA per
+  // kx covers all lanes at once on N = 8 * (rows + 2) halo pixels (3 / 6 MMA groups per chunk instead of 9); lane l's
+  // accumulator row r + l holds its part of output row r, and the epilogue warps of a channel group add the lanes up through
+  // the fp32 tile S (each warp takes another pixel block per phase, the last phase finishes the block).
+  int tl;
   unsigned long long skip[9];                    // bit ch of skip[tap]: weight block (tap, chunk ch) is all zero -> no load, no MMA
   int has_kk, kk_mask[9], kk_first_tap, kk_first_kk;   // single-chunk layers: bit kk of kk_mask[tap] set <=> the K=16 step kk of
                                                   // tap's weight tile is all zero (space-to-depth block structure) -> no MMA
@@ -68,7 +74,7 @@ __device__ __forceinline__ void named_bar(int id, int nthreads) {
 // kMode = 0: the plain 9-tap path with nothing extra on the MMA issue path (the big layers run at > 90% of the tensor
 // peak only while the issuing thread does no more than descriptor arithmetic); the tap-stacked mode and the zero-block /
 // K-step skip lists are separate instances.
-// kMode: 0 plain | 1 tap-stacked | 2 zero-block skip list | 3 K-step skip masks (one instance each: see above)
+// kMode: 0 plain | 1 tap-stacked | 2 zero-block skip list | 3 K-step skip masks | 4 tap lanes (one instance each: see above)
 template <int kMode>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
@@ -154,7 +160,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         __syncwarp();
         if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
         if (!p.w_resident) {
-          for (int tap = 0; tap < (kMode == 1 ? 1 : 9); tap += p.tps) {
+          for (int tap = 0; tap < (kMode == 1 ? 1 : kMode == 4 ? p.ntaps : 9); tap += p.tps) {
             if ((kMode == 2) && ((p.skip[tap] >> ch) & 1ull)) continue;
             ptx::mbar_wait(w_empty(s), wph ^ 1);
             if (ptx::elect_one()) {
@@ -199,7 +205,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         int ftap = 0;                                        // first tap actually issued for this chunk
         if ((kMode == 2)) while (ftap < 8 && ((p.skip[ftap] >> ch) & 1ull)) ++ftap;
         auto issue_tap = [&](uint32_t sw, int tap) {
-          const int ky = tap / 3, kx = tap - 3 * ky;
+          const int ky = (kMode == 4) ? (tap < 3 ? 0 : 2) : tap / 3, kx = tap - 3 * (tap / 3);   // kMode 4: slots 3..5 = ky 2, one lane
           const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
           const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * p.kyr * 10 + kx) * row_bytes) >> 4);
           if ((kMode == 3)) {
@@ -224,7 +230,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           }
           __syncwarp();
         } else {
-          for (int tap0 = 0; tap0 < (kMode == 1 ? 1 : 9); tap0 += p.tps) {
+          for (int tap0 = 0; tap0 < (kMode == 1 ? 1 : kMode == 4 ? p.ntaps : 9); tap0 += p.tps) {
             if ((kMode == 2) && ((p.skip[tap0] >> ch) & 1ull)) continue;
             ptx::mbar_wait(w_full(s), wph);
             ptx::tc_fence_after();
@@ -323,6 +329,72 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           }
         }
         named_bar(2, 128);                                   // S may be overwritten by the next item
+        if (++acc == 2) { acc = 0; tph ^= 1; }
+        continue;
+      }
+      if ((kMode == 4)) {
+        // ---- tap lanes: warp = (lane l of the MMA rows, 32-channel group cgi); phase ph handles pixel block (l + ph) % G ----
+        const int G = p.tl, l = lg / p.cg, cgi = lg - l * p.cg;
+        const int bh = p.rows / G;                           // tile rows per pixel block
+        if (l < G) {
+          float* S = reinterpret_cast<float*>(smem_raw + (s_base - ptx::smem_addr(smem_raw))) + (size_t)cgi * p.rows * 8 * 32 + lane;
+          const uint32_t my_o = o_base + (uint32_t)lg * 2u * p.o_half;
+          for (int ph = 0; ph < G; ++ph) {
+            const int b = (l + ph) % G;
+            for (int r0 = 0; r0 < bh; r0 += p.o_rs) {
+              const int row = b * bh + r0, ncol = p.o_rs * 8;
+              uint32_t v[4][16];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {                   // lane l: output row r sits at r + l; never read past the
+                if (q * 16 + 16 <= ncol) ptx::tmem_ld16(taddr + (row + l) * 8 + q * 16, v[q]);   // accumulator's last column
+                else if (q * 16 < ncol) ptx::tmem_ld8(taddr + (row + l) * 8 + q * 16, *reinterpret_cast<uint32_t(*)[8]>(&v[q][0]));
+              }
+              ptx::tmem_ld_wait();
+              float* sp = S + (size_t)row * 8 * 32;
+              if (ph < G - 1) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    if (q * 16 + i < ncol) {
+                      const float a = __uint_as_float(v[q][i]);
+                      sp[(q * 16 + i) * 32] = (ph == 0) ? a : sp[(q * 16 + i) * 32] + a;
+                    }
+              } else {
+                const uint32_t so = my_o + (uint32_t)wbuf * p.o_half;
+                if (lane == 0) ptx::bulk_wait_read1();
+                __syncwarp();
+                uint16_t* st = reinterpret_cast<uint16_t*>(smem_raw + (so - ptx::smem_addr(smem_raw))) + lane;
+                const float bia = (cgi * 32 + lane < p.cout) ? __ldg(p.bias + cgi * 32 + lane) : 0.f;
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                  for (int i = 0; i < 16; ++i)
+                    if (q * 16 + i < ncol) {
+                      const float a = __uint_as_float(v[q][i]) + sp[(q * 16 + i) * 32] + bia;
+                      st[(q * 16 + i) * 32] = pack1_h16(fmaxf(a, a * p.slope), p.fp16);
+                    }
+                ptx::fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                  ptx::tma_store_4d(second ? &tmO2 : &tmO, so, cgi * 32, rx + d * tx0, ry + p.dy * (ty0 + row), nn);
+                  ptx::bulk_commit();
+                }
+                wbuf ^= 1;
+              }
+            }
+            if (ph == G - 1) {                               // every TMEM read of this item is done
+              ptx::tc_fence_before();
+              __syncwarp();
+              if (lane == 0) ptx::mbar_arrive(t_empty(acc));
+            }
+            named_bar(3 + cgi, 32 * G);                      // the block's partial sums are visible to the next phase's warp
+          }
+        } else {
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(t_empty(acc));
+        }
         if (++acc == 2) { acc = 0; tph ^= 1; }
         continue;
       }

@@ -64,12 +64,34 @@ def _stacked(wfn_or_key):
     return make
 
 
+def _lanes(wfn_or_key, cout):
+    """Tap-lane weight tensor for layers with Cout <= 64 (include/pwc_b200.h, out_f32 | 32; WmParams::tl): a [128, Cin, 3, 3]
+    tensor whose packer tap slot t = 3*a + kx holds, for Cout <= 32 (three lanes of 32 rows), row 32*l + co = W[co, :, ky=l, kx] in
+    slots a = 0; for Cout <= 64 (two lanes of 64 rows), rows co / 64 + co = W[co, :, ky = 0 / 1, kx] in slots a = 0 and
+    row co = W[co, :, ky=2, kx] in slots a = 1.  Unused slots / rows stay zero and are never loaded."""
+    def make(sd):
+        w, b = wfn_or_key(sd) if callable(wfn_or_key) else (sd[wfn_or_key + ".weight"], sd[wfn_or_key + ".bias"])
+        cin = w.shape[1]
+        wl = torch.zeros(128, cin, 3, 3, device=w.device, dtype=torch.float32)
+        if cout <= 32:
+            for l in range(3):
+                wl[32 * l:32 * l + cout, :, 0, :] = w[:, :, l, :]
+        else:
+            wl[0:cout, :, 0, :] = w[:, :, 0, :]
+            wl[64:64 + cout, :, 0, :] = w[:, :, 1, :]
+            wl[0:cout, :, 1, :] = w[:, :, 2, :]
+        return wl, b
+    return make
+
+
+TL_MODE = os.environ.get("PWC_TC_TL", "1") != "0"
 TS_MODE = os.environ.get("PWC_TC_TS", "1") != "0"
 S2D_DEC = os.environ.get("PWC_TC_S2D_DEC", "1") != "0"
 # measured (B200, batch 8, 1024x448): the super-pixel form halves the MMA count but streams 4x larger weight tiles per item,
 # so it only pays where items are plentiful (level 2) and the M operand was 3/4 empty (Cout = 32): conv2_4 178 -> 153 us
 S2D_DEC_MAXLVL = int(os.environ.get("PWC_TC_S2D_DEC_MAXLVL", "2"))
 S2D_DEC_MAXCOUT = int(os.environ.get("PWC_TC_S2D_DEC_MAXCOUT", "32"))
+TL_MAXLVL = int(os.environ.get("PWC_TC_TL_MAXLVL", "3"))        # decoder levels whose Cout <= 64 layers run in tap-lane form
 
 
 def _pfup_weights(lvl):
@@ -191,7 +213,8 @@ class PlanBF16:
     # ------------------------------------------------------------------ layer construction
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
-            flops=None, ts=False, groups=None, kkskip=False, in_lo=0, out_lo=0, up_lo=0, up_dup=0, kpad=None, no_small=False):
+            flops=None, ts=False, groups=None, kkskip=False, in_lo=0, out_lo=0, up_lo=0, up_dup=0, kpad=None, no_small=False,
+            tl=False):
         """in_lo / out_lo: channel offset of the lo plane of a split-precision input / output (0 = single precision);
         up_lo / up_dup: lo / second-hi offsets of the fused upfeat outputs; kpad = (idx, lo_pos, dup_pos): the torch input
         channels idx are also read from their lo copies / second hi copies at those slice positions (split.kpad_weights)."""
@@ -207,11 +230,13 @@ class PlanBF16:
         L = _TcLayer()
         L.kkskip = bool(kkskip and span <= 64 and cmap is None and os.environ.get("PWC_TC_KKSKIP", "1") != "0")
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
-        L.wfn = _stacked(wfn if wfn is not None else key) if ts else wfn
+        tl = bool(tl and TL_MODE and cout <= 64 and stride == 1 and dil == 1 and not out_f32 and not ts and groups is None
+                  and not out_lo and dst2 is None and src2 is None)
+        L.wfn = _stacked(wfn if wfn is not None else key) if ts else (_lanes(wfn if wfn is not None else key, cout) if tl else wfn)
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
-        L.coutp = 128 if ts else _roundup(cout, 16)
+        L.coutp = 128 if (ts or tl) else _roundup(cout, 16)
         L.kc = pick_kc(span, stride, dil, src2 is not None, W=win, coutp=L.coutp, out_f32=bool(out_f32) or dst2 is not None)
-        L.wrows = 128 if ts else cout                   # rows of the weight tensor handed to the packer
+        L.wrows = 128 if (ts or tl) else cout           # rows of the weight tensor handed to the packer
         L.split_in, L.kpad, L.mask_key = bool(in_lo), kpad, key
         L.products = 2 if in_lo < 0 else 3                # in_lo < 0: split activations only (lo plane at -in_lo)
         # adjacent [hi | lo] planes that fit one swizzle row run the fused form of the stride-2 kernel (TcConvParams::fused)
@@ -226,7 +251,7 @@ class PlanBF16:
         args = (ctypes.byref(h), _lib.ptr(src), src.shape[-1], src_coff,
                 _lib.ptr(src2), (src2.shape[-1] if src2 is not None else 0), src2_coff, n_split, span, L.kc,
                 _lib.ptr(L.w), _lib.ptr(L.b), cout, L.coutp, _lib.ptr(dst), dst.shape[-1], dst_coff,
-                _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32) | (16 if ts else 0),
+                _lib.ptr(dst2), (dst2.shape[-1] if dst2 is not None else 0), dst2_coff, int(out_f32) | (16 if ts else 0) | (32 if tl else 0),
                 _lib.ptr(residual), (residual.shape[-1] if residual is not None else 0), N, hin, win, stride, dil, slope)
         if in_lo or out_lo or up_lo or up_dup:
             e = self.lib.pwc_tc_conv_create_split(*args, in_lo, out_lo, up_lo, up_dup)
@@ -377,6 +402,11 @@ class PlanBF16:
                 cm = chan_map(l, DEC_START[k])
                 cout = [128, 128, 96, 64, 32][k]
                 g = 128 // cout
+                if TL_MODE and cout <= 64 and l <= TL_MAXLVL:
+                    # Cout = 64 / 32: tap lanes -- 6 / 3 MMA groups per chunk instead of 9 (WmParams::tl)
+                    self._tc(f"conv{l}_{k}.0", len(cm), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w,
+                             cmap=cm, tl=True)
+                    continue
                 if S2D_DEC and cout <= S2D_DEC_MAXCOUT and l <= S2D_DEC_MAXLVL and w % g == 0:
                     # Cout = 64 / 32: g adjacent pixels form one super-pixel so that all 128 MMA rows carry outputs
                     # (weight block-structured as in _s2d_weights; all-zero (tap, chunk) blocks are skipped)
@@ -403,7 +433,9 @@ class PlanBF16:
         src, cin, span, cmap = self.cat[2], len(cm), concat_width(2), cm
         for i, (name, cout, dil) in enumerate(DC):
             g = 128 // cout if cout <= S2D_DEC_MAXCOUT else 1
-            if S2D_DEC and g > 1 and dil == 1 and cmap is None and w % g == 0 and src.shape[-1] == span:
+            if TL_MODE and cout <= 64 and dil == 1 and span >= 128:      # (dc_conv6, one chunk: 28 us as s2d, 49 us in lanes)
+                self._tc(name + ".0", cin, cout, src, 0, span, self.dc[i], 0, B, h, w, cmap=cmap, tl=True)
+            elif S2D_DEC and g > 1 and dil == 1 and cmap is None and w % g == 0 and src.shape[-1] == span:
                 vi, vo = src[:B].view(B, h, w // g, g * span), self.dc[i].view(B, h, w // g, g * cout)
                 self._tc(name + ".0", g * cin, g * cout, vi, 0, g * span, vo, 0, B, h, w // g,
                          wfn=_s2d_weights(name + ".0", g), flops=2.0 * B * h * w * cout * cin * 9, groups=(g, cout))

@@ -24,7 +24,8 @@ from . import _lib
 from . import split as S
 from .engine import (C1_OFF, CORR_OFF, DC, DEC_START, DEC_WRITE, FLOW_SCALE, PYR_CH, UPFEAT_OFF, UPFLOW_OFF, chan_map,
                      concat_width)
-from .engine_bf16 import PlanBF16, _TcLayer, _pfup_weights, _roundup, _s2d_weights, S2D_DEC, S2D_DEC_MAXCOUT, S2D_DEC_MAXLVL
+from .engine_bf16 import (PlanBF16, _TcLayer, _pfup_weights, _roundup, _s2d_weights, S2D_DEC, S2D_DEC_MAXCOUT, S2D_DEC_MAXLVL,
+                          TL_MODE, TL_MAXLVL)
 
 CPM = [4, 16, 32, 64, 96, 128, 224]     # channels per PLANE of the pyramid tensors (level 6: 196 -> 128 + 96 output groups)
 import os
@@ -182,6 +183,10 @@ class PlanMixed(PlanBF16):
                 kp, cme = _kpad(key, l, DEC_START[k])
                 kpf = (lambda f: (lambda sd: f(sd, self.hdt)))(kp)
                 g = 128 // cout
+                if TL_MODE and cout <= 64 and l <= TL_MAXLVL:
+                    self._tc(key, len(cme), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w, cmap=cme, wfn=kpf,
+                             flops=2.0 * B * h * w * cout * len(cm) * 9, tl=True)
+                    continue
                 if S2D_DEC and cout <= S2D_DEC_MAXCOUT and l <= S2D_DEC_MAXLVL and w % g == 0:
                     v = cat[:B].view(B, h, w // g, g * wd)
                     cm2 = [dxp * wd + DEC_START[k] + c for dxp in range(g) for c in cme]
@@ -219,7 +224,9 @@ class PlanMixed(PlanBF16):
         src, cin, span, cmap, wfn = self.cat[2], len(cme), concat_width(2), cme, (lambda f: (lambda sd: f(sd, self.hdt)))(kp)
         for i, (name, cout, dil) in enumerate(DC):
             g = 128 // cout if cout <= S2D_DEC_MAXCOUT else 1
-            if S2D_DEC and g > 1 and dil == 1 and cmap is None and w % g == 0 and src.shape[-1] == span:
+            if TL_MODE and cout <= 64 and dil == 1 and span >= 128:
+                self._tc(name + ".0", cin, cout, src, 0, span, self.dc[i], 0, B, h, w, cmap=cmap, wfn=wfn, tl=True)
+            elif S2D_DEC and g > 1 and dil == 1 and cmap is None and w % g == 0 and src.shape[-1] == span:
                 vi, vo = src[:B].view(B, h, w // g, g * span), self.dc[i].view(B, h, w // g, g * cout)
                 self._tc(name + ".0", g * cin, g * cout, vi, 0, g * span, vo, 0, B, h, w // g,
                          wfn=_s2d_weights(name + ".0", g), flops=2.0 * B * h * w * cout * cin * 9, groups=(g, cout))

@@ -145,7 +145,7 @@ def pick_kc(cin_span, stride=1, dil=1, has_in2=False, W=None, coutp=None, out_f3
 
 
 def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=None, out=None, out_coff=0,
-               chan_map=None, out_f32=False, residual=None, reps=1, ts=False):
+               chan_map=None, out_f32=False, residual=None, reps=1, ts=False, tl=False):
     """bf16 tcgen05 conv (pwc_tc_conv_*) on an NHWC bf16 tensor x [N,H,W,pitch]; weight torch [Cout,Cin,3,3] fp32.
     ts=True: tap-stacked mode for 9*Cout <= 128 (fp32 output)."""
     import ctypes
@@ -155,7 +155,7 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     assert x.dtype == _h16(lib)
     cout, cin = weight.shape[:2]
     span = cin_span if cin_span is not None else (cin + 15) // 16 * 16
-    coutp = 128 if ts else (cout + 15) // 16 * 16
+    coutp = 128 if (ts or tl) else (cout + 15) // 16 * 16
     kc = pick_kc(span, stride, dil, W=W, coutp=coutp, out_f32=bool(out_f32))
     wp = torch.empty(9 * ((span + kc - 1) // kc) * kc * coutp, device=x.device, dtype=x.dtype)
     mp = None if chan_map is None else torch.tensor(chan_map, device=x.device, dtype=torch.int32)
@@ -167,16 +167,27 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
         for tap in range(9):
             ws[tap * cout:(tap + 1) * cout, :, 0, 0] = w32[:, :, tap // 3, tap % 3]
         w32, wrows = ws, 128
+    if tl:                                      # tap lanes (include/pwc_b200.h, out_f32 | 32): Cout <= 64, 16-bit output
+        assert cout <= 64 and not out_f32 and stride == 1 and dil == 1
+        ws = torch.zeros(128, cin, 3, 3, device=x.device, dtype=torch.float32)
+        if cout <= 32:
+            for l in range(3):
+                ws[32 * l:32 * l + cout, :, 0, :] = w32[:, :, l, :]
+        else:
+            ws[0:cout, :, 0, :] = w32[:, :, 0, :]
+            ws[64:64 + cout, :, 0, :] = w32[:, :, 1, :]
+            ws[0:cout, :, 1, :] = w32[:, :, 2, :]
+        w32, wrows = ws, 128
     _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), wrows, cin, span, kc, coutp, st), "pack")
     ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
     if out is None:
-        out = torch.zeros(N, ho, wo, coutp if not out_f32 else cout, device=x.device,
+        out = torch.zeros(N, ho, wo, ((cout + 31) // 32 * 32 if tl else coutp) if not out_f32 else cout, device=x.device,
                           dtype=torch.float32 if out_f32 else x.dtype)
     b32 = bias.detach().float().contiguous()
     h = ctypes.c_void_p()
     e = lib.pwc_tc_conv_create(ctypes.byref(h), _lib.ptr(x), pitch, in_coff, None, 0, 0, N, span, kc,
                                _lib.ptr(wp), _lib.ptr(b32), cout, coutp, _lib.ptr(out), out.shape[-1], out_coff,
-                               None, 0, 0, int(out_f32) | (16 if ts else 0), _lib.ptr(residual),
+                               None, 0, 0, int(out_f32) | (16 if ts else 0) | (32 if tl else 0), _lib.ptr(residual),
                                (residual.shape[-1] if residual is not None else 0), N, H, W, stride, dil, slope)
     _lib.check(e, "pwc_tc_conv_create")
     try:

@@ -49,6 +49,32 @@ def test_conv3x3_tc_tap_stacked(case):
     assert (out - ref).abs().max().item() <= 2e-3 * ref.abs().max().item()
 
 
+@pytest.mark.parametrize("fmt", ["bf16", "f16"])
+@pytest.mark.parametrize("case", [
+    # cin, cout, N, H, W      tap-lane mode (Cout <= 64): decoder conv{2,3}_3 / _4 and dc_conv6 shapes, ragged tiles, odd channel counts
+    (533, 32, 2, 112, 256), (469, 64, 1, 112, 256), (565, 32, 1, 56, 128), (501, 64, 2, 56, 128), (64, 32, 1, 112, 256),
+    (128, 64, 2, 21, 37), (96, 32, 1, 7, 16), (72, 48, 1, 30, 9), (192, 20, 3, 13, 50), (64, 64, 8, 14, 32),
+])
+def test_conv3x3_tc_tap_lanes(case, fmt):
+    from opticalflow_b200 import ops
+    cin, cout, N, H, W = case
+    dt = torch.float16 if fmt == "f16" else torch.bfloat16
+    g = torch.Generator().manual_seed(400 + cin + cout)
+    x = torch.randn(N, cin, H, W, generator=g).to(dt)
+    w = (torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin ** 0.5)).to(dt).float()
+    b = torch.randn(cout, generator=g) * 0.1
+    ref = F.leaky_relu(F.conv2d(x.float(), w, b, padding=1), 0.1)
+    d = torch.device("cuda:0")
+    span = (cin + 15) // 16 * 16
+    xn = torch.zeros(N, H, W, span, dtype=dt)
+    xn[..., :cin] = x.permute(0, 2, 3, 1)
+    with ops.half_format(fmt):
+        out = ops.conv3x3_tc(xn.to(d), w.to(d), b.to(d), 1, 1, 0.1, cin_span=span, tl=True)
+    got = out.float().permute(0, 3, 1, 2).cpu()
+    assert (got[:, :cout] - ref).abs().max().item() <= (1.5e-3 if fmt == "f16" else 1e-2) * ref.abs().max().item()
+    assert got[:, cout:].abs().max().item() == 0.0 if got.shape[1] > cout else True
+
+
 @pytest.mark.parametrize("case", TC_CASES)
 def test_conv3x3_tc_matches_torch(case):
     from opticalflow_b200 import ops
