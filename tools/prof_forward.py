@@ -10,7 +10,7 @@ B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 H = int(sys.argv[2]) if len(sys.argv) > 2 else 448
 W = int(sys.argv[3]) if len(sys.argv) > 3 else 1024
 torch.manual_seed(0)
-m = PWCDCNet(conv_mode="bf16").eval().cuda()
+m = PWCDCNet(conv_mode=os.environ.get("PWC_MODE", "bf16")).eval().cuda()
 dev = torch.device("cuda")
 plan = m._plan(B, H, W, dev)
 plan.pack_weights(m)
