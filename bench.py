@@ -402,6 +402,17 @@ def run_ours(args):
                         f"durations (each launch captured 8x into a CUDA graph and timed alone); peak = bf16 burst ({peaks['source']}); whole-step figure "
                         f"{step_tflops:.1f} TFLOP/s incl. all other kernels"}
         kern_table = {n: round(t * 1e6, 1) for n, t, _ in ops_t}
+        # FLOP-weighted fractions per layer group (north_star: "the decoder convs at 50% or more of tensor-pipe peak")
+        import re as _re
+
+        def grp(pat):
+            sel = [(t, f) for n, t, f in ops_t if _re.match(pat, n)]
+            tt, ff = sum(t for t, _ in sel), sum(f for _, f in sel)
+            return {"us": round(tt * 1e6, 1), "TFLOPs": round(ff / tt / 1e12, 1), "frac": ff / tt / 1e12 / peak} if tt > 0 else None
+        roof["groups"] = {"decoder_conv2-6_0-4": grp(r"conv[2-6]_[0-4]\."), "decoder_level2": grp(r"conv2_[0-4]\."),
+                          "decoder_level3": grp(r"conv3_[0-4]\."), "decoder_levels4-6": grp(r"conv[4-6]_[0-4]\."),
+                          "context_dc_conv1-6": grp(r"dc_conv[1-6]\."), "pyramid": grp(r"conv[1-6](a|aa|b)\."),
+                          "note": "algorithmic FLOPs / summed launch times; split-precision layers issue 2-3x the tensor work per algorithmic FLOP"}
     corr_res, corr_bytes, corr_t = corr_microbench(dev, B)
     roof_corr_f32 = {"bound": "hbm", "achieved": corr_bytes / corr_t / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": corr_bytes / corr_t / 1e9 / peaks["hbm_gbs"], "traffic": None, "levels": corr_res,

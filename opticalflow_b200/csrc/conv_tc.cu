@@ -368,7 +368,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   const int ts = (out_f32 >> 4) & 1;              // tap-stacked weights ([chunk][tap*cout + co][64] in the tap-0 section)
   const int tlf = (out_f32 >> 5) & 1;             // tap-lane weights (WmParams::tl): cout <= 64 real channels, coutp = 128 rows
   out_f32 &= 3;
-  if (tlf && (ts || dil != 1 || cout > 64 || coutp != 128 || out_f32 || kc != 64 || out2 || g_split.out_lo_off)) return (int)cudaErrorInvalidValue;
+  if (tlf && (ts || dil != 1 || cout > 64 || coutp != 128 || out_f32 || kc != 64 || out2)) return (int)cudaErrorInvalidValue;
   if (ts && (dil != 1 || 9 * cout > 128 || coutp != 128 || !out_f32 || kc != 64)) return (int)cudaErrorInvalidValue;
   pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
   if (!h) return (int)cudaErrorMemoryAllocation;
@@ -377,6 +377,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.ts = ts; p.ntaps = ts ? 1 : 9; p.s_stride = 0; p.s_bytes = 0;
   p.tl = tlf ? (cout <= 32 ? 3 : 2) : 0;
   if (p.tl) p.ntaps = p.tl == 3 ? 3 : 6;
+  p.tl_bc = cout <= 16 ? 16 : 32;
   p.has_skip = 0; p.out_groups = 1; p.has_kk = 0; p.kk_first_tap = 0; p.kk_first_kk = 0;
   for (int i = 0; i < 9; ++i) p.kk_mask[i] = 0;
   for (int i = 0; i < 9; ++i) p.skip[i] = 0ull;
@@ -555,8 +556,8 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
     // output slice as a 4-D tensor (CoutP, W, H, images); box = half an item; dilation = element strides; no swizzle
     if ((out_pitch & 7) || (out_coff & 7) || (out2 && ((out2_pitch & 7) || (out2_coff & 7)))) e = (int)cudaErrorInvalidValue;
     const int n1 = out2 ? p.n_split : N;
-    const int bc = p.wstore ? 32 : coutp, br = p.wstore ? p.o_rs : rows / 2;
-    if (p.tl) coutp = 32 * p.cg;                   // the map covers the real channel groups only (coutp = 128 counted MMA rows)
+    const int bc = p.tl ? p.tl_bc : p.wstore ? 32 : coutp, br = p.wstore ? p.o_rs : rows / 2;
+    if (p.tl) coutp = p.tl_bc * p.cg;              // the map covers the real channel groups only (coutp = 128 counted MMA rows)
     if (p.out_lo_off && !p.wstore) e = (int)cudaErrorInvalidValue;     // split output exists in the per-warp store path only
     if (!e) e = make_tmap_nhwc(&h->tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, reinterpret_cast<__nv_bfloat16*>(out) + out_coff,
                                out_pitch, coutp + p.out_lo_off, W, H, n1, bc, 8 * dil, br * p.dy, dil, p.dy, CU_TENSOR_MAP_SWIZZLE_NONE);

@@ -47,7 +47,7 @@ struct WmParams {
   // kx covers all lanes at once on N = 8 * (rows + 2) halo pixels (3 / 6 MMA groups per chunk instead of 9); lane l's
   // accumulator row r + l holds its part of output row r, and the epilogue warps of a channel group add the lanes up through
   // the fp32 tile S (each warp takes another pixel block per phase, the last phase finishes the block).
-  int tl;
+  int tl, tl_bc;                                  // tl_bc: channels per output store box (16 for Cout <= 16, else 32)
   unsigned long long skip[9];                    // bit ch of skip[tap]: weight block (tap, chunk ch) is all zero -> no load, no MMA
   int has_kk, kk_mask[9], kk_first_tap, kk_first_kk;   // single-chunk layers: bit kk of kk_mask[tap] set <=> the K=16 step kk of
                                                   // tap's weight tile is all zero (space-to-depth block structure) -> no MMA
@@ -362,25 +362,35 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
                     }
               } else {
                 const uint32_t so = my_o + (uint32_t)wbuf * p.o_half;
-                if (lane == 0) ptx::bulk_wait_read1();
+                const uint32_t so_lo = my_o + (uint32_t)(wbuf ^ 1) * p.o_half;     // split output: the other buffer takes the lo plane
+                if (lane == 0) { if (p.out_lo_off) ptx::bulk_wait_read0(); else ptx::bulk_wait_read1(); }
                 __syncwarp();
+                const int bc = p.tl_bc;                      // staged pixel = bc channels (the store box)
                 uint16_t* st = reinterpret_cast<uint16_t*>(smem_raw + (so - ptx::smem_addr(smem_raw))) + lane;
+                uint16_t* st_lo = reinterpret_cast<uint16_t*>(smem_raw + (so_lo - ptx::smem_addr(smem_raw))) + lane;
                 const float bia = (cgi * 32 + lane < p.cout) ? __ldg(p.bias + cgi * 32 + lane) : 0.f;
+                if (lane < bc) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
+                  for (int q = 0; q < 4; ++q)
 #pragma unroll
-                  for (int i = 0; i < 16; ++i)
-                    if (q * 16 + i < ncol) {
-                      const float a = __uint_as_float(v[q][i]) + sp[(q * 16 + i) * 32] + bia;
-                      st[(q * 16 + i) * 32] = pack1_h16(fmaxf(a, a * p.slope), p.fp16);
-                    }
+                    for (int i = 0; i < 16; ++i)
+                      if (q * 16 + i < ncol) {
+                        const float a = __uint_as_float(v[q][i]) + sp[(q * 16 + i) * 32] + bia;
+                        const float r = fmaxf(a, a * p.slope);
+                        const uint16_t hb = pack1_h16(r, p.fp16);
+                        st[(q * 16 + i) * bc] = hb;
+                        if (p.out_lo_off) st_lo[(q * 16 + i) * bc] = pack1_h16(r - unpack1_h16(hb, p.fp16), p.fp16);
+                      }
+                }
                 ptx::fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) {
                   ptx::tma_store_4d(second ? &tmO2 : &tmO, so, cgi * 32, rx + d * tx0, ry + p.dy * (ty0 + row), nn);
+                  if (p.out_lo_off)
+                    ptx::tma_store_4d(second ? &tmO2 : &tmO, so_lo, cgi * 32 + p.out_lo_off, rx + d * tx0, ry + p.dy * (ty0 + row), nn);
                   ptx::bulk_commit();
                 }
-                wbuf ^= 1;
+                if (!p.out_lo_off) wbuf ^= 1;
               }
             }
             if (ph == G - 1) {                               // every TMEM read of this item is done

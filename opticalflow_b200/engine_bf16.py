@@ -231,7 +231,7 @@ class PlanBF16:
         L.kkskip = bool(kkskip and span <= 64 and cmap is None and os.environ.get("PWC_TC_KKSKIP", "1") != "0")
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
         tl = bool(tl and TL_MODE and cout <= 64 and stride == 1 and dil == 1 and not out_f32 and not ts and groups is None
-                  and not out_lo and dst2 is None and src2 is None)
+                  and dst2 is None and src2 is None)
         L.wfn = _stacked(wfn if wfn is not None else key) if ts else (_lanes(wfn if wfn is not None else key, cout) if tl else wfn)
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
         L.coutp = 128 if (ts or tl) else _roundup(cout, 16)
@@ -242,7 +242,7 @@ class PlanBF16:
         # adjacent [hi | lo] planes that fit one swizzle row run the fused form of the stride-2 kernel (TcConvParams::fused)
         L.fused = in_lo > 0 and stride == 2 and in_lo == span == L.kc and L.kc <= 32 and cmap is None and \
             os.environ.get("PWC_TC_FUSED_SPLIT", "1") != "0"
-        if out_lo:
+        if out_lo and not tl:
             L.coutp = _roundup(cout, 32)                  # split stores exist in the per-warp (32-channel group) store path
         dev = self.device
         L.w = torch.zeros(9 * _roundup(span, L.kc) * L.coutp * ((4 if L.fused else L.products) if in_lo else 1), device=dev, dtype=self.hdt)

@@ -35,6 +35,9 @@ SPLIT_LEVELS = tuple(int(v) for v in os.environ.get("PWC_MIXED_LEVELS", "5,4").s
 # the B200 0.0131 -> 0.0149 / 0.0091 -> 0.0103 / 0.0130 -> 0.0151 px at 1024x448 for a third less tensor work there; dropping
 # W_lo in the pyramid instead costs 0.025-0.028 px (PWC_MIXED_DEC_PRODUCTS=3 restores the full split)
 DEC_PRODUCTS = int(os.environ.get("PWC_MIXED_DEC_PRODUCTS", "2"))
+# levels 1-2 stride-1 layers on the tcgen05 tap-lane kernel instead of the mma.sync one: measured 458 / 120 us against 89 / 77 us
+# (one 64-channel chunk per tile: nine 16 KB weight tiles stream from L2 for nine MMAs) -- off
+THIN_TC = os.environ.get("PWC_MIXED_THIN_TC", "0") != "0"
 KP_LO, KP_DUP = 4, 8                    # K padding: lo copies of up_flow|up_feat at +4 (533..536), second hi copies at +8
 
 
@@ -148,7 +151,11 @@ class PlanMixed(PlanBF16):
                          in_lo=CPM[l - 1], out_lo=CP, no_small=True)
             for name, src, dst in ((names[1], self.pa[l], self.pb[l]), (names[2], self.pb[l], self.pa[l])):
                 key = name + ".0"
-                if C <= 32:
+                if C <= 32 and THIN_TC:
+                    # (experiment, off by default) three tap lanes, split in and out; the mma.sync form below sits at the legacy
+                    # tensor pipe's limit (3 x 25 GFLOP at ~300 TFLOP/s = 77-89 us per layer)
+                    self._tc(key, C, C, src, 0, C, dst, 0, NP, h, w, in_lo=CP, out_lo=CP, no_small=True, tl=True)
+                elif C <= 32:
                     self._thin_split(key, C, src, dst, NP, h, w)
                 elif C <= 128:
                     self._tc(key, C, C, src, 0, C, dst, 0, NP, h, w, in_lo=CP, out_lo=CP, no_small=True)

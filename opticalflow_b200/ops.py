@@ -205,7 +205,7 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
     return out
 
 
-def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, split_out=True, reps=1):
+def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, split_out=True, reps=1, tl=False):
     """Split-precision tcgen05 conv (pwc_tc_conv_create_split) for tests / tools: x32 [N,H,W,cin] fp32 NHWC is stored as
     hi | lo planes of the current 16-bit format; returns the fp32 reconstruction hi + lo of the output [N,Ho,Wo,cout]."""
     import ctypes
@@ -218,6 +218,11 @@ def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, spli
     P = (cin + 15) // 16 * 16
     span = P
     coutp = (cout + 31) // 32 * 32 if split_out else (cout + 15) // 16 * 16
+    opl = coutp                                  # channels per output plane
+    if tl:                                       # tap lanes: 128 MMA rows; output planes of 16 (Cout <= 16) or 32*ceil(Cout/32) channels
+        assert cout <= 64 and stride == 1
+        opl = 16 if cout <= 16 else (cout + 31) // 32 * 32
+        coutp = 128
     kc = pick_kc(span, stride, 1, W=W, coutp=coutp)
     dev = x32.device
     xin = torch.zeros(N, H, W, 2 * P if split_in else P, device=dev, dtype=dt)
@@ -226,6 +231,17 @@ def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, spli
     if split_in:
         xin[..., P:P + cin] = lo
     w32 = weight.detach().float().contiguous()
+    wrows = cout
+    if tl:
+        ws = torch.zeros(128, cin, 3, 3, device=dev, dtype=torch.float32)
+        if cout <= 32:
+            for l in range(3):
+                ws[32 * l:32 * l + cout, :, 0, :] = w32[:, :, l, :]
+        else:
+            ws[0:cout, :, 0, :] = w32[:, :, 0, :]
+            ws[64:64 + cout, :, 0, :] = w32[:, :, 1, :]
+            ws[0:cout, :, 1, :] = w32[:, :, 2, :]
+        w32, wrows = ws, 128
     import os
     fused = split_in and stride == 2 and P == span == kc and kc <= 32 and os.environ.get("PWC_TC_FUSED_SPLIT", "1") != "0"
     kc_pack = kc
@@ -238,14 +254,14 @@ def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, spli
         wv, cm, vspan = w32, list(range(cin)), (span + kc - 1) // kc * kc
     wp = torch.zeros(9 * vspan * coutp, device=dev, dtype=dt)
     mp = torch.tensor(cm, device=dev, dtype=torch.int32)
-    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wv), _lib.ptr(wp), _lib.ptr(mp), cout, wv.shape[1], vspan, kc_pack, coutp, st), "pack")
+    _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wv), _lib.ptr(wp), _lib.ptr(mp), wrows, wv.shape[1], vspan, kc_pack, coutp, st), "pack")
     ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
-    out = torch.zeros(N, ho, wo, 2 * coutp if split_out else coutp, device=dev, dtype=dt)
+    out = torch.zeros(N, ho, wo, 2 * opl if split_out else opl, device=dev, dtype=dt)
     b32 = bias.detach().float().contiguous()
     h = ctypes.c_void_p()
     e = lib.pwc_tc_conv_create_split(ctypes.byref(h), _lib.ptr(xin), xin.shape[-1], 0, None, 0, 0, N, span, kc, _lib.ptr(wp),
-                                     _lib.ptr(b32), cout, coutp, _lib.ptr(out), out.shape[-1], 0, None, 0, 0, 0, None, 0,
-                                     N, H, W, stride, 1, slope, P if split_in else 0, coutp if split_out else 0, 0, 0)
+                                     _lib.ptr(b32), cout, coutp, _lib.ptr(out), out.shape[-1], 0, None, 0, 0, 32 if tl else 0, None, 0,
+                                     N, H, W, stride, 1, slope, P if split_in else 0, opl if split_out else 0, 0, 0)
     _lib.check(e, "pwc_tc_conv_create_split")
     try:
         _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
@@ -261,7 +277,7 @@ def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, spli
         lib.pwc_tc_conv_destroy(h)
     res = out[..., :cout].float()
     if split_out:
-        res = res + out[..., coutp:coutp + cout].float()
+        res = res + out[..., opl:opl + cout].float()
     return res
 
 

@@ -72,3 +72,18 @@ def test_conv3x3_thin_split_matches_fp32(case, fmt):
     out = out.permute(0, 3, 1, 2).cpu()
     tol = TOL if fmt == "f16" else 3e-4
     assert (out - ref).abs().max().item() <= tol * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("case", [(16, 16, 2, 224, 512), (32, 32, 2, 112, 256), (16, 16, 1, 37, 70), (32, 32, 3, 9, 21), (64, 64, 1, 56, 128),
+                                  (533, 32, 1, 28, 64), (565, 64, 2, 14, 32)])
+def test_conv3x3_tc_split_tap_lanes(case):
+    """split input and output on the tap-lane form of the tcgen05 kernel (pyramid levels 1-2 of the mixed plan; decoder shapes)"""
+    from opticalflow_b200 import ops
+    cin, cout, N, H, W = case
+    x, w, b = _case(cin, cout, N, H, W, 1000 + cin + cout)
+    ref = F.leaky_relu(F.conv2d(x, w, b, padding=1), 0.1)
+    d = torch.device("cuda:0")
+    with ops.half_format("f16"):
+        out = ops.conv3x3_tc_split(x.permute(0, 2, 3, 1).contiguous().to(d), w.to(d), b.to(d), tl=True)
+    out = out.permute(0, 3, 1, 2).cpu()
+    assert (out - ref).abs().max().item() <= TOL * ref.abs().max().item()
