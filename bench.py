@@ -206,10 +206,16 @@ def gpu_reference_baseline(dev, B, H, W, steps=5):
 
 
 def ncu_traffic(layer):
-    """DRAM bytes per launch of `layer` from the committed ncu --set full capture (profiles/r1_ncu_traffic.json), or None."""
-    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")
+    """DRAM bytes per launch of `layer` from the committed ncu --set full capture (profiles/r2_ncu_traffic.json), or None --
+    also None when the kernel's source files changed since the capture (the entry carries their sha256)."""
+    import hashlib
+    p = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
     try:
-        return json.load(open(p)).get(layer, {}).get("bytes")
+        e = json.load(open(p)).get(layer, {})
+        m = hashlib.sha256()
+        for f in e["source_files"]:
+            m.update(open(os.path.join(ROOT, f), "rb").read())
+        return e.get("bytes") if m.hexdigest()[:16] == e["source_sha"] else None
     except Exception:  # noqa: BLE001
         return None
 
@@ -392,7 +398,7 @@ def run_ours(args):
         peak = peaks["bf16_tflops"]
         roof = {"bound": "tensor", "achieved": tc_f / tc_t / 1e12, "peak": peak, "unit": "TFLOP/s",
                 "frac": tc_f / tc_t / 1e12 / peak, "traffic": ncu_traffic(top[0]),
-                "traffic_note": f"DRAM bytes of ONE launch of the top layer ({top[0]}), ncu --set full (profiles/r1_ncu_traffic.json)",
+                "traffic_note": f"DRAM bytes of ONE launch of the top layer ({top[0]}), ncu --set full (profiles/r2_ncu_traffic.json)",
                 "kernel": "conv_tc_wm_kernel / conv_tc_halo_kernel / conv_tc_kernel (tcgen05 3x3 convolutions) + "
                           "conv_mma_small_kernel (level-6 layers)",
                 "launches_per_step": len(tc), "share_of_step": tc_t / all_t,
@@ -431,7 +437,7 @@ def run_ours(args):
                 cb += by; ct += t_
         roof_corr = {"bound": "hbm", "achieved": cb / ct / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": cb / ct / 1e9 / peaks["hbm_gbs"], "traffic": ncu_traffic("warp_corr2"),
-                     "traffic_note": "DRAM bytes of the level-2 launch alone (ncu --set full, profiles/r1_ncu_traffic.json)", "levels": lv,
+                     "traffic_note": "DRAM bytes of the level-2 launch alone (ncu --set full, profiles/r2_ncu_traffic.json)", "levels": lv,
                      "kernel": "warp_corr_tc_kernel (levels 2,3: tcgen05) / warp_corr_mma_kernel (levels 4-6: mma.sync)",
                      "note": "the 5 cost-volume launches of one forward (bf16 features in the concat buffers); each launch captured 8x into "
                              "a CUDA graph and timed with CUDA events (no host launch cost); algorithmic bytes B*H*W*(2*C*2 + 81*2 + 8)"}
