@@ -181,6 +181,9 @@ int pwc_tc_conv_set_skip(pwc_tc_conv* handle, const unsigned long long* masks);
 int pwc_tc_conv_set_kk_skip(pwc_tc_conv* handle, const int* masks);
 int pwc_tc_conv_set_out_groups(pwc_tc_conv* handle, int g, long group_pitch);
 void pwc_tc_conv_destroy(pwc_tc_conv* handle);
+/* kernels ONE pwc_tc_conv_launch of the handle enqueues: 1, or 2 for small layers that run as deterministic two-pass split-K
+ * (conv kernel storing per-CTA fp32 partial tiles to handle-owned scratch + a reduce kernel); for launch accounting. */
+int pwc_tc_conv_num_launches(const pwc_tc_conv* handle);
 /* Split-K launch of a created handle that ALLOCATES NOTHING.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  The split-K form of the tcgen05 kernel (`ksplit` CTAs share one pixel tile, each a range of

@@ -795,6 +795,9 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
 
 extern "C" void pwc_tc_conv_destroy(pwc_tc_conv* h) { delete h; }
 
+// kernels one pwc_tc_conv_launch of this handle enqueues (2 = deterministic two-pass split-K: conv kernel + reduce kernel)
+extern "C" int pwc_tc_conv_num_launches(const pwc_tc_conv* h) { return !h ? 0 : (h->halo == 2 && h->wp.ks2pass) ? 2 : 1; }
+
 extern "C" int pwc_tc_conv_create_split(pwc_tc_conv** handle,
                                         const void* in, long in_pitch, int in_coff,
                                         const void* in2, long in2_pitch, int in2_coff, int n_split, int cin_span, int kc,

@@ -308,7 +308,9 @@ static int launch_warp_corr_mma(const WarpCorrParams& g, cudaStream_t s) {
   p.nk = cdiv(g.C, 16);
   p.pitch = 32 * p.nk + 16;
   static const int r_env = []() { const char* e = getenv("PWC_CORR_MMA_R"); return e ? atoi(e) : 0; }();
-  int R = r_env > 0 ? r_env : 4;
+  // rows per block: 4; 2 while blocks of 4 rows leave more than half of the SMs without an item (levels 5 and 6 at batch 8:
+  // 12.9 -> 9.9 us and 13.3 -> 10.4 us; level 4 with 112 items is faster at 4: 13.7 vs 17.5 us)
+  int R = r_env > 0 ? r_env : ((long)g.B * cdiv(g.W, XS) * cdiv(g.H, 4) * 2 <= num_sms ? 2 : 4);
   int smem = 0;
   for (;; R >>= 1) {
     const int ring = (R + 8) * WX * p.pitch, f1b = R * XS * p.pitch;

@@ -467,7 +467,7 @@ class PlanBF16:
             uo = (_lib.ptr(self.flow_out4), 4, 0, _lib.ptr(self.out), B, h, w, 1.0)
             self.op_info.append(("unpack_flow", 0.0))
             self.ops.append(lambda st: _lib.check(lib.pwc_unpack_flow_f32(*uo, st), "unpack_flow"))
-        self.launches = len(self.ops)
+        self.launches = len(self.ops) + sum(self.lib.pwc_tc_conv_num_launches(L.handle) - 1 for L in self.layers.values() if L.handle)
 
     # ------------------------------------------------------------------ weights
     def pack_weights(self, model):

@@ -257,4 +257,4 @@ class PlanMixed(PlanBF16):
               _lib.ptr(self.out), B, h, w)
         self.op_info.append(("dc_conv7", 2.0 * B * h * w * 2 * 32 * 9))
         self.ops.append(lambda st: _lib.check(lib.pwc_conv3x3_flow_head_fwd(*ha, st), "dc_conv7"))
-        self.launches = len(self.ops)
+        self.launches = len(self.ops) + sum(lib.pwc_tc_conv_num_launches(L.handle) - 1 for L in self.layers.values() if L.handle)
