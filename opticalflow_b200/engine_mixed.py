@@ -35,8 +35,10 @@ SPLIT_LEVELS = tuple(int(v) for v in os.environ.get("PWC_MIXED_LEVELS", "5,4").s
 # the B200 0.0131 -> 0.0149 / 0.0091 -> 0.0103 / 0.0130 -> 0.0151 px at 1024x448 for a third less tensor work there; dropping
 # W_lo in the pyramid instead costs 0.025-0.028 px (PWC_MIXED_DEC_PRODUCTS=3 restores the full split)
 DEC_PRODUCTS = int(os.environ.get("PWC_MIXED_DEC_PRODUCTS", "2"))
-# levels 1-2 stride-1 layers on the tcgen05 tap-lane kernel instead of the mma.sync one: measured 458 / 120 us against 89 / 77 us
-# (one 64-channel chunk per tile: nine 16 KB weight tiles stream from L2 for nine MMAs) -- off
+# levels 1-2 stride-1 layers on the tcgen05 tap-lane kernel instead of the mma.sync one: measured 458 / 120 us against 89 / 77 us.
+# Not a weight-streaming problem (a narrow resident-weight chunk gave 450 us): the ncu source page (tools/prof_tl.py) shows the
+# three epilogue warps issue ~3500 instructions per 240-pixel tile at ~0.3 IPC each (96 fp32 TMEM values summed through shared
+# memory per 16-channel output pixel, then the hi/lo split), 16.6k cycles per tile against 2.6k of MMA issue -- off
 THIN_TC = os.environ.get("PWC_MIXED_THIN_TC", "0") != "0"
 KP_LO, KP_DUP = 4, 8                    # K padding: lo copies of up_flow|up_feat at +4 (533..536), second hi copies at +8
 
