@@ -238,6 +238,12 @@ int pwc_conv3x3_thin_split_fwd(const void* in, long in_pitch, int in_coff, int c
                                const void* w_packed, const float* bias, int cout,
                                void* out, long out_pitch, int out_coff,
                                int N, int H, int W, float slope, void* stream);
+/* the same layer at stride 1 or 2 (stride 2: cin = 16 only -- conv2a of the 'mixed' plan, 16 -> 32 channels, PWCNet.py:54,186 --
+ * wider pixels do not fit two input patches in shared memory: cudaErrorInvalidValue; H, W are the INPUT dims) */
+int pwc_conv3x3_thin_split_strided_fwd(const void* in, long in_pitch, int in_coff, int cin,
+                                       const void* w_packed, const float* bias, int cout,
+                                       void* out, long out_pitch, int out_coff,
+                                       int N, int H, int W, int stride, float slope, void* stream);
 int pwc_conv1a_split_fwd(const float* x, const float* w, const float* bias, void* out,
                          int B, int H, int W, float slope, int frames, void* stream);
 int pwc_deconv4x4s2_c2_split_fwd(const void* in, int in_dtype, long in_pitch, int in_coff, int Cin,

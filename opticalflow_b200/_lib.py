@@ -33,6 +33,7 @@ SIGNATURES = {
     "pwc_tc_conv_create_split": (_i, [ctypes.POINTER(_vp), _vp, _l, _i, _vp, _l, _i, _i, _i, _i, _vp, _vp, _i, _i,
                                       _vp, _l, _i, _vp, _l, _i, _i, _vp, _l, _i, _i, _i, _i, _i, _f, _i, _i, _i, _i]),
     "pwc_conv3x3_thin_split_fwd": (_i, [_vp, _l, _i, _i, _vp, _vp, _i, _vp, _l, _i, _i, _i, _i, _f, _vp]),
+    "pwc_conv3x3_thin_split_strided_fwd": (_i, [_vp, _l, _i, _i, _vp, _vp, _i, _vp, _l, _i, _i, _i, _i, _i, _f, _vp]),
     "pwc_conv1a_split_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp]),
     "pwc_deconv4x4s2_c2_split_fwd": (_i, [_vp, _i, _l, _i, _i, _vp, _vp, _vp, _i, _l, _i, _vp, _l, _i, _i, _i, _i, _i, _vp]),
     "pwc_copy_channels_h16": (_i, [_vp, _l, _i, _vp, _l, _i, _i, _l, _vp]),

@@ -40,10 +40,39 @@ struct TcConvParams {
   const float* residual; long res_pitch;
   int fp16;                                       // 16-bit operands / outputs are IEEE half instead of bf16
   int split, lo_off, out_lo_off;                  // split precision: see WmParams::split (conv_tc_wm.cuh)
+  uint32_t w_resident, w_tile;                    // the whole packed weight set (9 * nchunk tiles of w_tile bytes) stays in shared memory
+                                                  // behind the A ring: a stage is the A box alone (streamed, the weight tile is half of
+                                                  // every stage's bytes and the L2 -> SM ingest, ~30 B/cycle, is what bounds these layers)
+  int xdup;                                       // split == 3: the (x_hi, W_lo) chunk reuses the A box of the (x_hi, W_hi) chunk before it
+  int pairs;                                      // stride 2 without TMA element strides (which fetch the skipped pixels too: half of
+                                                  // the ingest): tmA0 / tmA1 = the even / odd input rows as (C, column parity, W/2,
+                                                  // rows, N); tap (ky, kx) = a dense box of map (ky != 1), parity (kx != 1), shifted by
+                                                  // -1 pair / row for kx == 0 / ky == 0
   int fused;                                      // split input whose planes are adjacent and fit one swizzle row ([hi | lo] <= 64
                                                   // channels): kc counts BOTH planes, one stage = the A box + two weight tiles
                                                   // [W_hi | W_hi] and [W_lo | 0]; the second runs on the hi half only
 };
+
+// 16 output channels of one pixel: 16-bit rounding and 2 x 16-byte stores; LO: the rounding residuals go to the lo plane
+template <bool F16>
+__device__ __forceinline__ void tc_store16(const float* f, uint16_t* o, int lo_off) {
+  uint32_t w[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) w[i] = pack2_h16(f[2 * i], f[2 * i + 1], F16 ? 1 : 0);
+  uint4* o4 = reinterpret_cast<uint4*>(o);
+  o4[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  o4[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  if (lo_off) {                                   // lo plane: the exact remainders of the hi roundings
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 hv = unpack2_h16(w[i], F16 ? 1 : 0);
+      w[i] = pack2_h16(f[2 * i] - hv.x, f[2 * i + 1] - hv.y, F16 ? 1 : 0);
+    }
+    uint4* l4 = reinterpret_cast<uint4*>(o + lo_off);
+    l4[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    l4[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  }
+}
 
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
@@ -51,7 +80,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-B aligned base (SWIZZLE_128B atoms)
   const uint32_t base = (ptx::smem_addr(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = base + p.stages * p.stage_bytes;
+  const uint32_t w_base = base + p.stages * p.stage_bytes;           // resident weight set (w_resident)
+  const uint32_t bar_base = w_base + (p.w_resident ? 9u * p.nchunk * p.w_tile : 0u);
+  const uint32_t w_all = bar_base + 8u * (2 * p.stages + 6);
+  // bias, zero padded to coutp, in shared memory: the epilogue thread (= one pixel) needs every channel's bias, and a global
+  // load per value put an L2 round trip on the one epilogue warp of each scheduler (ncu: the top stall of the stride-2 layers)
+  float* sbias = reinterpret_cast<float*>(smem_raw + (bar_base + 8u * (2 * p.stages + 8) - ptx::smem_addr(smem_raw)));
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (p.stages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * p.stages + a); };
@@ -67,8 +101,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     ptx::prefetch_tmap(&tmA0); ptx::prefetch_tmap(&tmA1); ptx::prefetch_tmap(&tmB);
     for (int s = 0; s < p.stages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 4); }
+    ptx::mbar_init(w_all, 1);
     ptx::fence_barrier_init();
     ptx::fence_proxy_async();
+    if (p.w_resident) {                                // weights do not depend on the previous kernel: before the PDL wait
+      ptx::mbar_expect_tx(w_all, 9u * p.nchunk * (uint32_t)p.coutp * p.kc * 2u);
+      for (int j = 0; j < 9 * p.nchunk; ++j) ptx::tma_load_2d(w_base + j * p.w_tile, &tmB, w_all, 0, j * p.coutp);
+    }
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, p.tmem_cols);
   ptx::tc_fence_before();
@@ -95,22 +134,28 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             ptx::mbar_wait(empty_bar(s), ph ^ 1);
             if (ptx::elect_one()) {
               const uint32_t sa = base + s * p.stage_bytes, bb = (uint32_t)p.coutp * p.kc * 2;
-              ptx::mbar_expect_tx(full_bar(s), p.a_bytes + 2 * bb);
-              ptx::tma_load_4d(sa, tmA, full_bar(s), 0, x, y, nn);
-              ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * 2) * p.coutp);
-              ptx::tma_load_2d(sa + p.a_bytes + bb, &tmB, full_bar(s), 0, (tap * 2 + 1) * p.coutp);
+              ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (p.w_resident ? 0u : 2 * bb));
+              if (p.pairs) ptx::tma_load_5d(sa, ky == 1 ? &tmA0 : &tmA1, full_bar(s), 0, kx != 1, tx0 - (kx == 0), ty0 - (ky == 0), nn);
+              else ptx::tma_load_4d(sa, tmA, full_bar(s), 0, x, y, nn);
+              if (!p.w_resident) {
+                ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * 2) * p.coutp);
+                ptx::tma_load_2d(sa + p.a_bytes + bb, &tmB, full_bar(s), 0, (tap * 2 + 1) * p.coutp);
+              }
             }
             __syncwarp();
             if (++s == p.stages) { s = 0; ph ^= 1; }
             continue;
           }
           for (int ch = 0; ch < p.nchunk; ++ch) {
+            if (p.xdup && ch % 3 == 1) continue;       // resident weights: the MMA warp reuses the stage of chunk ch - 1
             ptx::mbar_wait(empty_bar(s), ph ^ 1);
             if (ptx::elect_one()) {
               const uint32_t sa = base + s * p.stage_bytes;
-              ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (uint32_t)p.coutp * p.kc * 2);
-              ptx::tma_load_4d(sa, tmA, full_bar(s), p.split ? (ch / p.split) * p.kc + ((ch % p.split) == p.split - 1 ? p.lo_off : 0) : ch * p.kc, x, y, nn);
-              ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * p.nchunk + ch) * p.coutp);
+              ptx::mbar_expect_tx(full_bar(s), p.a_bytes + (p.w_resident ? 0u : (uint32_t)p.coutp * p.kc * 2));
+              const int xc = p.split ? (ch / p.split) * p.kc + ((ch % p.split) == p.split - 1 ? p.lo_off : 0) : ch * p.kc;
+              if (p.pairs) ptx::tma_load_5d(sa, ky == 1 ? &tmA0 : &tmA1, full_bar(s), xc, kx != 1, tx0 - (kx == 0), ty0 - (ky == 0), nn);
+              else ptx::tma_load_4d(sa, tmA, full_bar(s), xc, x, y, nn);
+              if (!p.w_resident) ptx::tma_load_2d(sa + p.a_bytes, &tmB, full_bar(s), 0, (tap * p.nchunk + ch) * p.coutp);
             }
             __syncwarp();
             if (++s == p.stages) { s = 0; ph ^= 1; }
@@ -127,28 +172,35 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
       const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
       int s = 0; uint32_t ph = 0;
       int acc = 0; uint32_t aph = 0;
+      if (p.w_resident) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
       for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
         ptx::mbar_wait(tempty_bar(acc), aph ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.coutp);
         for (int k = 0; k < ksteps; ++k) {
-          ptx::mbar_wait(full_bar(s), ph);
-          ptx::tc_fence_after();
+          // k = tap * nchunk + ch (fused: k = tap).  xdup: chunk ch % 3 == 1 multiplies the stage chunk ch - 1 left in place
+          const int ch = p.fused ? 0 : k % p.nchunk;
+          const bool reuse = p.xdup && ch % 3 == 1, keep = p.xdup && ch % 3 == 0;
+          if (!reuse) {
+            ptx::mbar_wait(full_bar(s), ph);
+            ptx::tc_fence_after();
+          }
           if (ptx::elect_one()) {
             const uint32_t sa = base + s * p.stage_bytes;
+            const uint32_t sb = p.w_resident ? w_base + (uint32_t)(p.fused ? 2 * k : k) * p.w_tile : sa + p.a_bytes;
             const uint64_t da = ptx::make_kmajor_desc(sa, 8 * row_bytes, ltype);
-            const uint64_t db = ptx::make_kmajor_desc(sa + p.a_bytes, 8 * row_bytes, ltype);
+            const uint64_t db = ptx::make_kmajor_desc(sb, 8 * row_bytes, ltype);
             for (int kk = 0; kk < p.kc / 16; ++kk)
               ptx::umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (k | kk) ? 1u : 0u);
             if (p.fused) {                            // x_hi * W_lo: the hi half of the box against the second weight tile
-              const uint64_t db2 = ptx::make_kmajor_desc(sa + p.a_bytes + (uint32_t)p.coutp * row_bytes, 8 * row_bytes, ltype);
+              const uint64_t db2 = ptx::make_kmajor_desc(sb + (p.w_resident ? p.w_tile : (uint32_t)p.coutp * row_bytes), 8 * row_bytes, ltype);
               for (int kk = 0; kk < p.kc / 32; ++kk) ptx::umma_bf16(d_tmem, da + 2 * kk, db2 + 2 * kk, idesc, 1u);
             }
-            ptx::umma_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
+            if (!keep) ptx::umma_commit(empty_bar(s));          // frees the smem stage when these MMAs retire
             if (k == ksteps - 1) ptx::umma_commit(tfull_bar(acc));   // accumulator complete -> epilogue
           }
           __syncwarp();
-          if (++s == p.stages) { s = 0; ph ^= 1; }
+          if (!keep && ++s == p.stages) { s = 0; ph ^= 1; }
         }
         if (++acc == 2) { acc = 0; aph ^= 1; }
       }
@@ -159,6 +211,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const int m = lg * 32 + lane;                  // pixel within the tile
     const int py = m >> 4, px = m & 15;
     int acc = 0; uint32_t aph = 0;
+    for (int i = threadIdx.x - 64; i < p.coutp; i += 128) sbias[i] = (i < p.cout) ? __ldg(p.bias + i) : 0.f;
+    asm volatile("bar.sync 1, 128;" ::: "memory");
     for (int t = blockIdx.x; t < p.num_tiles; t += gridDim.x) {
       const int n = t / (p.tiles_x * p.tiles_y);
       const int r = t - n * (p.tiles_x * p.tiles_y);
@@ -177,10 +231,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         if (live) {
           float f[16];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int co = c0 + i;
-            const float b = (co < p.cout) ? __ldg(p.bias + co) : 0.f;
-            f[i] = lrelu(__uint_as_float(v[i]) + b, p.slope);
+          for (int q = 0; q < 4; ++q) {
+            const float4 b4 = *reinterpret_cast<const float4*>(sbias + c0 + 4 * q);
+            f[4 * q + 0] = lrelu(__uint_as_float(v[4 * q + 0]) + b4.x, p.slope);
+            f[4 * q + 1] = lrelu(__uint_as_float(v[4 * q + 1]) + b4.y, p.slope);
+            f[4 * q + 2] = lrelu(__uint_as_float(v[4 * q + 2]) + b4.z, p.slope);
+            f[4 * q + 3] = lrelu(__uint_as_float(v[4 * q + 3]) + b4.w, p.slope);
           }
           if (p.out_f32) {
             float* o = reinterpret_cast<float*>(p.out) + pix * p.out_pitch + p.out_coff;
@@ -194,24 +250,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
               }
             }
           } else {
-            __nv_bfloat16* o = second ? reinterpret_cast<__nv_bfloat16*>(p.out2) + pix * p.out2_pitch + p.out2_coff
-                                      : reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.out_pitch + p.out_coff;
-            uint32_t w[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) w[i] = pack2_h16(f[2 * i], f[2 * i + 1], p.fp16);
-            uint4* o4 = reinterpret_cast<uint4*>(o + c0);
-            o4[0] = make_uint4(w[0], w[1], w[2], w[3]);
-            o4[1] = make_uint4(w[4], w[5], w[6], w[7]);
-            if (p.out_lo_off) {                     // lo plane: the exact remainders of the hi roundings
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float2 hv = unpack2_h16(w[i], p.fp16);
-                w[i] = pack2_h16(f[2 * i] - hv.x, f[2 * i + 1] - hv.y, p.fp16);
-              }
-              uint4* l4 = reinterpret_cast<uint4*>(o + c0 + p.out_lo_off);
-              l4[0] = make_uint4(w[0], w[1], w[2], w[3]);
-              l4[1] = make_uint4(w[4], w[5], w[6], w[7]);
-            }
+            uint16_t* o = second ? reinterpret_cast<uint16_t*>(p.out2) + pix * p.out2_pitch + p.out2_coff
+                                 : reinterpret_cast<uint16_t*>(p.out) + pix * p.out_pitch + p.out_coff;
+            if (p.fp16) tc_store16<true>(f, o + c0, p.out_lo_off);
+            else tc_store16<false>(f, o + c0, p.out_lo_off);
           }
         }
       }
@@ -359,17 +401,55 @@ static int make_tmap_xsplit(CUtensorMap* m, const void* base, long pitch, int C,
   return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
 }
 
+// Rows of one parity of an NHWC slice, W split as (W/2, 2): 5-D (C, column parity, W/2, rows, N) with a two-row row stride;
+// `base` points at the first row of that parity, img_elems = elements per image.  Box (boxC, 1, boxPairs, boxH, 1), dense.
+static int make_tmap_pairs_rows(CUtensorMap* m, const void* base, long pitch, int C, int W, int rows, int N, long img_elems,
+                                int boxC, int boxPairs, int boxH, CUtensorMapSwizzle swz) {
+  EncodeTiledFn enc = get_encode_tiled();
+  if (!enc) return (int)cudaErrorNotSupported;
+  cuuint64_t dims[5] = {(cuuint64_t)C, 2, (cuuint64_t)(W / 2), (cuuint64_t)rows, (cuuint64_t)N};
+  cuuint64_t strides[4] = {(cuuint64_t)pitch * 2, (cuuint64_t)pitch * 4, (cuuint64_t)pitch * 2 * W * 2, (cuuint64_t)img_elems * 2};
+  cuuint32_t box[5] = {(cuuint32_t)boxC, 1, (cuuint32_t)boxPairs, (cuuint32_t)boxH, 1};
+  cuuint32_t es[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+// NHWC slice with W split as (W/2, 2): 5-D (C, column parity, W/2, H, N); box (boxC, 1, boxPairs, boxH, 1) = the columns of one
+// parity of a stride-2 layer's input tile, dense.  Needs W % 2 == 0.
+static int make_tmap_pairs(CUtensorMap* m, const void* base, long pitch, int C, int W, int H, int N,
+                           int boxC, int boxPairs, int boxH, CUtensorMapSwizzle swz) {
+  EncodeTiledFn enc = get_encode_tiled();
+  if (!enc) return (int)cudaErrorNotSupported;
+  cuuint64_t dims[5] = {(cuuint64_t)C, 2, (cuuint64_t)(W / 2), (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[4] = {(cuuint64_t)pitch * 2, (cuuint64_t)pitch * 4, (cuuint64_t)pitch * 2 * W,
+                           (cuuint64_t)pitch * 2 * W * H};
+  cuuint32_t box[5] = {(cuuint32_t)boxC, 1, (cuuint32_t)boxPairs, (cuuint32_t)boxH, 1};
+  cuuint32_t es[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
 static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in_coff, int cin_span, int kc,
                      const void* w_packed, const float* bias, int cout, int coutp,
                      void* out, long out_pitch, int out_coff, void* out2, long out2_pitch, int out2_coff, int n_split,
-                     int out_f32, const float* residual, long res_pitch, int N, int H, int W, int dil, float slope) {
+                     int out_f32, const float* residual, long res_pitch, int N, int H, int W, int dil, float slope, int stride = 1) {
   if (coutp % 16 || coutp < 16 || coutp > 128 || cout > coutp || (in_pitch & 7) || (in_coff & 7))
     return (int)cudaErrorInvalidValue;
+  // stride 2 (WmParams::s2): from here on H, W are the OUTPUT dims (tiles, stores); Hin, Win describe the input map
+  const int s2 = stride == 2 ? 1 : 0, Hin = H, Win = W;
+  if (stride != 1 && stride != 2) return (int)cudaErrorInvalidValue;
+  if (s2) {
+    if (dil != 1 || (W & 1) || out_f32 || (kc != 16 && kc != 32 && kc != 64) || cin_span % kc) return (int)cudaErrorInvalidValue;
+    H = (H + 1) / 2; W = W / 2;
+  }
   const int ts = (out_f32 >> 4) & 1;              // tap-stacked weights ([chunk][tap*cout + co][64] in the tap-0 section)
   const int tlf = (out_f32 >> 5) & 1;             // tap-lane weights (WmParams::tl): cout <= 64 real channels, coutp = 128 rows
   out_f32 &= 3;
-  if (tlf && (ts || dil != 1 || cout > 64 || coutp != 128 || out_f32 || kc != 64 || out2)) return (int)cudaErrorInvalidValue;
-  if (ts && (dil != 1 || 9 * cout > 128 || coutp != 128 || !out_f32 || kc != 64)) return (int)cudaErrorInvalidValue;
+  if (tlf && (ts || dil != 1 || cout > 64 || coutp != 128 || out_f32 || kc != 64 || out2 || s2)) return (int)cudaErrorInvalidValue;
+  if (ts && (dil != 1 || 9 * cout > 128 || coutp != 128 || !out_f32 || kc != 64 || s2)) return (int)cudaErrorInvalidValue;
   pwc_tc_conv* h = new (std::nothrow) pwc_tc_conv();
   if (!h) return (int)cudaErrorMemoryAllocation;
   h->halo = 2;
@@ -384,9 +464,15 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.N = N; p.H = H; p.W = W; p.dil = dil;
   p.split = g_split.in_lo_off ? g_split.products : 0; p.lo_off = g_split.in_lo_off; p.out_lo_off = g_split.out_lo_off;
   p.up_lo_off = g_split.up_lo_off; p.up_dup_off = g_split.up_dup_off;
-  const int vmul = p.split ? p.split : 1;           // virtual chunks per logical chunk (see WmParams::split)
+  int vmul = p.split ? p.split : 1;                 // virtual chunks per logical chunk (see WmParams::split)
+  p.s2 = s2; p.x_sub = 0;
+  // adjacent [hi | lo] planes that fit one swizzle row (stride-2 pyramid layers of 16 / 32 channels): one chunk of both planes,
+  // weights [W_hi | W_hi] then [W_lo | 0] (the layout of TcConvParams::fused)
+  p.fused = (s2 && p.split == 3 && p.lo_off == cin_span && cin_span == kc && kc <= 32 && env_int("PWC_TC_FUSED_SPLIT", 1)) ? 1 : 0;
+  if (p.fused) { kc *= 2; cin_span = kc; p.split = 0; p.lo_off = 0; vmul = 2; }
+  p.xdup = (s2 && (p.fused || p.split == 3) && env_int("PWC_TC_WM_XDUP", 1)) ? 1 : 0;   // (stride 1: measured no gain)
   p.cout = cout; p.coutp = coutp; p.kc = kc; p.nchunk = cdiv(cin_span, kc) * vmul;
-  if ((p.split || p.out_lo_off) && (dil != 1 || kc != 64 || (p.lo_off & 7) || (p.out_lo_off & 7))) { delete h; return (int)cudaErrorInvalidValue; }
+  if ((p.split || p.out_lo_off) && (dil != 1 || (kc != 64 && !s2) || (p.lo_off & 7) || (p.out_lo_off & 7))) { delete h; return (int)cudaErrorInvalidValue; }
   // large dilations: phases in x only, the y dilation is a row shift inside a (rows + 2*dil)-row halo tile -- 16 x fewer,
   // 16 x larger items than d x d sub-lattices of a 7 x 16 image (dc_conv5: N = 56 pixels per MMA otherwise)
   const int ydense = (dil >= env_int("PWC_TC_WM_YDENSE_MINDIL", 8) && !ts) ? 1 : 0;
@@ -397,6 +483,8 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   const int nph = ydense ? dil : dil * dil;
   int max_rows = (256 / dil - 2) < 32 ? ((256 / dil - 2) & ~1) : 32;
   if (ydense) { max_rows = 50 - 2 * dil; if (max_rows > 32) max_rows = 32; max_rows &= ~1; }
+  auto s2_sub = [&](int r) { return ((uint32_t)(2 * r + 1) * 9u * (uint32_t)kc * 2u + 1023u) & ~1023u; };   // one parity's sub-tile
+  if (s2) while (max_rows > 2 && 4u * s2_sub(max_rows) > 116u * 1024u) max_rows -= 2;
   auto even_up = [](int v) { return (v + 1) & ~1; };
   auto ntiles = [&](int rows) { return (long)N * nph * cdiv(Hd, rows) * cdiv(Wd, 8); };
   int rows = even_up(cdiv(Hd, cdiv(Hd, max_rows)));           // fewest row tiles, least padding
@@ -447,6 +535,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   const int xextra = p.tl == 2 ? 2 : 0;
   p.x_bytes_tx = (uint32_t)(rows + 2 * p.kyr + xextra) * 10u * row_bytes;
   p.x_bytes = (p.x_bytes_tx + 1023u) & ~1023u;
+  if (s2) { p.x_sub = s2_sub(rows); p.x_bytes_tx = 2u * (uint32_t)(2 * rows + 1) * 9u * row_bytes; p.x_bytes = 2u * p.x_sub; }
   if (ts) {
     const uint32_t need = (uint32_t)p.npx * row_bytes;        // the MMA reads npx pixel rows (tail rows: don't-care columns)
     if (p.x_bytes < ((need + 1023u) & ~1023u)) p.x_bytes = (need + 1023u) & ~1023u;
@@ -537,7 +626,9 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
   int e = 0;
-  if (p.xsplit) {
+  if (s2) {
+    e = make_tmap_pairs(&h->tmA0, a0, in_pitch, cin_span + p.lo_off, Win, Hin, N, kc, 9, 2 * rows + 1, swz);
+  } else if (p.xsplit) {
     if (!p.wstore) e = (int)cudaErrorInvalidValue;
     if (!e) e = make_tmap_xsplit(&h->tmA0, a0, in_pitch, cin_span, W, H, N, dil, kc, 10, rows + 2 * dil, swz);
   } else {
@@ -631,6 +722,7 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
       cudaFuncSetAttribute(conv_tc_wm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
       cudaFuncSetAttribute(conv_tc_wm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
       cudaFuncSetAttribute(conv_tc_wm_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(conv_tc_wm_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
       attr_dev = dev;
     }
   }
@@ -641,6 +733,19 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
                             out2, out2_pitch, out2_coff, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope);
     if (!e || dil <= 8) return e;
     *handle = nullptr;                                     // dilation 16 outside the y-dense mode's shapes: per-tap kernel
+  }
+  // (measured: big stride-2 layers lose there -- four input pixels per output pixel make the halo tiles small, so Cout <= 32
+  // leaves one epilogue warp working and Cout >= 64 streams the whole weight set per 96-pixel tile; the layers whose 128-pixel
+  // per-tap tiles cannot fill the SMs gain from its split-K: conv5a 34 -> 21 us)
+  const long pt_tiles = (long)N * (((Hin - 1) / 2 + 1 + 7) / 8) * (((Win - 1) / 2 + 1 + 15) / 16);
+  const int s2_mode = env_int("PWC_TC_WM_S2", 1);
+  if (stride == 2 && dil == 1 && !in2 && !out2 && coutp <= 128 && !(Win & 1) && !out_f32 &&
+      (s2_mode == 2 || (s2_mode == 1 && pt_tiles < g_num_sms))) {
+    // stride 2 through the halo kernel's pair view (WmParams::s2); shapes it does not take fall through to the per-tap kernel
+    const int e = create_wm(handle, in, in_pitch, in_coff, cin_span, kc, w_packed, bias, cout, coutp, out, out_pitch, out_coff,
+                            nullptr, 0, 0, n_split, out_f32, residual, res_pitch, N, Hin, Win, dil, slope, 2);
+    if (!e) return 0;
+    *handle = nullptr;
   }
   if (out_f32 == 2) return (int)cudaErrorInvalidValue;     // fused predict_flow+upfeat exists in the WM kernel only
   if (halo_eligible(stride, dil, in2 != nullptr, kc)) {
@@ -667,7 +772,14 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   p.tiles_x = cdiv(p.Wout, kTcTW); p.tiles_y = cdiv(p.Hout, kTcTH); p.num_tiles = p.tiles_x * p.tiles_y * N;
   p.a_bytes = (uint32_t)kTcM * kc * 2;
   p.stage_bytes = (p.a_bytes + (uint32_t)coutp * kc * 2 * (p.fused ? 2 : 1) + 1023u) & ~1023u;
-  int stages = (int)((200u * 1024u) / p.stage_bytes);
+  p.w_tile = ((uint32_t)coutp * kc * 2 + 1023u) & ~1023u;
+  {
+    const uint32_t all_w = 9u * p.nchunk * p.w_tile, a_stage = (p.a_bytes + 1023u) & ~1023u;
+    p.w_resident = (all_w + 4u * a_stage <= 200u * 1024u && env_int("PWC_TC_RESIDENT", 1)) ? 1u : 0u;
+    if (p.w_resident) p.stage_bytes = a_stage;
+    p.xdup = (p.w_resident && p.split == 3 && !p.fused && env_int("PWC_TC_XDUP", 1)) ? 1 : 0;
+  }
+  int stages = (int)((200u * 1024u - (p.w_resident ? 9u * p.nchunk * p.w_tile : 0u)) / p.stage_bytes);
   p.stages = stages > 8 ? 8 : (stages < 2 ? 2 : stages);
   uint32_t cols = 32; while (cols < 2u * coutp) cols <<= 1;
   if (cols > 512) { delete h; return (int)cudaErrorInvalidValue; }
@@ -677,13 +789,23 @@ extern "C" int pwc_tc_conv_create(pwc_tc_conv** handle,
   p.out2 = out2; p.out2_pitch = out2_pitch; p.out2_coff = out2_coff;
   p.out_f32 = out_f32; p.residual = residual; p.res_pitch = res_pitch;
   p.fp16 = g_half_format;
-  h->smem_bytes = (size_t)p.stages * p.stage_bytes + 8 * (2 * p.stages + 5) + 1024;
+  h->smem_bytes = (size_t)p.stages * p.stage_bytes + (p.w_resident ? (size_t)9 * p.nchunk * p.w_tile : 0) + 8 * (2 * p.stages + 8) +
+                  (size_t)coutp * 4 + 1024;
   const CUtensorMapSwizzle swz = swizzle_for_bytes(kc * 2);
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(in) + in_coff;
   if (p.fused) cin_span = kc;                                        // both planes are one box now
-  int e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span + (p.fused ? 0 : p.lo_off), Win, Hin,
-                         in2 ? p.n_split : N, kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
-  if (!e) {
+  p.pairs = (stride == 2 && dil == 1 && !in2 && !(Win & 1) && Hin >= 2 && env_int("PWC_TC_PAIRS", 1)) ? 1 : 0;
+  int e = 0;
+  if (p.pairs) {
+    const int cs = cin_span + (p.fused ? 0 : p.lo_off);
+    e = make_tmap_pairs_rows(&h->tmA0, a0, in_pitch, cs, Win, (Hin + 1) / 2, N, (long)in_pitch * Win * Hin, kc, kTcTW, kTcTH, swz);
+    if (!e) e = make_tmap_pairs_rows(&h->tmA1, a0 + (long)in_pitch * Win, in_pitch, cs, Win, Hin / 2, N, (long)in_pitch * Win * Hin,
+                                     kc, kTcTW, kTcTH, swz);
+  } else {
+    e = make_tmap_nhwc(&h->tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a0, in_pitch, cin_span + (p.fused ? 0 : p.lo_off), Win, Hin,
+                       in2 ? p.n_split : N, kc, kTcTW * stride, kTcTH * stride, stride, stride, swz);
+  }
+  if (!e && !p.pairs) {
     if (in2) {
       const __nv_bfloat16* a1 = reinterpret_cast<const __nv_bfloat16*>(in2) + in2_coff;
       e = make_tmap_nhwc(&h->tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a1, in2_pitch, cin_span + (p.fused ? 0 : p.lo_off), Win, Hin, N - p.n_split,
@@ -770,7 +892,8 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
 #define PWC_WM_LAUNCH(MODE) \
   pwc::launch_pdl(pwc::conv_tc_wm_kernel<MODE>, dim3(h->grid), dim3(pwc::kHaloThreads), h->smem_bytes, st, h->tmA0, h->tmB, h->tmO, \
                   h->tmO2, h->wp)
-    if (h->wp.tl) PWC_WM_LAUNCH(4);
+    if (h->wp.s2) PWC_WM_LAUNCH(5);
+    else if (h->wp.tl) PWC_WM_LAUNCH(4);
     else if (h->wp.ts) PWC_WM_LAUNCH(1);
     else if (h->wp.has_skip) PWC_WM_LAUNCH(2);
     else if (h->wp.has_kk) PWC_WM_LAUNCH(3);
@@ -890,7 +1013,8 @@ extern "C" int pwc_tc_conv_launch_static_splitk(const pwc_tc_conv* h, int ksplit
   const int grid = v < nsm ? v : nsm;
   cudaLaunchConfig_t cfg = {};                                      // plain stream order (no programmatic early launch)
   cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kHaloThreads); cfg.dynamicSmemBytes = h->smem_bytes; cfg.stream = st;
-  if (p.has_skip) e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<2>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
+  if (p.s2) e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<5>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
+  else if (p.has_skip) e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<2>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
   else if (p.has_kk) e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<3>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
   else e = cudaLaunchKernelEx(&cfg, conv_tc_wm_kernel<0>, h->tmA0, h->tmB, h->tmO, h->tmO2, p);
   return (int)(e != cudaSuccess ? e : cudaGetLastError());

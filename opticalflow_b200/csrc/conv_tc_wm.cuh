@@ -48,6 +48,15 @@ struct WmParams {
   // accumulator row r + l holds its part of output row r, and the epilogue warps of a channel group add the lanes up through
   // the fp32 tile S (each warp takes another pixel block per phase, the last phase finishes the block).
   int tl, tl_bc;                                  // tl_bc: channels per output store box (16 for Cout <= 16, else 32)
+  // stride 2 (s2): H, W are the OUTPUT dims; the input is read through a pair view (C, col parity, W_in/2, H_in, N): one stage
+  // = two dense sub-tiles of (2*rows + 1) input rows x 9 column pairs, x_sub bytes apart -- [0] the odd columns, [1] the even
+  // ones -- so tap (ky, kx) is again a shifted start address: row ky (SBO = 2 tile rows = 18 pixel rows), pair (kx ? 1 : 0), sub-tile
+  // (kx == 1).  Every input pixel enters shared memory once, as whole 2*kc-byte rows (the per-tap kernel gathers it 2.25 times
+  // through element strides, at ~12 B/cycle/SM).
+  int s2; uint32_t x_sub;
+  // xdup: a virtual chunk that multiplies the same x tile as the one before it (split == 3: (x_hi, W_lo) after (x_hi, W_hi);
+  // fused: [W_lo | 0] after [W_hi | W_hi] on the [hi | lo] tile) reuses the tile in shared memory instead of loading it again
+  int xdup, fused;
   unsigned long long skip[9];                    // bit ch of skip[tap]: weight block (tap, chunk ch) is all zero -> no load, no MMA
   int has_kk, kk_mask[9], kk_first_tap, kk_first_kk;   // single-chunk layers: bit kk of kk_mask[tap] set <=> the K=16 step kk of
                                                   // tap's weight tile is all zero (space-to-depth block structure) -> no MMA
@@ -123,7 +132,7 @@ __device__ __forceinline__ void wm_stage(const uint32_t* v, int ncol, int fp16, 
 // kMode = 0: the plain 9-tap path with nothing extra on the MMA issue path (the big layers run at > 90% of the tensor
 // peak only while the issuing thread does no more than descriptor arithmetic); the tap-stacked mode and the zero-block /
 // K-step skip lists are separate instances.
-// kMode: 0 plain | 1 tap-stacked | 2 zero-block skip list | 3 K-step skip masks | 4 tap lanes (one instance each: see above)
+// kMode: 0 plain | 1 tap-stacked | 2 zero-block skip list | 3 K-step skip masks | 4 tap lanes | 5 stride 2 (one instance each: see above)
 template <int kMode>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
@@ -176,6 +185,9 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     ty0 = (r / p.tiles_x) * p.rows; tx0 = (r % p.tiles_x) * 8;
   };
 
+  // chunk ch multiplies the x tile chunk ch - 1 loaded (WmParams::xdup); a CTA's first chunk always loads
+  auto reuse_x = [&](int ch, int ch_lo) { return (kMode == 5) && p.xdup && ch != ch_lo && (p.fused ? (ch & 1) != 0 : (ch % 3) == 1); };
+
   if (warp == 0) {
     // ===================== TMA producer (whole warp converged; one elected lane issues) =====================
     if (p.w_resident && ptx::elect_one()) {
@@ -198,16 +210,21 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       const int it_idx = (vitem - (int)blockIdx.x) / (int)gridDim.x;
       for (int ch = ch_lo; ch < ch_hi; ++ch) {
         if (ch == ch_lo) wm_mark(trp, 0, it_idx, 0);
-        ptx::mbar_wait(x_empty(xb), xph ^ 1);
-        if (ch == ch_lo) wm_mark(trp, 0, it_idx, 1);
-        if (ptx::elect_one()) {
-          ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
-          const int xc = p.split ? (ch / p.split) * p.kc + ((ch % p.split) == p.split - 1 ? p.lo_off : 0) : ch * p.kc;
-          if (p.xsplit) ptx::tma_load_5d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, rx, tx0 - 1, ya, n);
-          else ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, xa, ya, n);
+        if (!reuse_x(ch, ch_lo)) {
+          ptx::mbar_wait(x_empty(xb), xph ^ 1);
+          if (ch == ch_lo) wm_mark(trp, 0, it_idx, 1);
+          if (ptx::elect_one()) {
+            ptx::mbar_expect_tx(x_full(xb), p.x_bytes_tx);
+            const int xc = ((kMode == 5) && p.fused) ? 0 : p.split ? (ch / p.split) * p.kc + ((ch % p.split) == p.split - 1 ? p.lo_off : 0) : ch * p.kc;
+            if ((kMode == 5)) {
+              ptx::tma_load_5d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, 1, tx0 - 1, 2 * ty0 - 1, n);
+              ptx::tma_load_5d(x_base + xb * p.x_bytes + p.x_sub, &tmX, x_full(xb), xc, 0, tx0 - 1, 2 * ty0 - 1, n);
+            } else if (p.xsplit) ptx::tma_load_5d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, rx, tx0 - 1, ya, n);
+            else ptx::tma_load_4d(x_base + xb * p.x_bytes, &tmX, x_full(xb), xc, xa, ya, n);
+          }
+          __syncwarp();
+          if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
         }
-        __syncwarp();
-        if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
         if (!p.w_resident) {
           for (int tap = 0; tap < (kMode == 1 ? 1 : kMode == 4 ? p.ntaps : 9); tap += p.tps) {
             if ((kMode == 2) && ((p.skip[tap] >> ch) & 1ull)) continue;
@@ -229,7 +246,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     if (p.fp16) idesc &= ~((7u << 7) | (7u << 10));          // A/B format 0 = F16
     const uint32_t row_bytes = p.kc * 2;
     const uint32_t ltype = (p.kc == 64) ? 2u : (p.kc == 32) ? 4u : 6u;
-    const uint32_t sbo_x = ((kMode == 1) ? 8u : 10u) * row_bytes;     // TS: all halo pixels in order; else 8 of every 10
+    const uint32_t sbo_x = ((kMode == 1) ? 8u : (kMode == 5) ? 18u : 10u) * row_bytes;   // TS: all halo pixels in order; else 8 of every 10
+                                                                                  // (stride 2: of every second 9-pair row)
     int xb = 0; uint32_t xph = 0; uint32_t s = 0, wph = 0;
     int acc = 0; uint32_t tph = 0;
     if (p.w_resident) ptx::mbar_wait(w_all, 0);
@@ -245,18 +263,24 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * ((kMode == 1) ? 256 : p.npx));
       bool first = true;                                   // the first MMA of an item overwrites the accumulator
       for (int ch = ch_lo; ch < ch_hi; ++ch) {
-        ptx::mbar_wait(x_full(xb), xph);
-        ptx::tc_fence_after();
+        const bool keep_x = (ch + 1 < ch_hi) && reuse_x(ch + 1, ch_lo);   // the next chunk multiplies this tile again
+        if (!reuse_x(ch, ch_lo)) {
+          ptx::mbar_wait(x_full(xb), xph);
+          ptx::tc_fence_after();
+        }
         if (ch == ch_lo) wm_mark(trm, 1, it_idx, 2);
         const uint32_t sx = x_base + xb * p.x_bytes;
-        const int nkk = min(p.kc, p.cin_span - (p.split ? ch / p.split : ch) * p.kc + 15) >> 4;     // K=16 steps holding real channels
+        const int nkk = ((kMode == 5) && p.fused) ? ((ch & 1) ? p.kc >> 5 : p.kc >> 4)       // [W_lo | 0]: the hi half of the K range only
+                                : min(p.kc, p.cin_span - (p.split ? ch / p.split : ch) * p.kc + 15) >> 4;   // K=16 steps holding real channels
         const uint64_t dx0 = ptx::make_kmajor_desc(sx, sbo_x, ltype);
         int ftap = 0;                                        // first tap actually issued for this chunk
         if ((kMode == 2)) while (ftap < 8 && ((p.skip[ftap] >> ch) & 1ull)) ++ftap;
         auto issue_tap = [&](uint32_t sw, int tap) {
           const int ky = (kMode == 4) ? (tap < 3 ? 0 : 2) : tap / 3, kx = tap - 3 * (tap / 3);   // kMode 4: slots 3..5 = ky 2, one lane
           const uint64_t dw = ptx::make_kmajor_desc(sw, 8 * row_bytes, ltype);
-          const uint64_t dx = dx0 + (uint64_t)(((uint32_t)(ky * p.kyr * 10 + kx) * row_bytes) >> 4);
+          const uint32_t xoff = (kMode == 5) ? (uint32_t)(ky * 9 + (kx ? 1 : 0)) * row_bytes + (kx == 1 ? p.x_sub : 0u)
+                                     : (uint32_t)(ky * p.kyr * 10 + kx) * row_bytes;
+          const uint64_t dx = dx0 + (uint64_t)(xoff >> 4);
           if ((kMode == 3)) {
             const int km = p.kk_mask[tap];
 #pragma unroll
@@ -274,7 +298,7 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           if (ptx::elect_one()) {
 #pragma unroll 1
             for (int tap = 0; tap < 9; ++tap) issue_tap(w_base + (tap * p.nchunk + ch) * p.w_bytes, tap);
-            ptx::umma_commit(x_empty(xb));
+            if (!keep_x) ptx::umma_commit(x_empty(xb));
             if (ch == ch_hi - 1) ptx::umma_commit(t_full(acc));
           }
           __syncwarp();
@@ -293,14 +317,14 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
             if (++s == p.w_stages) { s = 0; wph ^= 1; }
           }
           if (ptx::elect_one()) {
-            ptx::umma_commit(x_empty(xb));
+            if (!keep_x) ptx::umma_commit(x_empty(xb));
             if (ch == ch_hi - 1) ptx::umma_commit(t_full(acc));
           }
           __syncwarp();
         }
         if (ch == ch_hi - 1) wm_mark(trm, 1, it_idx, 3);
         if (!(kMode == 2) || !((p.skip[ftap] >> ch) & 1ull)) first = false;   // some tap of this chunk was issued
-        if (++xb == p.x_stages) { xb = 0; xph ^= 1; }
+        if (!keep_x && ++xb == p.x_stages) { xb = 0; xph ^= 1; }
       }
       if (++acc == 2) { acc = 0; tph ^= 1; }
     }
@@ -514,6 +538,8 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
           for (int r0 = 0; r0 < R; r0 += p.o_rs) {
             const uint32_t so = my_o + (uint32_t)wbuf * p.o_half;
             const uint32_t so_lo = my_o + (uint32_t)(wbuf ^ 1) * p.o_half;   // split output: the other buffer takes the lo plane
+            // (four buffers per warp, so that a split output's stores need not drain before the next step, were measured: no gain
+            // on the pyramid layers and the smaller weight ring cost conv4_1 24.8 -> 29.1 us)
             if (lane == 0) { if (p.out_lo_off) ptx::bulk_wait_read0(); else ptx::bulk_wait_read1(); }   // buffer(s) released
             __syncwarp();
             uint16_t* st = reinterpret_cast<uint16_t*>(smem_raw + (so - ptx::smem_addr(smem_raw))) + lane;

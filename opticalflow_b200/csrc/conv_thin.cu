@@ -82,11 +82,11 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
   // (patch pixel e / NCH, 16-byte chunk e % NCH).  The pixel's shared-memory offset, its offset from the tile origin and its
   // (row, column) are computed ONCE (table in shared memory), so that the per-tile staging loop is a table read, a bounds
   // test and one address add per copy.
-  uint4* tab = reinterpret_cast<uint4*>(thin_smem + p.off_tab);
+  uint2* tab = reinterpret_cast<uint2*>(thin_smem + p.off_tab);
   const int nel = p.ih * p.iw * NCH;
   for (int px = tid; px < p.ih * p.iw; px += 256) {
     const int r = px / p.iw, c = px - r * p.iw;
-    tab[px] = make_uint4((uint32_t)(px * p.pp), (uint32_t)(r * p.W + c), ((uint32_t)r << 16) | (uint32_t)c, 0u);
+    tab[px] = make_uint2((uint32_t)(r * p.W + c), ((uint32_t)r << 16) | (uint32_t)c);
   }
   __syncthreads();
   // tile walk without divisions: (n, ty, tx) advance by the decomposition of gridDim.x
@@ -109,10 +109,11 @@ __global__ void __launch_bounds__(256) conv_thin_kernel(const ThinConvParams p) 
     const uint32_t dst0 = patch_addr + buf * p.patch_bytes;
 #pragma unroll 2
     for (int e = tid; e < nel; e += 256) {
-      const uint4 t = tab[e / NCH];                                      // NCH is a power of two
+      const int px = e / NCH;                                            // NCH is a power of two
+      const uint2 t = tab[px];
       const int ch = e & (NCH - 1);
-      const bool ok = (unsigned)(iy0 + (int)(t.z >> 16)) < (unsigned)p.H && (unsigned)(ix0 + (int)(t.z & 0xffffu)) < (unsigned)p.W;
-      thin_cp16(dst0 + t.x + ch * 16, ok ? (const void*)(org + (int)t.y * sp + ch * 8) : (const void*)src, ok);
+      const bool ok = (unsigned)(iy0 + (int)(t.y >> 16)) < (unsigned)p.H && (unsigned)(ix0 + (int)(t.y & 0xffffu)) < (unsigned)p.W;
+      thin_cp16(dst0 + (uint32_t)(px * p.pp) + ch * 16, ok ? (const void*)(org + (int)t.x * sp + ch * 8) : (const void*)src, ok);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
@@ -260,7 +261,7 @@ static int launch_thin(ThinConvParams& p, cudaStream_t s) {
     p.patch_bytes = (p.ih * p.iw * p.pp + 127) & ~127;
     p.off_ostg = p.off_patch + 2 * p.patch_bytes;
     p.off_tab = p.off_ostg + 8 * 16 * ((SPLIT ? 2 : 1) * NT * 16 + 16);
-    smem = p.off_tab + p.ih * p.iw * 16;
+    smem = p.off_tab + p.ih * p.iw * 8;
     if (smem <= 113 * 1024 || (p.mp == 1 && smem <= 227 * 1024)) break;   // keep two CTAs per SM if the wide tile allows it
   }
   if (p.mp < 1) return (int)cudaErrorInvalidValue;
@@ -639,12 +640,13 @@ extern "C" int pwc_conv3x3_thin_fwd(const void* in, long in_pitch, int in_coff,
 // Split-precision form of the thin layers (conv_mode 'mixed': fp32-grade pyramid levels 1 and 2, PWCNet.py:52-56,184-187):
 // in / out are [hi | lo] plane pairs -- 2*cin / 2*cout 16-bit channels per pixel at in_coff / out_coff --, w_packed holds rows
 // [9][cout][W_hi(cin) | W_lo(cin)] (pwc_pack_conv_weight_bf16 with Cin = span = kc = 2*cin).  cin, cout in {16, 32}, stride 1.
-extern "C" int pwc_conv3x3_thin_split_fwd(const void* in, long in_pitch, int in_coff, int cin,
-                                          const void* w_packed, const float* bias, int cout,
-                                          void* out, long out_pitch, int out_coff,
-                                          int N, int H, int W, float slope, void* stream) {
+extern "C" int pwc_conv3x3_thin_split_strided_fwd(const void* in, long in_pitch, int in_coff, int cin,
+                                                  const void* w_packed, const float* bias, int cout,
+                                                  void* out, long out_pitch, int out_coff,
+                                                  int N, int H, int W, int stride, float slope, void* stream) {
   using namespace pwc;
-  if (N <= 0 || H <= 0 || W <= 0 || !(cin == 16 || cin == 32) || !(cout == 16 || cout == 32) || (in_pitch & 7) || (in_coff & 7) ||
+  if (N <= 0 || H <= 0 || W <= 0 || (stride != 1 && stride != 2) ||
+      !(cin == 16 || cin == 32) || !(cout == 16 || cout == 32) || (in_pitch & 7) || (in_coff & 7) ||
       (out_pitch & 7) || (out_coff & 7) || slope < 0.f || slope > 1.f || in_pitch < 2 * cin || out_pitch < 2 * cout ||
       ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(w_packed)) & 15))
     return (int)cudaErrorInvalidValue;
@@ -654,8 +656,9 @@ extern "C" int pwc_conv3x3_thin_split_fwd(const void* in, long in_pitch, int in_
   p.w = reinterpret_cast<const __nv_bfloat16*>(w_packed); p.bias = bias; p.cin = 2 * cin; p.cout = cout;
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.out_pitch = out_pitch; p.out_coff = out_coff;
   p.out2 = nullptr; p.out2_pitch = 0; p.out2_coff = 0; p.n_split = N;
-  p.N = N; p.H = H; p.W = W; p.stride = 1; p.slope = slope; p.Ho = H; p.Wo = W;
-  p.tiles_y = cdiv(H, 8); p.ih = 10;
+  p.N = N; p.H = H; p.W = W; p.stride = stride; p.slope = slope;
+  p.Ho = (H - 1) / stride + 1; p.Wo = (W - 1) / stride + 1;
+  p.tiles_y = cdiv(p.Ho, 8); p.ih = 7 * stride + 3;
   p.pp = 4 * cin + 16; p.wp = 4 * cin + 16;
   p.flow_out = nullptr; p.residual = nullptr; p.res_pitch = 0;
   cudaStream_t s = (cudaStream_t)stream;
@@ -665,4 +668,12 @@ extern "C" int pwc_conv3x3_thin_split_fwd(const void* in, long in_pitch, int in_
   PWC_THIN_SPLIT(2, 1); PWC_THIN_SPLIT(4, 1); PWC_THIN_SPLIT(2, 2); PWC_THIN_SPLIT(4, 2);
 #undef PWC_THIN_SPLIT
   return (int)cudaErrorInvalidValue;
+}
+
+extern "C" int pwc_conv3x3_thin_split_fwd(const void* in, long in_pitch, int in_coff, int cin,
+                                          const void* w_packed, const float* bias, int cout,
+                                          void* out, long out_pitch, int out_coff,
+                                          int N, int H, int W, float slope, void* stream) {
+  return pwc_conv3x3_thin_split_strided_fwd(in, in_pitch, in_coff, cin, w_packed, bias, cout, out, out_pitch, out_coff, N, H, W, 1,
+                                            slope, stream);
 }

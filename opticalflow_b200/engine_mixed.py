@@ -40,6 +40,7 @@ DEC_PRODUCTS = int(os.environ.get("PWC_MIXED_DEC_PRODUCTS", "2"))
 # three epilogue warps issue ~3500 instructions per 240-pixel tile at ~0.3 IPC each (96 fp32 TMEM values summed through shared
 # memory per 16-channel output pixel, then the hi/lo split), 16.6k cycles per tile against 2.6k of MMA issue -- off
 THIN_TC = os.environ.get("PWC_MIXED_THIN_TC", "0") != "0"
+THIN_S2 = os.environ.get("PWC_MIXED_THIN_S2", "1") != "0"
 KP_LO, KP_DUP = 4, 8                    # K padding: lo copies of up_flow|up_feat at +4 (533..536), second hi copies at +8
 
 
@@ -84,19 +85,23 @@ class PlanMixed(PlanBF16):
         self.ops.append(launch(L))
         return L
 
-    def _thin_split(self, key, C, src, dst, N, h, w):
-        """16 -> 16 / 32 -> 32 stride-1 pyramid layer on [hi | lo] tensors (pwc_conv3x3_thin_split_fwd)."""
+    def _thin_split(self, key, C, src, dst, N, h, w, cout=None, stride=1):
+        """16 -> 16 / 32 -> 32 stride-1 (or 16 -> 32 stride-2: conv2a) pyramid layer on [hi | lo] tensors
+        (pwc_conv3x3_thin_split_strided_fwd); h, w: input dims."""
         lib = self.lib
+        cout = C if cout is None else cout
 
         def wfn(sd):
             wt = sd[key + ".weight"]
             return torch.cat([wt, S.residual(wt, self.hdt)], 1).contiguous(), sd[key + ".bias"]
 
         def launch(L):
-            args = (_lib.ptr(src), src.shape[-1], 0, C, _lib.ptr(L.w), _lib.ptr(L.b), C, _lib.ptr(dst), dst.shape[-1], 0, N, h, w, 0.1)
-            return lambda st: _lib.check(lib.pwc_conv3x3_thin_split_fwd(*args, st), key)
-        L = self._plain(key, 2 * C, C, 9 * C * 2 * C, wfn, launch, 2.0 * N * h * w * C * C * 9)
-        L.span, L.kc, L.coutp, L.wrows = 2 * C, 2 * C, C, C
+            args = (_lib.ptr(src), src.shape[-1], 0, C, _lib.ptr(L.w), _lib.ptr(L.b), cout, _lib.ptr(dst), dst.shape[-1], 0, N, h, w,
+                    stride, 0.1)
+            return lambda st: _lib.check(lib.pwc_conv3x3_thin_split_strided_fwd(*args, st), key)
+        ho, wo = (h - 1) // stride + 1, (w - 1) // stride + 1
+        L = self._plain(key, 2 * C, cout, 9 * cout * 2 * C, wfn, launch, 2.0 * N * ho * wo * C * cout * 9)
+        L.span, L.kc, L.coutp, L.wrows = 2 * C, 2 * C, cout, cout
 
     def _copy(self, name, src, src_coff, dst, dst_coff, C, n_img, h, w):
         lib = self.lib
@@ -147,7 +152,12 @@ class PlanMixed(PlanBF16):
             names = (f"conv{l}a", f"conv{l}aa", f"conv{l}b") if l < 6 else ("conv6aa", "conv6a", "conv6b")
             h, w = self.hw[l]
             C, CP = PYR_CH[l], CPM[l]
-            if l > 1:
+            if l == 2 and THIN_S2:
+                # conv2a (16 -> 32, stride 2) on the mma.sync thin kernel: the tcgen05 per-tap kernel's stride-2 gather is bound by
+                # the TMA's ~6 cycles per 64-byte pixel row (88 us)
+                hin, win = self.hw[1]
+                self._thin_split(names[0] + ".0", PYR_CH[1], self.pa[1], self.pa[2], NP, hin, win, cout=C, stride=2)
+            elif l > 1:
                 hin, win = self.hw[l - 1]
                 self._tc(names[0] + ".0", PYR_CH[l - 1], C, self.pa[l - 1], 0, PYR_CH[l - 1], self.pa[l], 0, NP, hin, win, stride=2,
                          in_lo=CPM[l - 1], out_lo=CP, no_small=True)

@@ -281,7 +281,7 @@ def conv3x3_tc_split(x32, weight, bias, stride=1, slope=0.1, split_in=True, spli
     return res
 
 
-def conv3x3_thin_split(x32, weight, bias, slope=0.1, reps=1):
+def conv3x3_thin_split(x32, weight, bias, slope=0.1, reps=1, stride=1):
     """Split-precision thin layer (pwc_conv3x3_thin_split_fwd): x32 [N,H,W,cin] fp32, cin / cout in {16, 32}; returns hi + lo."""
     from . import split as S
     lib = _lib.load()
@@ -296,12 +296,13 @@ def conv3x3_thin_split(x32, weight, bias, slope=0.1, reps=1):
     wv = torch.cat([w32, S.residual(w32, dt)], 1).contiguous()
     wp = torch.zeros(9 * cout * 2 * cin, device=dev, dtype=dt)
     _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(wv), _lib.ptr(wp), None, cout, 2 * cin, 2 * cin, 2 * cin, cout, st), "pack")
-    out = torch.full((N, H, W, 2 * cout), 7.0, device=dev, dtype=dt)
+    out = torch.full((N, (H - 1) // stride + 1, (W - 1) // stride + 1, 2 * cout), 7.0, device=dev, dtype=dt)
     b32 = bias.detach().float().contiguous()
 
     def launch():
-        _lib.check(lib.pwc_conv3x3_thin_split_fwd(_lib.ptr(xin), 2 * cin, 0, cin, _lib.ptr(wp), _lib.ptr(b32), cout, _lib.ptr(out),
-                                                  2 * cout, 0, N, H, W, slope, st), "pwc_conv3x3_thin_split_fwd")
+        _lib.check(lib.pwc_conv3x3_thin_split_strided_fwd(_lib.ptr(xin), 2 * cin, 0, cin, _lib.ptr(wp), _lib.ptr(b32), cout,
+                                                          _lib.ptr(out), 2 * cout, 0, N, H, W, stride, slope, st),
+                   "pwc_conv3x3_thin_split_strided_fwd")
     launch()
     if reps > 1:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

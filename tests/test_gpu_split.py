@@ -61,14 +61,17 @@ def test_conv3x3_tc_split_half_configurations(case):
 @pytest.mark.parametrize("fmt", ["f16", "bf16"])
 @pytest.mark.parametrize("case", [(16, 16, 2, 40, 72), (32, 32, 2, 37, 70), (16, 16, 1, 224, 512), (32, 32, 1, 112, 256), (16, 32, 1, 20, 33),
                                   (32, 16, 1, 9, 130)])
-def test_conv3x3_thin_split_matches_fp32(case, fmt):
+@pytest.mark.parametrize("stride", [1, 2])
+def test_conv3x3_thin_split_matches_fp32(case, fmt, stride):
     from opticalflow_b200 import ops
     cin, cout, N, H, W = case
+    if stride == 2 and cin != 16:
+        pytest.skip("stride 2 exists for 16 input channels (conv2a): two 17 x 65 patches of wider pixels exceed shared memory")
     x, w, b = _case(cin, cout, N, H, W, 900 + cin + cout)
-    ref = F.leaky_relu(F.conv2d(x, w, b, padding=1), 0.1)
+    ref = F.leaky_relu(F.conv2d(x, w, b, stride=stride, padding=1), 0.1)
     d = torch.device("cuda:0")
     with ops.half_format(fmt):
-        out = ops.conv3x3_thin_split(x.permute(0, 2, 3, 1).contiguous().to(d), w.to(d), b.to(d))
+        out = ops.conv3x3_thin_split(x.permute(0, 2, 3, 1).contiguous().to(d), w.to(d), b.to(d), stride=stride)
     out = out.permute(0, 3, 1, 2).cpu()
     tol = TOL if fmt == "f16" else 3e-4
     assert (out - ref).abs().max().item() <= tol * ref.abs().max().item()
