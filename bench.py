@@ -402,8 +402,11 @@ def run_ours(args):
                 "kernel": "conv_tc_wm_kernel / conv_tc_halo_kernel / conv_tc_kernel (tcgen05 3x3 convolutions) + "
                           "conv_mma_small_kernel (level-6 layers)",
                 "launches_per_step": len(tc), "share_of_step": tc_t / all_t,
+                # frac is against the pool's measured cuBLAS bf16 figure (MEASURED_PEAKS.json, taken on another box at its
+                # power-capped clocks): a launch timed alone on a box holding higher clocks can exceed it, so the nominal dense
+                # bf16 peak (2250 TFLOP/s, 148 SMs x 8192 FLOP/cycle x 1.86 GHz) is quoted beside it
                 "top_launch": {"layer": top[0], "us": round(top[1] * 1e6, 1), "TFLOPs": round(top[2] / top[1] / 1e12, 1),
-                               "frac": top[2] / top[1] / 1e12 / peak},
+                               "frac": top[2] / top[1] / 1e12 / peak, "frac_of_nominal_2250": top[2] / top[1] / 1e12 / 2250.0},
                 "note": f"algorithmic conv FLOPs of the {len(tc)} tensor-core launches of one step / their summed CUDA-event "
                         f"durations (each launch captured 8x into a CUDA graph and timed alone); peak = bf16 burst ({peaks['source']}); whole-step figure "
                         f"{step_tflops:.1f} TFLOP/s incl. all other kernels"}
