@@ -104,9 +104,14 @@ class FlowPipeline:
                        static input), record(in_free[s]), graph replay of the other launches -> copy flow2 into out_dev[s] (after wait(out_free[s])) -> record(out_ready[s])
       copy-out stream: wait(out_ready[s]) -> D2H into out_host[s] -> record(out_done[s]), record(out_free[s])
     so the 22 MB/pair input upload of batch i+1 overlaps the forward of batch i.
+
+    inflight = 2 (default for the graph plans): batches alternate between TWO plans (own activation buffers and CUDA graph) on two
+    compute streams, so the forward of batch i+1 starts while batch i is still in its small pyramid-level 4-6 / decoder-level 4-6
+    layers, whose grids leave most SMs idle (a fifth of the step at ~10% of the tensor peak): +5-12% pairs/s on B200
+    (tools/two_plans.py).  A batch's latency grows accordingly; inflight = 1 restores one forward at a time.
     """
 
-    def __init__(self, model, B, H, W, device, depth=2, input="f32", swap_rb=True):
+    def __init__(self, model, B, H, W, device, depth=None, input="f32", swap_rb=True, inflight=None):
         """input='f32': host batches are the model's own input, [B,6,H,W] fp32 (H, W multiples of 64).
         input='u8' : host batches are the frames as the reference drivers hold them before frame_to_tensor /
         pad_to_multiple_of_64 (pwc_extract_flow_video.py:27-42, inference_kitti.py:53-63): uint8 [B,2,H,W,3] (frame 1,
@@ -117,7 +122,7 @@ class FlowPipeline:
             raise RuntimeError("FlowPipeline: CUDA device required -- this build has no CPU fallback")
         if input not in ("f32", "u8"):
             raise ValueError("FlowPipeline: input must be 'f32' or 'u8'")
-        self.model, self.B, self.device, self.depth = model, B, device, depth
+        self.model, self.B, self.device = model, B, device
         self.input, self.swap_rb, self.in_h, self.in_w = input, bool(swap_rb), H, W
         if input == "u8":
             from . import prepost
@@ -127,6 +132,15 @@ class FlowPipeline:
         with torch.cuda.device(device):
             self.plan = model._plan(B, H, W, device)
             self.plan.pack_weights(model)
+            if inflight is None:
+                inflight = 2 if hasattr(self.plan, "run_from") else 1
+            self.inflight = max(1, int(inflight))
+            # slots: the host hands batch i over once batch i - depth has left the device, so two forwards only overlap if more
+            # than two batches may be queued
+            self.depth = depth = max(2, int(depth)) if depth is not None else 2 * self.inflight
+            self.inflight = min(self.inflight, depth)
+            self.plans = [self.plan] + [model._plan(B, H, W, device, instance=k) for k in range(1, self.inflight)]
+            self.s_cmp = [torch.cuda.Stream(device) for _ in range(self.inflight)] if self.inflight > 1 else None
             self.s_in, self.s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
             self.x_dev = [torch.empty(B, 6, H, W, device=device) for _ in range(depth)]
             self.u8_dev = [torch.empty(B, 2, self.in_h, self.in_w, 3, device=device, dtype=torch.uint8) for _ in range(depth)] \
@@ -135,9 +149,11 @@ class FlowPipeline:
             self.o_host = [torch.empty(B, 2, H // 4, W // 4).pin_memory() for _ in range(depth)]
             ev = lambda: [torch.cuda.Event() for _ in range(depth)]  # noqa: E731
             self.in_ready, self.in_free, self.out_ready, self.out_free, self.out_done = ev(), ev(), ev(), ev(), ev()
-            self.plan.run(self.x_dev[0].zero_())          # capture the graph(s) outside the pipeline
-            if hasattr(self.plan, "run_from"):
-                self.plan.run_from(self.x_dev[0])
+            for pl in self.plans:                          # capture the graph(s) outside the pipeline
+                pl.pack_weights(model)
+                pl.run(self.x_dev[0].zero_())
+                if hasattr(pl, "run_from"):
+                    pl.run_from(self.x_dev[0])
             torch.cuda.synchronize(device)
         self.launches_per_batch = self.plan.launches
 
@@ -149,13 +165,19 @@ class FlowPipeline:
         uploaded(i, event): optional callback, called right after batch i's H2D copy has been enqueued; `event` (a
         torch.cuda.Event) completes when the copy has finished reading the host batch -- a loader that recycles its
         pinned buffers must wait for it (event.synchronize()) before overwriting batch i.  Returns the batch count."""
-        cs = torch.cuda.current_stream(self.device)
+        cur = torch.cuda.current_stream(self.device)
         pending = []                                     # (i, slot) whose D2H is in flight
         n = 0
         with torch.cuda.device(self.device):
-            self.plan.pack_weights(self.model)           # no-op unless the parameters changed since the last run
+            for pl in self.plans:
+                pl.pack_weights(self.model)              # no-op unless the parameters changed since the last run
+            if self.s_cmp is not None:
+                for st in self.s_cmp:
+                    st.wait_stream(cur)                  # what the caller enqueued so far (and the packing) comes first
             for i, xh in enumerate(host_batches):
                 s = i % self.depth
+                plan = self.plans[i % self.inflight]
+                cs = self.s_cmp[i % self.inflight] if self.s_cmp is not None else cur
                 slot = self.u8_dev[s] if self.input == "u8" else self.x_dev[s]
                 if xh.shape != slot.shape or xh.dtype != slot.dtype:
                     raise RuntimeError(f"FlowPipeline: batch {i} has shape {tuple(xh.shape)} / {xh.dtype}")
@@ -172,24 +194,25 @@ class FlowPipeline:
                     ev = torch.cuda.Event()
                     ev.record(self.s_in)
                     uploaded(i, ev)
-                cs.wait_event(self.in_ready[s])
-                if self.input == "u8":                   # /255 + swap + pad + cat into the fp32 slot; the u8 slot is free again
-                    from . import prepost
-                    prepost.frames_to_input(self.u8_dev[s][:, 0], self.u8_dev[s][:, 1], swap_rb=self.swap_rb, out=self.x_dev[s])
-                    self.in_free[s].record(cs)
-                    flow2 = self.plan.run_from(self.x_dev[s]) if hasattr(self.plan, "run_from") else self.plan.run(self.x_dev[s])
-                elif hasattr(self.plan, "run_from"):       # bf16 plan: conv1a reads the slot in place, the rest is one graph
-                    flow2 = self.plan.run_from(self.x_dev[s], release=self.in_free[s])
-                elif hasattr(self.plan, "x_static"):     # graph plan: release the slot right after the d2d copy
-                    self.plan.x_static.copy_(self.x_dev[s], non_blocking=True)
-                    self.in_free[s].record(cs)
-                    flow2 = self.plan.run()
-                else:
-                    flow2 = self.plan.run(self.x_dev[s])
-                    self.in_free[s].record(cs)
-                cs.wait_event(self.out_free[s])
-                self.o_dev[s].copy_(flow2, non_blocking=True)
-                self.out_ready[s].record(cs)
+                with torch.cuda.stream(cs):
+                    cs.wait_event(self.in_ready[s])
+                    if self.input == "u8":               # /255 + swap + pad + cat into the fp32 slot; the u8 slot is free again
+                        from . import prepost
+                        prepost.frames_to_input(self.u8_dev[s][:, 0], self.u8_dev[s][:, 1], swap_rb=self.swap_rb, out=self.x_dev[s])
+                        self.in_free[s].record(cs)
+                        flow2 = plan.run_from(self.x_dev[s]) if hasattr(plan, "run_from") else plan.run(self.x_dev[s])
+                    elif hasattr(plan, "run_from"):      # bf16 plan: conv1a reads the slot in place, the rest is one graph
+                        flow2 = plan.run_from(self.x_dev[s], release=self.in_free[s])
+                    elif hasattr(plan, "x_static"):      # graph plan: release the slot right after the d2d copy
+                        plan.x_static.copy_(self.x_dev[s], non_blocking=True)
+                        self.in_free[s].record(cs)
+                        flow2 = plan.run()
+                    else:
+                        flow2 = plan.run(self.x_dev[s])
+                        self.in_free[s].record(cs)
+                    cs.wait_event(self.out_free[s])
+                    self.o_dev[s].copy_(flow2, non_blocking=True)
+                    self.out_ready[s].record(cs)
                 with torch.cuda.stream(self.s_out):
                     self.s_out.wait_event(self.out_ready[s])
                     self.o_host[s].copy_(self.o_dev[s], non_blocking=True)
@@ -201,6 +224,9 @@ class FlowPipeline:
                 self.out_done[sj].synchronize()
                 if sink is not None:
                     sink(j, self.o_host[sj])
+            if self.s_cmp is not None:
+                for st in self.s_cmp:
+                    cur.wait_stream(st)                  # later work on the caller's stream follows the pipeline's
         return n
 
 

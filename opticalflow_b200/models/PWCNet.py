@@ -87,8 +87,10 @@ class PWCDCNet(nn.Module):
         self.verify_weights = False      # True: checksum the parameters every forward (catches edits through .data)
 
     # -- execution ---------------------------------------------------------------------------------
-    def _plan(self, B, H, W, device, video=False):
-        key = (B, H, W, str(device), self.conv_mode, bool(self.align_corners), bool(video))
+    def _plan(self, B, H, W, device, video=False, instance=0):
+        """instance > 0: another plan of the same shape with its own activation buffers and CUDA graph, for callers that keep
+        several forwards in flight on different streams (driver.FlowPipeline(inflight=2))."""
+        key = (B, H, W, str(device), self.conv_mode, bool(self.align_corners), bool(video), int(instance))
         plan = self._plans.get(key)
         if plan is None:
             plan = engine.make_plan(self, B, H, W, device, self.conv_mode, self.align_corners, video=video)

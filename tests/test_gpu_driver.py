@@ -96,12 +96,13 @@ def test_video_pipeline_matches_reference_steps(full_res, share):
         assert got[t].shape == ref.shape[1:]
         # the video plan's stride-2 pyramid layers read one tensor of B + 1 images, the pair plan's two tensors of B: the small
         # levels take different tcgen05 kernels (chunk-major against tap-major fp32 accumulation, tools/dbg_s2_plan.py), so a
-        # bf16 rounding of a level-5/6 feature can flip (1 ulp) and move the x20 flow by tenths of a pixel.  The bar is half of
-        # the bf16 mode's own mean-EPE bar against the fp32 oracle (0.60 px); a plumbing error is tens of pixels
+        # bf16 rounding of a level-5/6 feature can flip (1 ulp) and move the x20 flow by tenths of a pixel on a 30-pixel flow
+        # (pairs 4 and 5 of this clip: mean 0.2 / 0.13 px, the others bit-identical; tools/dbg_s2_video.py).  The bar is 1.5% of
+        # the flow range in the mean (full_res scales flows and differences alike); a plumbing error is tens of percent
         d = got[t] - ref[0]
         epe = d.pow(2).sum(0).sqrt().mean().item()
         print("pair", t, "max abs", d.abs().max().item(), "mean EPE", epe, "flow max", ref.abs().max().item())
-        assert epe <= 0.30, f"pair {t}"
+        assert epe <= 0.015 * max(1.0, ref.abs().max().item()), f"pair {t}"
 
 
 def test_run_from_reads_the_callers_tensor_in_place():
