@@ -259,15 +259,17 @@ class VideoFlowPipeline:
     frame size) and the x`mult` flow scale (ONE kernel, prepost.postprocess_flow).  Per pair 3 bytes/pixel go up instead
     of the 24 bytes/pixel of the fp32 [1,6,H,W] tensor the reference uploads.  Three streams as in FlowPipeline."""
 
-    def __init__(self, model, B, H, W, device, swap_rb=True, mult=20.0, full_res=False, depth=2, share_pyramid=None):
-        """share_pyramid (default: on for the 16-bit conv modes): frame t is image 2 of pair t-1 and image 1 of pair t, so the plan
+    def __init__(self, model, B, H, W, device, swap_rb=True, mult=20.0, full_res=False, depth=None, share_pyramid=None, inflight=None):
+        """inflight (default 2 for the graph plans; depth defaults to 2 * inflight slots): batches alternate between that many plans on
+        their own compute streams, as in FlowPipeline.
+        share_pyramid (default: on for the 16-bit conv modes): frame t is image 2 of pair t-1 and image 1 of pair t, so the plan
         runs the feature pyramid once per frame (B+1 images per batch instead of 2B) and the cost volumes read frame t+1's
         features in place (engine_bf16.PlanBF16(video=True))."""
         from . import prepost
         if device.type != "cuda":
             raise RuntimeError("VideoFlowPipeline: CUDA device required -- this build has no CPU fallback")
         self.pp = prepost
-        self.model, self.B, self.H, self.W, self.device, self.depth = model, B, H, W, device, depth
+        self.model, self.B, self.H, self.W, self.device = model, B, H, W, device
         self.swap_rb, self.mult, self.full_res = swap_rb, float(mult), full_res
         self.ph, self.pw = prepost.pad_amounts(H, W)
         Hp, Wp = H + self.ph, W + self.pw
@@ -276,26 +278,39 @@ class VideoFlowPipeline:
         self.oh, self.ow = (H, W) if full_res else (Hp // 4 - self.ph, Wp // 4 - self.pw)
         with torch.cuda.device(device):
             self.share = (getattr(model, "conv_mode", "") != "fp32") if share_pyramid is None else bool(share_pyramid)
-            self.plan = model._plan(B, Hp, Wp, device, video=True) if self.share else model._plan(B, Hp, Wp, device)
+            mk = lambda k: model._plan(B, Hp, Wp, device, video=True, instance=k) if self.share \
+                else model._plan(B, Hp, Wp, device, instance=k)      # noqa: E731
+            self.plan = mk(0)
             self.plan.pack_weights(model)
+            if inflight is None:
+                inflight = 2 if hasattr(self.plan, "x_static") and hasattr(self.plan, "run_from") else 1
+            self.inflight = max(1, int(inflight))
+            self.depth = depth = max(2, int(depth)) if depth is not None else 2 * self.inflight
+            self.inflight = min(self.inflight, depth)
+            self.plans = [self.plan] + [mk(k) for k in range(1, self.inflight)]
+            self.s_cmp = [torch.cuda.Stream(device) for _ in range(self.inflight)] if self.inflight > 1 else None
             self.s_in, self.s_out = torch.cuda.Stream(device), torch.cuda.Stream(device)
             self.f_dev = [torch.empty(B + 1, H, W, 3, device=device, dtype=torch.uint8) for _ in range(depth)]
-            self.x_dev = self.plan.x_static if hasattr(self.plan, "x_static") else torch.empty(B, 6, Hp, Wp, device=device)
+            self.x_devs = [pl.x_static if hasattr(pl, "x_static") else torch.empty(B, 6, Hp, Wp, device=device) for pl in self.plans]
+            self.x_dev = self.x_devs[0]
             self.o_dev = [torch.empty(B, 2, self.oh, self.ow, device=device) for _ in range(depth)]
             self.o_host = [torch.empty(B, 2, self.oh, self.ow).pin_memory() for _ in range(depth)]
             ev = lambda: [torch.cuda.Event() for _ in range(depth)]  # noqa: E731
             self.in_ready, self.in_free, self.out_ready, self.out_free, self.out_done = ev(), ev(), ev(), ev(), ev()
-            self.plan.run(self.x_dev.zero_())
+            for pl, xd in zip(self.plans, self.x_devs):
+                pl.pack_weights(model)
+                pl.run(xd.zero_())
             torch.cuda.synchronize(device)
         self.launches_per_batch = self.plan.launches + 2
 
-    def _compute(self, s):
+    def _compute(self, s, k=0):
         f = self.f_dev[s]
+        plan, x_dev = self.plans[k], self.x_devs[k]
         if self.share:
-            self.pp.frames_to_stack(f, swap_rb=self.swap_rb, out=self.x_dev)
+            self.pp.frames_to_stack(f, swap_rb=self.swap_rb, out=x_dev)
         else:
-            self.pp.frames_to_input(f[:-1], f[1:], swap_rb=self.swap_rb, out=self.x_dev)
-        flow2 = self.plan.run() if hasattr(self.plan, "x_static") else self.plan.run(self.x_dev)
+            self.pp.frames_to_input(f[:-1], f[1:], swap_rb=self.swap_rb, out=x_dev)
+        flow2 = plan.run() if hasattr(plan, "x_static") else plan.run(x_dev)
         lib, _lib = self.pp._lib.load(), self.pp._lib
         h, w = self.Hp // 4, self.Wp // 4
         e = lib.pwc_flow_postprocess_fwd(_lib.ptr(flow2), self.B, h, w, h - self.ph, w - self.pw, _lib.ptr(self.o_dev[s]),
@@ -312,7 +327,7 @@ class VideoFlowPipeline:
             raise RuntimeError(f"VideoFlowPipeline: uint8 [N,{self.H},{self.W},3] frames expected, got {tuple(frames.shape)}")
         n_pairs = frames.shape[0] - 1
         todo = batches(0, n_pairs, self.B)
-        cs = torch.cuda.current_stream(self.device)
+        cur = torch.cuda.current_stream(self.device)
         pending = []
 
         def deliver(j, sj):
@@ -321,9 +336,15 @@ class VideoFlowPipeline:
                 sink(todo[j][0], todo[j][1], self.o_host[sj][:todo[j][1]])
 
         with torch.cuda.device(self.device):
-            self.plan.pack_weights(self.model)           # no-op unless the parameters changed since the last run
+            for pl in self.plans:
+                pl.pack_weights(self.model)              # no-op unless the parameters changed since the last run
+            if self.s_cmp is not None:
+                for st in self.s_cmp:
+                    st.wait_stream(cur)
             for i, (t0, cnt) in enumerate(todo):
                 s = i % self.depth
+                k = i % self.inflight
+                cs = self.s_cmp[k] if self.s_cmp is not None else cur
                 if len(pending) == self.depth:
                     deliver(*pending.pop(0))
                 with torch.cuda.stream(self.s_in):
@@ -332,11 +353,12 @@ class VideoFlowPipeline:
                     if cnt < self.B:                      # ragged tail: repeat the last frame (its flows are dropped)
                         self.f_dev[s][cnt + 1:] = self.f_dev[s][cnt:cnt + 1]
                     self.in_ready[s].record(self.s_in)
-                cs.wait_event(self.in_ready[s])
-                cs.wait_event(self.out_free[s])
-                self._compute(s)
-                self.in_free[s].record(cs)
-                self.out_ready[s].record(cs)
+                with torch.cuda.stream(cs):
+                    cs.wait_event(self.in_ready[s])
+                    cs.wait_event(self.out_free[s])
+                    self._compute(s, k)
+                    self.in_free[s].record(cs)
+                    self.out_ready[s].record(cs)
                 with torch.cuda.stream(self.s_out):
                     self.s_out.wait_event(self.out_ready[s])
                     self.o_host[s].copy_(self.o_dev[s], non_blocking=True)
@@ -345,6 +367,9 @@ class VideoFlowPipeline:
                 pending.append((i, s))
             for j, sj in pending:
                 deliver(j, sj)
+            if self.s_cmp is not None:
+                for st in self.s_cmp:
+                    cur.wait_stream(st)
         return n_pairs
 
 
