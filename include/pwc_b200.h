@@ -183,6 +183,14 @@ int pwc_tc_conv_set_out_groups(pwc_tc_conv* handle, int g, long group_pitch);
 void pwc_tc_conv_destroy(pwc_tc_conv* handle);
 /* kernels ONE pwc_tc_conv_launch of the handle enqueues: 1, or 2 for small layers that run as deterministic two-pass split-K
  * (conv kernel storing per-CTA fp32 partial tiles to handle-owned scratch + a reduce kernel); for launch accounting. */
+/* Two layers that read the same input in one pass.  A three-lane tap-lane layer (Cout <= 32, out_f32 | 32) leaves MMA rows 96..127
+ * idle: pwc_tc_conv_set_head_rows makes them `nhead` (<= 10) output channels of another layer -- packed weight rows 96 + ky*nhead + h =
+ * kernel row ky of channel h -- whose raw sums (no bias, no activation) are stored as fp32 [N*H*W][nhead] to head_out;
+ * pwc_tc_conv_set_partial makes a tap-stacked layer (out_f32 | 16) add such a tensor to its outputs before the activation.  Used for
+ * predict_flow2 and predict_flow3 + upfeat3 (PWCNet.py:264-266, 252-255): their 533 shared input channels ride along with conv2_4 /
+ * conv3_4, the head itself reads the remaining 32.  No counterpart in the reference (it runs every layer as its own cuDNN call). */
+int pwc_tc_conv_set_head_rows(pwc_tc_conv* h, float* head_out, int nhead);
+int pwc_tc_conv_set_partial(pwc_tc_conv* h, const float* partial, int pitch);
 int pwc_tc_conv_num_launches(const pwc_tc_conv* handle);
 /* Split-K launch of a created handle that ALLOCATES NOTHING.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,

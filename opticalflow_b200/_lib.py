@@ -44,6 +44,8 @@ SIGNATURES = {
     "pwc_tc_conv_set_out_groups": (_i, [_vp, _i, _l]),
     "pwc_tc_conv_destroy": (None, [_vp]),
     "pwc_tc_conv_num_launches": (_i, [_vp]),
+    "pwc_tc_conv_set_head_rows": (_i, [_vp, _vp, _i]),
+    "pwc_tc_conv_set_partial": (_i, [_vp, _vp, _i]),
     "pwc_set_half_format": (_i, [_i]),
     "pwc_get_half_format": (_i, []),
     "pwc_debug_halo_trace": (_i, [_vp, _i]),

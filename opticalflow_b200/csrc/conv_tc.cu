@@ -466,6 +466,7 @@ static int create_wm(pwc_tc_conv** handle, const void* in, long in_pitch, int in
   p.up_lo_off = g_split.up_lo_off; p.up_dup_off = g_split.up_dup_off;
   int vmul = p.split ? p.split : 1;                 // virtual chunks per logical chunk (see WmParams::split)
   p.s2 = s2; p.x_sub = 0;
+  p.nhead = 0; p.head_out = nullptr; p.partial = nullptr; p.partial_pitch = 0;
   // adjacent [hi | lo] planes that fit one swizzle row (stride-2 pyramid layers of 16 / 32 channels): one chunk of both planes,
   // weights [W_hi | W_hi] then [W_lo | 0] (the layout of TcConvParams::fused)
   p.fused = (s2 && p.split == 3 && p.lo_off == cin_span && cin_span == kc && kc <= 32 && env_int("PWC_TC_FUSED_SPLIT", 1)) ? 1 : 0;
@@ -919,6 +920,25 @@ extern "C" int pwc_tc_conv_launch(const pwc_tc_conv* h, void* stream) {
 extern "C" void pwc_tc_conv_destroy(pwc_tc_conv* h) { delete h; }
 
 // kernels one pwc_tc_conv_launch of this handle enqueues (2 = deterministic two-pass split-K: conv kernel + reduce kernel)
+// Head rows of a three-lane tap-lane layer (WmParams::nhead): weight rows 96 + ky * nhead + h of the packed [128, Cin, 3, 3] tensor
+// are kernel row ky of `nhead` extra output channels; their raw sums go to head_out [N*H*W][nhead] fp32.
+extern "C" int pwc_tc_conv_set_head_rows(pwc_tc_conv* h, float* head_out, int nhead) {
+  if (!h || h->halo != 2 || h->wp.tl != 3 || h->wp.cg != 1 || !head_out || nhead < 1 || 3 * nhead > 32) return (int)cudaErrorInvalidValue;
+  if (!h->wp.nhead) {                               // 48 pixels x 32 lanes of fp32 behind the barriers (see the kernel's head warp)
+    if (h->smem_bytes + 6144 + 32 > 227u * 1024u || h->wp.rows % 6) return (int)cudaErrorInvalidValue;
+    h->smem_bytes += 6144 + 32;
+  }
+  h->wp.nhead = nhead; h->wp.head_out = head_out;
+  return 0;
+}
+
+// Tap-stacked layer (out_f32 | 16): partial [N*H*W][pitch] fp32 is added to every output channel before the activation.
+extern "C" int pwc_tc_conv_set_partial(pwc_tc_conv* h, const float* partial, int pitch) {
+  if (!h || h->halo != 2 || !h->wp.ts || !partial || pitch < h->wp.cout) return (int)cudaErrorInvalidValue;
+  h->wp.partial = partial; h->wp.partial_pitch = pitch;
+  return 0;
+}
+
 extern "C" int pwc_tc_conv_num_launches(const pwc_tc_conv* h) { return !h ? 0 : (h->halo == 2 && h->wp.ks2pass) ? 2 : 1; }
 
 extern "C" int pwc_tc_conv_create_split(pwc_tc_conv** handle,

@@ -48,6 +48,14 @@ struct WmParams {
   // accumulator row r + l holds its part of output row r, and the epilogue warps of a channel group add the lanes up through
   // the fp32 tile S (each warp takes another pixel block per phase, the last phase finishes the block).
   int tl, tl_bc;                                  // tl_bc: channels per output store box (16 for Cout <= 16, else 32)
+  // head rows (tl == 3 only): the fourth lane quarter of the 128 MMA rows, idle otherwise, holds nhead <= 10 extra output channels
+  // of ANOTHER layer that reads the same input -- row 96 + ky * nhead + h = that layer's weights of kernel row ky -- and the fourth
+  // epilogue warp adds the three ky rows up (row offset undone as for the lanes) and stores them RAW (no bias, no activation) as
+  // fp32 [pixel][nhead] to head_out: predict_flow / upfeat over the 533 concat channels conv{2,3}_4 reads anyway (their own pass
+  // over the concat buffer is bound by its halo-tile traffic: 71 us for 2 output channels).  The consumer (a tap-stacked head over
+  // the remaining 32 channels) adds `partial` before its activation.
+  int nhead; float* head_out;
+  const float* partial; int partial_pitch;
   // stride 2 (s2): H, W are the OUTPUT dims; the input is read through a pair view (C, col parity, W_in/2, H_in, N): one stage
   // = two dense sub-tiles of (2*rows + 1) input rows x 9 column pairs, x_sub bytes apart -- [0] the odd columns, [1] the even
   // ones -- so tap (ky, kx) is again a shifted start address: row ky (SBO = 2 tile rows = 18 pixel rows), pair (kx ? 1 : 0), sub-tile
@@ -387,8 +395,9 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
 #pragma unroll
           for (int tap = 0; tap < 9; ++tap)
             a += sp[(size_t)tap * p.cout * p.s_stride + (tap / 3) * 10 + (tap % 3)];
-          float val = lrelu(a, p.slope);
           const long pix = ((long)n * p.H + oy) * p.W + ox;
+          if (p.partial) a += __ldg(p.partial + pix * p.partial_pitch + co2);   // the other input channels' share (WmParams::nhead)
+          float val = lrelu(a, p.slope);
           if ((p.out_f32 & 3) == 2 && co2 >= 2) {
             const int k = co2 - 2, j = k & 1, b = (k >> 1) & 1, aa = k >> 2;
             const long up = (((long)n * 2 * p.H + 2 * oy + aa) * (2 * p.W) + 2 * ox + b) * p.out2_pitch + p.out2_coff + j;
@@ -476,6 +485,39 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
             named_bar(3 + cgi, 32 * G);                      // the block's partial sums are visible to the next phase's warp
           }
         } else {
+          if (p.nhead > 0 && l == G) {
+            // ---- head rows: TMEM lane 96 + ky * nhead + h; output row r of kernel row ky sits at accumulator row r + ky.
+            //      Phase 1: every lane drops its row's value of the step's 48 pixels into hs[pixel][lane]; phase 2: the 48 * nhead
+            //      (pixel, channel) sums of three kernel rows are dealt over ALL lanes (two shuffles per value on nhead live lanes
+            //      made this warp the slowest of the tile: conv2_4 91 -> 145 us) and stored as contiguous fp32 runs ----
+            const int NH = p.nhead, kyt = lane / NH;
+            float* hs = reinterpret_cast<float*>(smem_raw + (((tmem_slot + 16u + 15u) & ~15u) - ptx::smem_addr(smem_raw)));
+            for (int r0 = 0; r0 < p.rows; r0 += 6) {         // six tile rows per step (rows % 6 == 0): ONE wait for the 64 columns
+              uint32_t v[4][16];                             // = accumulator rows r0 .. r0 + 7 that the three kernel rows need
+#pragma unroll
+              for (int q = 0; q < 4; ++q) ptx::tmem_ld16(taddr + r0 * 8 + q * 16, v[q]);
+              ptx::tmem_ld_wait();
+              const uint32_t* vf = &v[0][0];
+              if (kyt == 0) {
+#pragma unroll
+                for (int i = 0; i < 48; ++i) hs[i * 32 + lane] = __uint_as_float(vf[i]);
+              } else if (kyt == 1) {
+#pragma unroll
+                for (int i = 0; i < 48; ++i) hs[i * 32 + lane] = __uint_as_float(vf[i + 8]);
+              } else if (kyt == 2) {
+#pragma unroll
+                for (int i = 0; i < 48; ++i) hs[i * 32 + lane] = __uint_as_float(vf[i + 16]);
+              }
+              __syncwarp();
+              for (int idx = lane; idx < 48 * NH; idx += 32) {
+                const int i = idx / NH, hh = idx - i * NH;
+                const float tot = hs[i * 32 + hh] + hs[i * 32 + NH + hh] + hs[i * 32 + 2 * NH + hh];
+                const int oy = ty0 + r0 + (i >> 3), ox = tx0 + (i & 7);
+                if (oy < p.H && ox < p.W) p.head_out[(((long)n * p.H + oy) * p.W + ox) * NH + hh] = tot;
+              }
+              __syncwarp();
+            }
+          }
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(t_empty(acc));

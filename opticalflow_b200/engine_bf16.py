@@ -64,11 +64,13 @@ def _stacked(wfn_or_key):
     return make
 
 
-def _lanes(wfn_or_key, cout):
+def _lanes(wfn_or_key, cout, head=None):
     """Tap-lane weight tensor for layers with Cout <= 64 (include/pwc_b200.h, out_f32 | 32; WmParams::tl): a [128, Cin, 3, 3]
     tensor whose packer tap slot t = 3*a + kx holds, for Cout <= 32 (three lanes of 32 rows), row 32*l + co = W[co, :, ky=l, kx] in
     slots a = 0; for Cout <= 64 (two lanes of 64 rows), rows co / 64 + co = W[co, :, ky = 0 / 1, kx] in slots a = 0 and
-    row co = W[co, :, ky=2, kx] in slots a = 1.  Unused slots / rows stay zero and are never loaded."""
+    row co = W[co, :, ky=2, kx] in slots a = 1.  Unused slots / rows stay zero and are never loaded.
+    head = (wfn, nhead) (Cout <= 32 only): rows 96 + ky * nhead + h = kernel row ky of the nhead output channels of another layer
+    over the same input channels (pwc_tc_conv_set_head_rows)."""
     def make(sd):
         w, b = wfn_or_key(sd) if callable(wfn_or_key) else (sd[wfn_or_key + ".weight"], sd[wfn_or_key + ".bias"])
         cin = w.shape[1]
@@ -76,6 +78,11 @@ def _lanes(wfn_or_key, cout):
         if cout <= 32:
             for l in range(3):
                 wl[32 * l:32 * l + cout, :, 0, :] = w[:, :, l, :]
+            if head is not None:
+                wh, nh = head[0](sd)[0], head[1]
+                assert wh.shape[0] == nh and wh.shape[1] == cin and 3 * nh <= 32, (tuple(wh.shape), nh, cin)
+                for ky in range(3):
+                    wl[96 + ky * nh:96 + (ky + 1) * nh, :, 0, :] = wh[:, :, ky, :]
         else:
             wl[0:cout, :, 0, :] = w[:, :, 0, :]
             wl[64:64 + cout, :, 0, :] = w[:, :, 1, :]
@@ -214,7 +221,7 @@ class PlanBF16:
     def _tc(self, key, cin, cout, src, src_coff, span, dst, dst_coff, N, hin, win, stride=1, dil=1, slope=0.1,
             cmap=None, src2=None, src2_coff=0, dst2=None, dst2_coff=0, n_split=0, out_f32=False, residual=None, wfn=None,
             flops=None, ts=False, groups=None, kkskip=False, in_lo=0, out_lo=0, up_lo=0, up_dup=0, kpad=None, no_small=False,
-            tl=False):
+            tl=False, head=None, partial=None):
         """in_lo / out_lo: channel offset of the lo plane of a split-precision input / output (0 = single precision);
         up_lo / up_dup: lo / second-hi offsets of the fused upfeat outputs; kpad = (idx, lo_pos, dup_pos): the torch input
         channels idx are also read from their lo copies / second hi copies at those slice positions (split.kpad_weights)."""
@@ -232,7 +239,14 @@ class PlanBF16:
         ts = bool(ts and TS_MODE and 9 * cout <= 128 and stride == 1 and dil == 1 and out_f32)
         tl = bool(tl and TL_MODE and cout <= 64 and stride == 1 and dil == 1 and not out_f32 and not ts and groups is None
                   and dst2 is None and src2 is None)
-        L.wfn = _stacked(wfn if wfn is not None else key) if ts else (_lanes(wfn if wfn is not None else key, cout) if tl else wfn)
+        # head = (weight fn, nhead, fp32 buffer [N,H,W,nhead]): extra output channels in the idle lane quarter of a three-lane layer;
+        # partial = such a buffer, added by a tap-stacked layer before its activation (include/pwc_b200.h)
+        if head is not None and not (tl and cout <= 32):
+            raise RuntimeError(f"{key}: head rows need the three-lane tap-lane form")
+        if partial is not None and not ts:
+            raise RuntimeError(f"{key}: a partial input needs the tap-stacked form")
+        L.wfn = _stacked(wfn if wfn is not None else key) if ts else \
+            (_lanes(wfn if wfn is not None else key, cout, head=None if head is None else head[:2]) if tl else wfn)
         L.key, L.cin, L.cout, L.span, L.cmap = key, cin, cout, span, cmap
         L.coutp = 128 if (ts or tl) else _roundup(cout, 16)
         L.kc = pick_kc(span, stride, dil, src2 is not None, W=win, coutp=L.coutp, out_f32=bool(out_f32) or dst2 is not None)
@@ -258,6 +272,10 @@ class PlanBF16:
         else:
             e = self.lib.pwc_tc_conv_create(*args)
         _lib.check(e, f"pwc_tc_conv_create {key}")
+        if head is not None:
+            _lib.check(self.lib.pwc_tc_conv_set_head_rows(h, _lib.ptr(head[2]), head[1]), f"set_head_rows {key}")
+        if partial is not None:
+            _lib.check(self.lib.pwc_tc_conv_set_partial(h, _lib.ptr(partial), partial.shape[-1]), f"set_partial {key}")
         L.groups = groups
         if groups is not None and groups[1] != L.coutp // groups[0]:
             _lib.check(self.lib.pwc_tc_conv_set_out_groups(h, groups[0], groups[1]), f"set_out_groups {key}")

@@ -41,6 +41,11 @@ DEC_PRODUCTS = int(os.environ.get("PWC_MIXED_DEC_PRODUCTS", "2"))
 # memory per 16-channel output pixel, then the hi/lo split), 16.6k cycles per tile against 2.6k of MMA issue -- off
 THIN_TC = os.environ.get("PWC_MIXED_THIN_TC", "0") != "0"
 THIN_S2 = os.environ.get("PWC_MIXED_THIN_S2", "1") != "0"
+# the flow head's sums over the 533 concat channels conv{l}_4 reads ride along in that layer's idle MMA rows.  Level 2 only by default
+# (conv2_4 90 -> 94 us, predict_flow2 71 -> 22 us); at level 3 the 10-channel flow + upfeat head costs conv3_4 9 us and saves pfup3 8
+# (that head is bound by its scattered 2-byte upfeat stores, not by its input): PWC_MIXED_HEAD_ROWS_LEVELS=2,3 turns it on there too
+HEAD_ROWS = os.environ.get("PWC_MIXED_HEAD_ROWS", "1") != "0"
+HEAD_ROWS_LEVELS = tuple(int(v) for v in os.environ.get("PWC_MIXED_HEAD_ROWS_LEVELS", "2").split(",") if v)
 KP_LO, KP_DUP = 4, 8                    # K padding: lo copies of up_flow|up_feat at +4 (533..536), second hi copies at +8
 
 
@@ -178,6 +183,7 @@ class PlanMixed(PlanBF16):
                         self._tc(f"{key}#{part}", C, r1 - r0, src, 0, C, dst, r0, NP, h, w, in_lo=CP, out_lo=CP, wfn=sl,
                                  flops=fl * (r1 - r0) / C, no_small=True)
         # ---- decoders
+        self.head_part = {}
         for l in (6, 5, 4, 3, 2):
             h, w = self.hw[l]
             cat, wd = self.cat[l], concat_width(l)
@@ -203,8 +209,19 @@ class PlanMixed(PlanBF16):
                 kpf = (lambda f: (lambda sd: f(sd, self.hdt)))(kp)
                 g = 128 // cout
                 if TL_MODE and cout <= 64 and l <= TL_MAXLVL:
+                    head = None
+                    if k == 4 and HEAD_ROWS and l in HEAD_ROWS_LEVELS and DEC_START[4] == 32:
+                        # the level's head (predict_flow2 | predict_flow + upfeat) over this layer's 533 input channels
+                        nh = 2 if l == 2 else 10
+                        hb = f"predict_flow{l}" if l == 2 else _pfup_weights(l)
+                        hsuf = (lambda b_: (lambda sd: (lambda wb: (wb[0][:, 32:].contiguous(), wb[1]))(
+                            b_(sd) if callable(b_) else (sd[b_ + ".weight"], sd[b_ + ".bias"]))))(hb)
+                        hk, hcm = _kpad(hsuf, l, DEC_START[4])
+                        assert hcm == cme
+                        self.head_part[l] = torch.zeros(B, h, w, nh, device=self.device, dtype=torch.float32)
+                        head = ((lambda f: (lambda sd: f(sd, self.hdt)))(hk), nh, self.head_part[l])
                     self._tc(key, len(cme), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w, cmap=cme, wfn=kpf,
-                             flops=2.0 * B * h * w * cout * len(cm) * 9, tl=True)
+                             flops=2.0 * B * h * w * cout * len(cm) * 9, tl=True, head=head)
                     continue
                 if S2D_DEC and cout <= S2D_DEC_MAXCOUT and l <= S2D_DEC_MAXLVL and w % g == 0:
                     v = cat[:B].view(B, h, w // g, g * wd)
@@ -227,12 +244,21 @@ class PlanMixed(PlanBF16):
                 elif l == 6:
                     self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
                              dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True, up_lo=up_lo, up_dup=up_dup)
+                elif l in self.head_part:
+                    first32 = (lambda f: (lambda sd: (lambda wb: (wb[0][:, :32].contiguous(), wb[1]))(f(sd))))(_pfup_weights(l))
+                    self._tc(f"pfup{l}", 32, 10, cat, 0, 32, self.flow[l], 0, B, h, w, slope=1.0, out_f32=2,
+                             dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=first32, ts=True, up_lo=up_lo, up_dup=up_dup,
+                             flops=2.0 * B * h * w * 10 * len(cm) * 9, partial=self.head_part[l])
                 else:
                     kp, cme = _kpad(_pfup_weights(l), l, 0)
                     self._tc(f"pfup{l}", len(cme), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cme, out_f32=2,
                              dst2=self.cat[tgt], dst2_coff=UPFEAT_OFF, wfn=(lambda f: (lambda sd: f(sd, self.hdt)))(kp), ts=True,
                              up_lo=up_lo, up_dup=up_dup, flops=2.0 * B * h * w * 10 * len(cm) * 9)
                 self._deconv_split(f"deconv{l}", self.flow[l], self.cat[tgt], UPFLOW_OFF, h, w, up_lo, up_dup, self.upflow[tgt])
+            elif l in self.head_part:
+                first32 = (lambda k_: (lambda sd: (sd[k_ + ".weight"][:, :32].contiguous(), sd[k_ + ".bias"])))(f"predict_flow{l}")
+                self._tc(f"predict_flow{l}", 32, 2, cat, 0, 32, self.flow[l], 0, B, h, w, slope=1.0, out_f32=True, ts=True,
+                         wfn=first32, flops=2.0 * B * h * w * 2 * len(cm) * 9, partial=self.head_part[l])
             else:
                 kp, cme = _kpad(f"predict_flow{l}", l, 0)
                 self._tc(f"predict_flow{l}", len(cme), 2, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cme, out_f32=True,

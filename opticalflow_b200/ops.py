@@ -145,9 +145,11 @@ def pick_kc(cin_span, stride=1, dil=1, has_in2=False, W=None, coutp=None, out_f3
 
 
 def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=None, out=None, out_coff=0,
-               chan_map=None, out_f32=False, residual=None, reps=1, ts=False, tl=False):
+               chan_map=None, out_f32=False, residual=None, reps=1, ts=False, tl=False, head_w=None, partial=None):
     """bf16 tcgen05 conv (pwc_tc_conv_*) on an NHWC bf16 tensor x [N,H,W,pitch]; weight torch [Cout,Cin,3,3] fp32.
-    ts=True: tap-stacked mode for 9*Cout <= 128 (fp32 output)."""
+    ts=True: tap-stacked mode for 9*Cout <= 128 (fp32 output); partial [N,H,W,>=Cout] fp32 is added before the activation.
+    tl=True with head_w [nhead,Cin,3,3] (Cout <= 32): the raw sums of those extra output channels come back as conv3x3_tc.head
+    ([N,H,W,nhead] fp32; pwc_tc_conv_set_head_rows)."""
     import ctypes
     lib = _lib.load()
     st = _lib.stream_handle()
@@ -177,6 +179,11 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
             ws[0:cout, :, 0, :] = w32[:, :, 0, :]
             ws[64:64 + cout, :, 0, :] = w32[:, :, 1, :]
             ws[0:cout, :, 1, :] = w32[:, :, 2, :]
+        if head_w is not None:
+            nh = head_w.shape[0]
+            assert cout <= 32 and 3 * nh <= 32 and head_w.shape[1] == cin
+            for ky in range(3):
+                ws[96 + ky * nh:96 + (ky + 1) * nh, :, 0, :] = head_w.detach().float()[:, :, ky, :]
         w32, wrows = ws, 128
     _lib.check(lib.pwc_pack_conv_weight_bf16(_lib.ptr(w32), _lib.ptr(wp), _lib.ptr(mp), wrows, cin, span, kc, coutp, st), "pack")
     ho, wo = (H - 1) // stride + 1, (W - 1) // stride + 1
@@ -191,6 +198,12 @@ def conv3x3_tc(x, weight, bias, stride=1, dil=1, slope=0.1, in_coff=0, cin_span=
                                (residual.shape[-1] if residual is not None else 0), N, H, W, stride, dil, slope)
     _lib.check(e, "pwc_tc_conv_create")
     try:
+        conv3x3_tc.head = None
+        if head_w is not None:
+            conv3x3_tc.head = torch.full((N, H, W, head_w.shape[0]), 7.0, device=x.device, dtype=torch.float32)
+            _lib.check(lib.pwc_tc_conv_set_head_rows(h, _lib.ptr(conv3x3_tc.head), head_w.shape[0]), "pwc_tc_conv_set_head_rows")
+        if partial is not None:
+            _lib.check(lib.pwc_tc_conv_set_partial(h, _lib.ptr(partial), partial.shape[-1]), "pwc_tc_conv_set_partial")
         _lib.check(lib.pwc_tc_conv_launch(h, st), "pwc_tc_conv_launch")
         if reps > 1:        # timing aid for tools/: CUDA-event time of reps-1 further launches
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -75,6 +75,47 @@ def test_conv3x3_tc_tap_lanes(case, fmt):
     assert got[:, cout:].abs().max().item() == 0.0 if got.shape[1] > cout else True
 
 
+@pytest.mark.parametrize("fmt", ["bf16", "f16"])
+@pytest.mark.parametrize("case", [
+    # cin, cout, nhead, N, H, W      conv2_4 + predict_flow2 / conv3_4 + predict_flow3|upfeat3 shapes, ragged tiles
+    (533, 32, 2, 2, 112, 256), (565, 32, 10, 1, 56, 128), (96, 32, 2, 1, 7, 16), (192, 20, 10, 3, 13, 50), (64, 16, 5, 2, 30, 9),
+])
+def test_conv3x3_tc_head_rows_and_partial(case, fmt):
+    """Two layers over one input in one pass (pwc_tc_conv_set_head_rows): the tap-lane layer's own output is unchanged, the raw sums
+    of the extra channels equal a bias-free conv, and a tap-stacked layer over 32 further channels + that partial
+    (pwc_tc_conv_set_partial) equals the head over all channels."""
+    from opticalflow_b200 import ops
+    cin, cout, nh, N, H, W = case
+    dt = torch.float16 if fmt == "f16" else torch.bfloat16
+    g = torch.Generator().manual_seed(700 + cin + cout + nh)
+    x = torch.randn(N, cin, H, W, generator=g).to(dt)
+    w = (torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin ** 0.5)).to(dt).float()
+    b = torch.randn(cout, generator=g) * 0.1
+    wh = (torch.randn(nh, cin + 32, 3, 3, generator=g) / (3 * (cin + 32) ** 0.5)).to(dt).float()     # head over [32 new | cin]
+    bh = torch.randn(nh, generator=g) * 0.1
+    ref = F.leaky_relu(F.conv2d(x.float(), w, b, padding=1), 0.1)
+    ref_part = F.conv2d(x.float(), wh[:, 32:], None, padding=1)
+    d = torch.device("cuda:0")
+    span = (cin + 15) // 16 * 16
+    xn = torch.zeros(N, H, W, span, dtype=dt)
+    xn[..., :cin] = x.permute(0, 2, 3, 1)
+    with ops.half_format(fmt):
+        out = ops.conv3x3_tc(xn.to(d), w.to(d), b.to(d), 1, 1, 0.1, cin_span=span, tl=True, head_w=wh[:, 32:].to(d))
+        part = ops.conv3x3_tc.head
+        got = out.float().permute(0, 3, 1, 2).cpu()
+        tol = 1.5e-3 if fmt == "f16" else 1e-2
+        assert (got[:, :cout] - ref).abs().max().item() <= tol * ref.abs().max().item()
+        gp = part.permute(0, 3, 1, 2).cpu()
+        assert (gp - ref_part).abs().max().item() <= 2e-5 * max(1.0, ref_part.abs().max().item())       # fp32 sums of exact products
+        # the head: 32 new channels (rounded to the 16-bit format as a real layer output would be) + the partial
+        y = torch.randn(N, 32, H, W, generator=g).to(dt)
+        ref_head = F.conv2d(torch.cat([y.float(), x.float()], 1), wh, bh, padding=1)
+        yn = y.permute(0, 2, 3, 1).contiguous().to(d)
+        head = ops.conv3x3_tc(yn, wh[:, :32].to(d), bh.to(d), 1, 1, 1.0, cin_span=32, out_f32=True, ts=True, partial=part)
+    gh = head.permute(0, 3, 1, 2).cpu()[:, :nh]
+    assert (gh - ref_head).abs().max().item() <= 5e-5 * max(1.0, ref_head.abs().max().item())
+
+
 @pytest.mark.parametrize("case", TC_CASES)
 def test_conv3x3_tc_matches_torch(case):
     from opticalflow_b200 import ops
