@@ -384,30 +384,39 @@ conv_tc_wm_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         ptx::tc_fence_before();
         named_bar(2, 128);
         if (lane == 0) ptx::mbar_arrive(t_empty(acc));       // accumulator is in S now: the next item may start
+        // thread = output pixel, all Cout channels of it in turn (the (channel, row, pixel) enumeration this replaces paid two
+        // integer divisions and a 64-bit address per VALUE; neighbouring lanes still read neighbouring words of S)
         const int et = threadIdx.x - 64;
-        const int nout = p.cout * p.rows * 8;
-        for (int idx = et; idx < nout; idx += 128) {
-          const int px = idx & 7, r1 = idx >> 3, py = r1 % p.rows, co2 = r1 / p.rows;
+        const int npix = p.rows * 8;
+        for (int pxi = et; pxi < npix; pxi += 128) {
+          const int px = pxi & 7, py = pxi >> 3;
           const int oy = ty0 + py, ox = tx0 + px;
           if (oy >= p.H || ox >= p.W) continue;
-          const float* sp = S + (size_t)co2 * p.s_stride + py * 10 + px;
-          float a = __ldg(p.bias + co2);
-#pragma unroll
-          for (int tap = 0; tap < 9; ++tap)
-            a += sp[(size_t)tap * p.cout * p.s_stride + (tap / 3) * 10 + (tap % 3)];
           const long pix = ((long)n * p.H + oy) * p.W + ox;
-          if (p.partial) a += __ldg(p.partial + pix * p.partial_pitch + co2);   // the other input channels' share (WmParams::nhead)
-          float val = lrelu(a, p.slope);
-          if ((p.out_f32 & 3) == 2 && co2 >= 2) {
-            const int k = co2 - 2, j = k & 1, b = (k >> 1) & 1, aa = k >> 2;
-            const long up = (((long)n * 2 * p.H + 2 * oy + aa) * (2 * p.W) + 2 * ox + b) * p.out2_pitch + p.out2_coff + j;
-            const uint16_t hb = pack1_h16(val, p.fp16);
-            reinterpret_cast<uint16_t*>(p.out2)[up] = hb;
-            if (p.up_lo_off) reinterpret_cast<uint16_t*>(p.out2)[up + p.up_lo_off] = pack1_h16(val - unpack1_h16(hb, p.fp16), p.fp16);
-            if (p.up_dup_off) reinterpret_cast<uint16_t*>(p.out2)[up + p.up_dup_off] = hb;
-          } else {
-            if (p.residual) val += p.residual[pix * p.res_pitch + co2];
-            reinterpret_cast<float*>(p.out)[pix * p.out_pitch + p.out_coff + co2] = val;
+          const float* sp0 = S + py * 10 + px;
+          const float* part = p.partial ? p.partial + pix * p.partial_pitch : nullptr;
+          float* o32 = reinterpret_cast<float*>(p.out) + pix * p.out_pitch + p.out_coff;
+          const float* res = p.residual ? p.residual + pix * p.res_pitch : nullptr;
+          const long up0 = (((long)n * 2 * p.H + 2 * oy) * (2 * p.W) + 2 * ox) * p.out2_pitch + p.out2_coff;
+          for (int co2 = 0; co2 < p.cout; ++co2) {
+            const float* sp = sp0 + (size_t)co2 * p.s_stride;
+            float a = __ldg(p.bias + co2);
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap)
+              a += sp[(size_t)tap * p.cout * p.s_stride + (tap / 3) * 10 + (tap % 3)];
+            if (part) a += __ldg(part + co2);              // the other input channels' share (WmParams::nhead)
+            float val = lrelu(a, p.slope);
+            if ((p.out_f32 & 3) == 2 && co2 >= 2) {
+              const int k = co2 - 2, j = k & 1, b = (k >> 1) & 1, aa = k >> 2;
+              const long up = up0 + ((long)aa * (2 * p.W) + b) * p.out2_pitch + j;
+              const uint16_t hb = pack1_h16(val, p.fp16);
+              reinterpret_cast<uint16_t*>(p.out2)[up] = hb;
+              if (p.up_lo_off) reinterpret_cast<uint16_t*>(p.out2)[up + p.up_lo_off] = pack1_h16(val - unpack1_h16(hb, p.fp16), p.fp16);
+              if (p.up_dup_off) reinterpret_cast<uint16_t*>(p.out2)[up + p.up_dup_off] = hb;
+            } else {
+              if (res) val += res[co2];
+              o32[co2] = val;
+            }
           }
         }
         named_bar(2, 128);                                   // S may be overwritten by the next item
