@@ -169,8 +169,8 @@ class PlanMixed(PlanBF16):
             for name, src, dst in ((names[1], self.pa[l], self.pb[l]), (names[2], self.pb[l], self.pa[l])):
                 key = name + ".0"
                 if C <= 32 and THIN_TC:
-                    # (experiment, off by default) three tap lanes, split in and out; the mma.sync form below sits at the legacy
-                    # tensor pipe's limit (3 x 25 GFLOP at ~300 TFLOP/s = 77-89 us per layer)
+                    # (experiment, off by default) three tap lanes, split in and out; the mma.sync form below runs 3 x 8.5 GFLOP at
+                    # 290-330 TFLOP/s (54% of the legacy tensor pipe) = 77-89 us per layer
                     self._tc(key, C, C, src, 0, C, dst, 0, NP, h, w, in_lo=CP, out_lo=CP, no_small=True, tl=True)
                 elif C <= 32:
                     self._thin_split(key, C, src, dst, NP, h, w)
