@@ -557,6 +557,163 @@ static int launch_c16_tma(ThinConvParams& p, cudaStream_t s) {
   return (int)launch_pdl(conv_c16_tma_kernel<false>, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), 0, s, tm1, tm2, p, (int)nt);
 }
 
+// ---- 16 -> 16 channels, stride 1, SPLIT precision (conv1aa, conv1b of the 'mixed' plan): the TMA kernel above with [hi | lo] pixels.
+// Pixels are 64 bytes (16 hi + 16 lo channels), the patch comes in SWIZZLE_64B (the 16-byte chunk index is XORed with bits 7-8 of
+// the address = (pixel >> 1) & 3: conflict-free ldmatrix; 72-pixel rows = 9 x 512 B keep that phase independent of the row and of
+// the 16-pixel m-tile, so taps stay immediates), BOTH weight planes live in registers (72), and a tap issues its three products
+// x_hi*W_hi, x_hi*W_lo, x_lo*W_hi on four accumulator chains; the epilogue stores hi and the rounding residual lo straight from
+// the accumulators.  The generic kernel spends a quarter of its instructions staging the patch with cp.async and re-reads the
+// weights from shared memory for every m-tile.
+constexpr int kC16SPW = 72, kC16SPatch = kC16IH * kC16SPW * 64;
+
+template <int MT, int KY, bool F16>
+__device__ __forceinline__ void c16s_taps(const uint32_t (&ah)[3], const uint32_t (&al)[3], const uint32_t (&bh)[9][2][2],
+                                          const uint32_t (&bl)[9][2][2], float (&acc)[2][2][4]) {
+#pragma unroll
+  for (int kx = 0; kx < 3; ++kx) {
+    constexpr int O0 = (KY * kC16SPW + 16 * MT) * 64, O1 = O0 + 16 * 64;
+    const int t = KY * 3 + kx;
+    uint32_t a0[4], a1[4];
+    c16_ldsm4<O0>(a0, ah[kx]);
+    c16_ldsm4<O1>(a1, ah[kx]);
+    mma_h16<F16>(acc[0][0], a0, bh[t][0][0], bh[t][0][1]); mma_h16<F16>(acc[0][1], a0, bh[t][1][0], bh[t][1][1]);
+    mma_h16<F16>(acc[1][0], a1, bh[t][0][0], bh[t][0][1]); mma_h16<F16>(acc[1][1], a1, bh[t][1][0], bh[t][1][1]);
+    mma_h16<F16>(acc[0][0], a0, bl[t][0][0], bl[t][0][1]); mma_h16<F16>(acc[0][1], a0, bl[t][1][0], bl[t][1][1]);
+    mma_h16<F16>(acc[1][0], a1, bl[t][0][0], bl[t][0][1]); mma_h16<F16>(acc[1][1], a1, bl[t][1][0], bl[t][1][1]);
+    c16_ldsm4<O0>(a0, al[kx]);
+    c16_ldsm4<O1>(a1, al[kx]);
+    mma_h16<F16>(acc[0][0], a0, bh[t][0][0], bh[t][0][1]); mma_h16<F16>(acc[0][1], a0, bh[t][1][0], bh[t][1][1]);
+    mma_h16<F16>(acc[1][0], a1, bh[t][0][0], bh[t][0][1]); mma_h16<F16>(acc[1][1], a1, bh[t][1][0], bh[t][1][1]);
+  }
+}
+
+template <bool F16>
+__global__ void __launch_bounds__(256, 2)
+conv_c16_split_tma_kernel(const __grid_constant__ CUtensorMap tm1, const ThinConvParams p, int n_tiles) {
+  extern __shared__ __align__(1024) uint8_t c16s_smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, c = lane & 3;
+  const uint32_t p_addr = (ptx::smem_addr(c16s_smem) + 1023u) & ~1023u;
+  const uint32_t bar0 = p_addr + 2u * kC16SPatch;
+  if (tid == 0) {
+    ptx::prefetch_tmap(&tm1);
+    ptx::mbar_init(bar0, 1); ptx::mbar_init(bar0 + 8, 1);
+    ptx::fence_barrier_init();
+  }
+  // weight rows [9 * 16][W_hi(16) | W_lo(16)]: B fragments of both planes
+  uint32_t bh[9][2][2], bl[9][2][2];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const uint32_t* wr = reinterpret_cast<const uint32_t*>(p.w + (t * 16 + 8 * j + g) * 32);
+      bh[t][j][0] = __ldg(wr + c); bh[t][j][1] = __ldg(wr + 4 + c);
+      bl[t][j][0] = __ldg(wr + 8 + c); bl[t][j][1] = __ldg(wr + 12 + c);
+    }
+  float bia[2][2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) { bia[j][0] = p.bias[8 * j + 2 * c]; bia[j][1] = p.bias[8 * j + 2 * c + 1]; }
+  uint32_t ah[3], al[3];
+  {
+    const int px = (lane & 7) + 8 * ((lane >> 3) & 1), half = lane >> 4;
+#pragma unroll
+    for (int kx = 0; kx < 3; ++kx) {
+      const int q = px + kx, sw = (q >> 1) & 3;
+      ah[kx] = p_addr + (uint32_t)((warp * kC16SPW + q) * 64 + 16 * (half ^ sw));
+      al[kx] = p_addr + (uint32_t)((warp * kC16SPW + q) * 64 + 16 * ((half + 2) ^ sw));
+    }
+  }
+  __syncthreads();
+  pdl_wait();
+  pdl_launch_dependents();
+
+  const int H = p.H, W = p.W;
+  const float inv_tx = 1.0f / (float)p.tiles_x, inv_ty = 1.0f / (float)p.tiles_y;
+  auto decode = [&](int tile, int& ox0, int& oy0, int& img) {
+    const int t2 = (int)(((float)tile + 0.5f) * inv_tx); const int tx = tile - t2 * p.tiles_x;
+    img = (int)(((float)t2 + 0.5f) * inv_ty); const int ty = t2 - img * p.tiles_y;
+    ox0 = tx * 64; oy0 = ty * 8;
+  };
+  auto issue = [&](int tile, int buf) {                        // one thread
+    int ox0, oy0, img;
+    decode(tile, ox0, oy0, img);
+    ptx::mbar_expect_tx(bar0 + 8u * buf, (uint32_t)kC16SPatch);
+    ptx::tma_load_4d(p_addr + (uint32_t)buf * kC16SPatch, &tm1, bar0 + 8u * buf, 0, ox0 - 1, oy0 - 1, img);
+  };
+  int tile = blockIdx.x;
+  if (tid == 0 && tile < n_tiles) issue(tile, 0);
+  uint32_t ph0 = 0, ph1 = 0;
+  for (int it = 0; tile < n_tiles; tile += gridDim.x, ++it) {
+    const int b = it & 1;
+    if (tid == 0 && tile + (int)gridDim.x < n_tiles) issue(tile + gridDim.x, b ^ 1);   // that buffer was released by the last sync
+    if (b == 0) { ptx::mbar_wait(bar0, ph0); ph0 ^= 1; } else { ptx::mbar_wait(bar0 + 8, ph1); ph1 ^= 1; }
+    int ox0, oy0, img;
+    decode(tile, ox0, oy0, img);
+    const uint32_t boff = (uint32_t)b * kC16SPatch;
+    const uint32_t abh[3] = {ah[0] + boff, ah[1] + boff, ah[2] + boff};
+    const uint32_t abl[3] = {al[0] + boff, al[1] + boff, al[2] + boff};
+    const int oy = oy0 + warp;
+    if (oy < H) {
+      __nv_bfloat16* orow = p.out + (((long)img * H + oy) * W + ox0 + g) * p.out_pitch + p.out_coff + 2 * c;
+      const long opitch = p.out_pitch;
+#pragma unroll
+      for (int mp = 0; mp < 2; ++mp) {
+        if (ox0 + 32 * mp >= W) break;
+        float acc[2][2][4];
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[m][j][e] = 0.f;
+        if (mp == 0) {
+          c16s_taps<0, 0, F16>(abh, abl, bh, bl, acc); c16s_taps<0, 1, F16>(abh, abl, bh, bl, acc); c16s_taps<0, 2, F16>(abh, abl, bh, bl, acc);
+        } else {
+          c16s_taps<2, 0, F16>(abh, abl, bh, bl, acc); c16s_taps<2, 1, F16>(abh, abl, bh, bl, acc); c16s_taps<2, 2, F16>(abh, abl, bh, bl, acc);
+        }
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+              if (ox0 + 32 * mp + 16 * m + g + 8 * h < W) {
+                const float v0 = acc[m][j][2 * h] + bia[j][0], v1 = acc[m][j][2 * h + 1] + bia[j][1];
+                const float r0 = fmaxf(v0, v0 * p.slope), r1 = fmaxf(v1, v1 * p.slope);      // 0 <= slope <= 1
+                const uint32_t hi = pack2_h16(r0, r1, F16 ? 1 : 0);
+                const float2 hb = unpack2_h16(hi, F16 ? 1 : 0);
+                uint32_t* o = reinterpret_cast<uint32_t*>(orow + (32 * mp + 16 * m + 8 * h) * opitch + 8 * j);
+                o[0] = hi;
+                o[8] = pack2_h16(r0 - hb.x, r1 - hb.y, F16 ? 1 : 0);                        // lo plane: 16 channels further
+              }
+      }
+    }
+    __syncthreads();                                            // buffer b may be refilled
+  }
+}
+
+static int launch_c16_split_tma(ThinConvParams& p, cudaStream_t s) {
+  p.tiles_x = cdiv(p.W, 64); p.tiles_y = cdiv(p.H, 8);
+  const long nt = (long)p.N * p.tiles_x * p.tiles_y;
+  CUtensorMap tm1;
+  int e = make_tmap_nhwc(&tm1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p.in + p.in_coff, p.in_pitch, 32, p.W, p.H, p.N, 32,
+                         kC16SPW, kC16IH, 1, 1, CU_TENSOR_MAP_SWIZZLE_64B);
+  if (e) return e;
+  const int smem = 2 * kC16SPatch + 16 + 1024;
+  static int attr_dev = -1;
+  int dev = 0; cudaGetDevice(&dev);
+  if (attr_dev != dev) {
+    cudaError_t ce = cudaFuncSetAttribute(conv_c16_split_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (ce == cudaSuccess) ce = cudaFuncSetAttribute(conv_c16_split_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (ce != cudaSuccess) return (int)ce;
+    attr_dev = dev;
+  }
+  static const int ctas = []() { const char* e = getenv("PWC_THIN_C16S_CTAS"); return e ? atoi(e) : 148 * 2; }();
+  if (half_format())
+    return (int)launch_pdl(conv_c16_split_tma_kernel<true>, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), smem, s, tm1, p, (int)nt);
+  return (int)launch_pdl(conv_c16_split_tma_kernel<false>, dim3((unsigned)(nt < ctas ? nt : ctas)), dim3(256), smem, s, tm1, p, (int)nt);
+}
+
 static int launch_c16(ThinConvParams& p, cudaStream_t s) {
   p.tiles_x = cdiv(p.W, 64); p.tiles_y = cdiv(p.H, 8);
   const long nt = (long)p.N * p.tiles_x * p.tiles_y;
@@ -663,6 +820,9 @@ extern "C" int pwc_conv3x3_thin_split_strided_fwd(const void* in, long in_pitch,
   p.flow_out = nullptr; p.residual = nullptr; p.res_pitch = 0;
   cudaStream_t s = (cudaStream_t)stream;
   const bool f16 = half_format() != 0;
+  static const int use_c16s = []() { const char* e = getenv("PWC_THIN_C16_SPLIT"); return e ? atoi(e) : 1; }();
+  if (use_c16s && cin == 16 && cout == 16 && stride == 1 && (long)N * cdiv(H, 8) * cdiv(W, 64) < (1L << 20))
+    return launch_c16_split_tma(p, s);
 #define PWC_THIN_SPLIT(NTv, KSv) \
   if (cout == 8 * NTv && cin == 16 * KSv) return f16 ? launch_thin<NTv, KSv, true, true>(p, s) : launch_thin<NTv, KSv, false, true>(p, s)
   PWC_THIN_SPLIT(2, 1); PWC_THIN_SPLIT(4, 1); PWC_THIN_SPLIT(2, 2); PWC_THIN_SPLIT(4, 2);
