@@ -7,8 +7,10 @@ from oracle import pwcnet_oracle as O
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("mode", ["bf16", "fp32"])
-def test_pipeline_matches_blocking_forward(mode):
+@pytest.mark.parametrize("mode,inflight", [("bf16", None), ("bf16", 1), ("mixed", None), ("mixed", 3), ("fp32", None)])
+def test_pipeline_matches_blocking_forward(mode, inflight):
+    """inflight None = the default (two plans on two compute streams for the graph plans, one for fp32); every plan instance
+    must return exactly what the blocking call's plan returns."""
     from opticalflow_b200 import driver
     from opticalflow_b200.models.PWCNet import PWCDCNet
     dev = torch.device("cuda", 0)
@@ -18,7 +20,8 @@ def test_pipeline_matches_blocking_forward(mode):
     xs = [O.synthetic_input(B, H, W, 10 + i).pin_memory() for i in range(5)]
     want = [m(x.to(dev)).cpu() for x in xs]
     got = {}
-    pipe = driver.FlowPipeline(m, B, H, W, dev)
+    pipe = driver.FlowPipeline(m, B, H, W, dev, inflight=inflight)
+    assert pipe.inflight == (inflight if inflight else (1 if mode == "fp32" else 2)) and pipe.depth >= pipe.inflight
     n = pipe.run(iter(xs), sink=lambda i, f: got.__setitem__(i, f.clone()))
     assert n == 5 and sorted(got) == list(range(5))
     for i in range(5):
