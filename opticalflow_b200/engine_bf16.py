@@ -99,6 +99,7 @@ S2D_DEC = os.environ.get("PWC_TC_S2D_DEC", "1") != "0"
 S2D_DEC_MAXLVL = int(os.environ.get("PWC_TC_S2D_DEC_MAXLVL", "2"))
 S2D_DEC_MAXCOUT = int(os.environ.get("PWC_TC_S2D_DEC_MAXCOUT", "32"))
 TL_MAXLVL = int(os.environ.get("PWC_TC_TL_MAXLVL", "3"))        # decoder levels whose Cout <= 64 layers run in tap-lane form
+HEAD_ROWS = os.environ.get("PWC_TC_HEAD_ROWS", "1") != "0"       # predict_flow2's shared input channels as head rows of conv2_4
 
 
 def _pfup_weights(lvl):
@@ -411,6 +412,7 @@ class PlanBF16:
             else:
                 self._tc(names[2] + ".0", PYR_CH[l], PYR_CH[l], self.pb[l], 0, PYR_CP[l], self.f1_6, 0, NP, h, w,
                          dst2=self.f2[l], n_split=(NP if vid else B))
+        self.head_part = {}
         for l in (6, 5, 4, 3, 2):
             h, w = self.hw[l]
             cat, wd = self.cat[l], concat_width(l)
@@ -422,8 +424,15 @@ class PlanBF16:
                 g = 128 // cout
                 if TL_MODE and cout <= 64 and l <= TL_MAXLVL:
                     # Cout = 64 / 32: tap lanes -- 6 / 3 MMA groups per chunk instead of 9 (WmParams::tl)
+                    head = None
+                    if k == 4 and l == 2 and HEAD_ROWS and DEC_START[4] == 32:
+                        # predict_flow2's sums over the 533 channels this layer reads ride in its idle MMA rows (include/pwc_b200.h,
+                        # pwc_tc_conv_set_head_rows): the head's own pass over the concat buffer cost 69 us for 2 output channels
+                        hsuf = (lambda sd: (sd["predict_flow2.weight"][:, 32:].contiguous(), sd["predict_flow2.bias"]))
+                        self.head_part[l] = torch.zeros(B, h, w, 2, device=dev, dtype=torch.float32)
+                        head = (hsuf, 2, self.head_part[l])
                     self._tc(f"conv{l}_{k}.0", len(cm), cout, cat, DEC_START[k], wd - DEC_START[k], cat, DEC_WRITE[k], B, h, w,
-                             cmap=cm, tl=True)
+                             cmap=cm, tl=True, head=head)
                     continue
                 if S2D_DEC and cout <= S2D_DEC_MAXCOUT and l <= S2D_DEC_MAXLVL and w % g == 0:
                     # Cout = 64 / 32: g adjacent pixels form one super-pixel so that all 128 MMA rows carry outputs
@@ -443,6 +452,10 @@ class PlanBF16:
                 self._tc(f"pfup{l}", len(cm), 10, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=2,
                          dst2=self.cat[l - 1], dst2_coff=UPFEAT_OFF, wfn=_pfup_weights(l), ts=True)
                 self._deconv(f"deconv{l}", 2, self.flow[l], 0, 4, self.cat[l - 1], UPFLOW_OFF, h, w, dst_b=self.upflow[l - 1])
+            elif l in self.head_part:
+                first32 = (lambda sd: (sd["predict_flow2.weight"][:, :32].contiguous(), sd["predict_flow2.bias"]))
+                self._tc(f"predict_flow{l}", 32, 2, cat, 0, 32, self.flow[l], 0, B, h, w, slope=1.0, out_f32=True, ts=True,
+                         wfn=first32, flops=2.0 * B * h * w * 2 * len(cm) * 9, partial=self.head_part[l])
             else:
                 self._tc(f"predict_flow{l}", len(cm), 2, cat, 0, wd, self.flow[l], 0, B, h, w, slope=1.0, cmap=cm, out_f32=True,
                          ts=True)
